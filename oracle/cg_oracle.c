@@ -1,0 +1,240 @@
+/* oracle/cg_oracle.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU oracle for the dense conjugate-gradient hot path of
+ * mawunyega/conjugate_gradient (serialConjugate.c, parallel_cg.c).  Only
+ * tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load this library; the product (libcgb200.so, cg_b200) never does.
+ *
+ * Parity status: PINNED.  tests/test_oracle.py checks this restatement
+ *   - against the reference's shipped fixtures (matrixA.txt/vectorb.txt/
+ *     initialguess.txt -> x = (2/3, 1/3); matrixA1.txt/vectorb1.txt/X0.txt ->
+ *     x = (-1, 1, -1, 1)), committed under tests/golden/;
+ *   - bit for bit against the real reference sources compiled into oracle/_ref
+ *     (oracle/build_ref.sh) at n in {2, 4, 512, 2048}, FP32 as shipped and the
+ *     mechanical float->double build, serial and MPI (through oracle/mpi_shim).
+ *
+ * Build: see oracle/Makefile (gcc -O2 -ffp-contract=off, no -march).
+ */
+#define _GNU_SOURCE
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <time.h>
+#include <pthread.h>
+
+#include "spd_gen_ref.h"
+
+typedef struct {
+    int64_t iterations;   /* loop bodies executed (x and r updated that many times) */
+    int64_t break_k;      /* 0-based loop index at `break`, -1 if the loop ran out   */
+    int64_t first_hit_k;  /* first k at which sqrt(beta) < eps held, -1 if never     */
+    double  final_beta;   /* last r.r                                                */
+    double  rsold0;       /* initial r.r                                             */
+    double  seconds;      /* wall time of the solver region, where the reference     */
+                          /* times it (serialConjugate.c:208,249; parallel_cg.c:278-279,328-329) */
+} orc_stats;
+
+static void *orc_alloc(size_t bytes)
+{
+    void *p = NULL;
+    if (bytes == 0) bytes = 64;
+    if (posix_memalign(&p, 64, bytes) != 0 || !p) {
+        fprintf(stderr, "oracle: cannot allocate %zu bytes\n", bytes);
+        abort();
+    }
+    return p;
+}
+
+static double orc_now(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+#define REAL double
+#define SFX f64
+#include "cg_oracle_impl.h"
+#undef REAL
+#undef SFX
+
+#define REAL float
+#define SFX f32
+#include "cg_oracle_impl.h"
+#undef REAL
+#undef SFX
+
+/* ------------------------------------------------------------------ generator */
+
+/* Rows [row0, row0+m) of the seeded SPD matrix, row-major, into A (m x n). */
+void orc_gen_fill_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                    unsigned flags)
+{
+    const uint64_t key = orc_gen_key(seed);
+    for (int64_t i = 0; i < m; ++i)
+        for (int64_t j = 0; j < n; ++j)
+            A[i * n + j] = orc_gen_a(key, (uint64_t)n, (uint64_t)(row0 + i), (uint64_t)j, flags);
+}
+
+void orc_gen_fill_b(double *b, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                    unsigned flags)
+{
+    const uint64_t key = orc_gen_key(seed);
+    for (int64_t i = 0; i < m; ++i)
+        b[i] = orc_gen_b(key, (uint64_t)n, (uint64_t)(row0 + i), flags);
+}
+
+double orc_gen_sample_u(uint64_t seed, uint64_t k)
+{
+    return orc_gen_u(orc_gen_key(seed), k);
+}
+
+/* ------------------------------------------------- threaded SPMD (timing leg) */
+/* The same per-rank arithmetic as orc_conjugrad_spmd_f64, with the P ranks run
+ * as P host threads (the reference runs them as P MPI processes,
+ * parallel_cg.c:81-83).  Each thread generates and first-touches its own row
+ * block, so the matrix never exists twice (the reference keeps a second full
+ * copy on rank 0, parallel_cg.c:103) and lands on the thread's NUMA node.
+ * All-gather and all-reduce are shared arrays + barriers with rank-ordered
+ * sums, i.e. the same results as the sequential restatement.  Used by
+ * bench.py's cpu_baseline and --impl reference legs at sizes the real
+ * reference cannot index (n > 46340). */
+
+typedef struct {
+    int64_t n, P, m, max_iter;
+    uint64_t seed; unsigned flags;
+    double eps; int ignore_stop;
+    double *b, *x, *r, *ploc, *pall, *Ap, *tx, *tr, *tp;
+    double *slots;
+    pthread_barrier_t bar;
+    /* outputs (written by rank 0) */
+    orc_stats st;
+    double gen_seconds;
+} orc_team;
+
+typedef struct { orc_team *tm; int64_t g; } orc_member;
+
+static double team_allreduce(orc_team *tm, int64_t g, double part)
+{
+    tm->slots[g * 8] = part;                  /* one cache line per rank */
+    pthread_barrier_wait(&tm->bar);
+    double s = tm->slots[0];
+    for (int64_t q = 1; q < tm->P; ++q) s += tm->slots[q * 8];
+    pthread_barrier_wait(&tm->bar);
+    return s;
+}
+
+static void *team_rank_main(void *arg)
+{
+    orc_member *me = (orc_member *)arg;
+    orc_team *tm = me->tm;
+    const int64_t g = me->g, n = tm->n, m = tm->m, o = g * m;
+    double t0 = orc_now();
+    double *Ablk = orc_alloc((size_t)m * (size_t)n * sizeof(double));
+    orc_gen_fill_A(Ablk, n, o, m, tm->seed, tm->flags);
+    orc_gen_fill_b(tm->b + o, n, o, m, tm->seed, tm->flags);
+    memset(tm->x + o, 0, (size_t)m * sizeof(double));
+    pthread_barrier_wait(&tm->bar);
+    if (g == 0) tm->gen_seconds = orc_now() - t0;
+
+    double rsold, alpha, beta = 0.0;
+    int64_t k, done_iters = 0, break_k = -1, first_hit = -1;
+    pthread_barrier_wait(&tm->bar);
+    t0 = orc_now();
+    orc_matvec_f64(tm->Ap + o, Ablk, tm->x, m, n);
+    orc_residual_f64(tm->r + o, tm->b + o, tm->Ap + o, m);
+    orc_residual_f64(tm->ploc + o, tm->b + o, tm->Ap + o, m);
+    rsold = team_allreduce(tm, g, orc_vecvec_f64(tm->r + o, tm->r + o, m));
+    double rs0 = rsold;
+    for (k = 0; k < tm->max_iter; ++k) {
+        memcpy(tm->pall + o, tm->ploc + o, (size_t)m * sizeof(double));
+        pthread_barrier_wait(&tm->bar);                      /* allgather done */
+        orc_matvec_f64(tm->Ap + o, Ablk, tm->pall, m, n);
+        alpha = team_allreduce(tm, g, orc_vecvec_f64(tm->ploc + o, tm->Ap + o, m));
+        alpha = rsold / alpha;
+        /* x is replicated in the reference; each thread updates its slice,
+         * element-wise identical arithmetic (parallel_cg.c:299,303). */
+        orc_scalarvec_f64(tm->tx + o, tm->pall + o, alpha, m);
+        orc_vecadd_f64(tm->x + o, tm->x + o, tm->tx + o, m);
+        orc_scalarvec_f64(tm->tr + o, tm->Ap + o, alpha, m);
+        orc_vecsub_f64(tm->r + o, tm->r + o, tm->tr + o, m);
+        beta = team_allreduce(tm, g, orc_vecvec_f64(tm->r + o, tm->r + o, m));
+        done_iters = k + 1;
+        if (sqrt(beta) < tm->eps) {
+            if (first_hit < 0) first_hit = k;
+            if (!tm->ignore_stop) { break_k = k; break; }
+        }
+        orc_scalarvec_f64(tm->tp + o, tm->ploc + o, beta / rsold, m);
+        orc_vecadd_f64(tm->ploc + o, tm->r + o, tm->tp + o, m);
+        rsold = beta;
+    }
+    pthread_barrier_wait(&tm->bar);
+    if (g == 0) {
+        tm->st.seconds = orc_now() - t0;
+        tm->st.iterations = done_iters;
+        tm->st.break_k = break_k;
+        tm->st.first_hit_k = first_hit;
+        tm->st.final_beta = beta;
+        tm->st.rsold0 = rs0;
+    }
+    free(Ablk);
+    return NULL;
+}
+
+/* Generated-problem SPMD solve on P host threads.  x_out (n doubles) may be NULL.
+ * Returns 0, or -1 if n % P != 0 (parallel_cg.c:86-90). */
+int orc_team_solve_generated(int64_t n, uint64_t seed, unsigned flags, int64_t P,
+                             double eps, int64_t max_iter, int ignore_stop,
+                             double *x_out, orc_stats *st, double *gen_seconds)
+{
+    if (P < 1 || n % P != 0) return -1;
+    orc_team tm;
+    memset(&tm, 0, sizeof tm);
+    tm.n = n; tm.P = P; tm.m = n / P; tm.max_iter = max_iter;
+    tm.seed = seed; tm.flags = flags; tm.eps = eps; tm.ignore_stop = ignore_stop;
+    size_t vb = (size_t)n * sizeof(double);
+    tm.b = orc_alloc(vb); tm.x = orc_alloc(vb); tm.r = orc_alloc(vb);
+    tm.ploc = orc_alloc(vb); tm.pall = orc_alloc(vb); tm.Ap = orc_alloc(vb);
+    tm.tx = orc_alloc(vb); tm.tr = orc_alloc(vb); tm.tp = orc_alloc(vb);
+    tm.slots = orc_alloc((size_t)P * 8 * sizeof(double));
+    pthread_barrier_init(&tm.bar, NULL, (unsigned)P);
+    pthread_t *th = malloc((size_t)P * sizeof *th);
+    orc_member *mb = malloc((size_t)P * sizeof *mb);
+    for (int64_t g = 0; g < P; ++g) {
+        mb[g].tm = &tm; mb[g].g = g;
+        pthread_create(&th[g], NULL, team_rank_main, &mb[g]);
+    }
+    for (int64_t g = 0; g < P; ++g) pthread_join(th[g], NULL);
+    if (x_out) memcpy(x_out, tm.x, vb);
+    if (st) *st = tm.st;
+    if (gen_seconds) *gen_seconds = tm.gen_seconds;
+    pthread_barrier_destroy(&tm.bar);
+    free(th); free(mb); free(tm.slots);
+    free(tm.b); free(tm.x); free(tm.r); free(tm.ploc); free(tm.pall);
+    free(tm.Ap); free(tm.tx); free(tm.tr); free(tm.tp);
+    return 0;
+}
+
+/* Bounded matVec sample for the cpu_baseline leg: `rows` rows of the generated
+ * n-column matrix times a generated vector, `reps` passes, one thread; returns
+ * seconds per pass.  checksum defeats dead-code elimination. */
+double orc_time_matvec_sample(int64_t n, int64_t rows, uint64_t seed, int reps,
+                              double *checksum)
+{
+    double *A = orc_alloc((size_t)rows * (size_t)n * sizeof(double));
+    double *v = orc_alloc((size_t)n * sizeof(double));
+    double *y = orc_alloc((size_t)rows * sizeof(double));
+    orc_gen_fill_A(A, n, 0, rows, seed, 0);
+    orc_gen_fill_b(v, n, 0, n, seed, 0);
+    double t0 = orc_now(), acc = 0.0;
+    for (int r = 0; r < reps; ++r) {
+        orc_matvec_f64(y, A, v, rows, n);
+        acc += y[(r * 7919) % rows];
+    }
+    double dt = (orc_now() - t0) / (double)reps;
+    if (checksum) *checksum = acc;
+    free(A); free(v); free(y);
+    return dt;
+}

@@ -1,0 +1,128 @@
+"""CPU-only: pins the oracle (oracle/cg_oracle.c) against the reference.
+
+1. against golden vectors produced by the REAL reference (tests/golden/golden.json,
+   made by tests/golden/make_golden.py from oracle/_ref) -- runs everywhere;
+2. bit for bit against the live oracle/_ref build when it is present (build
+   container; on the GPU box the prebuilt files travel with the snapshot).
+"""
+import numpy as np
+import pytest
+
+import _oracle as O
+from conftest import unhex
+
+EPS = 1.0e-6  # serialConjugate.c:28
+
+
+def case_inputs(c):
+    n = c["n"]
+    if "A" in c:
+        return unhex(c["A"]).reshape(n, n), unhex(c["b"]), unhex(c["x0"])
+    return O.gen_A(n, c["seed"], c["flags"]), O.gen_b(n, c["seed"], c["flags"]), np.zeros(n)
+
+
+@pytest.mark.parametrize("tag", ["g1", "g2", "g3", "g4"])
+@pytest.mark.parametrize("prec", ["f64", "f32"])
+def test_oracle_matches_reference_golden_bit_for_bit(golden, tag, prec):
+    c = golden["cases"][tag]
+    dt = np.float64 if prec == "f64" else np.float32
+    A, b, x0 = (a.astype(dt) for a in case_inputs(c))
+    x, st = O.conjugrad(A, b, x0, eps=EPS)
+    want = unhex(c["x"][f"serial_{prec}"], dt)
+    assert x.tobytes() == want.tobytes()
+    for P in c["ranks"]:
+        xs, _ = O.conjugrad(A, b, x0, eps=EPS, ranks=P)
+        want = unhex(c["x"][f"spmd{P}_{prec}"], dt)
+        assert xs.tobytes() == want.tobytes(), (tag, prec, P)
+
+
+def test_shipped_fixtures_known_answers(golden):
+    # G1 -> (2/3, 1/3) at k=1 with beta = 0; G2 -> (-1,1,-1,1) at k=3
+    A, b, x0 = case_inputs(golden["cases"]["g1"])
+    x, st = O.conjugrad(A, b, x0)
+    assert st["break_k"] == 1 and st["final_beta"] == 0.0
+    np.testing.assert_allclose(x, [2 / 3, 1 / 3], rtol=1e-15)
+    A, b, x0 = case_inputs(golden["cases"]["g2"])
+    x, st = O.conjugrad(A, b, x0)
+    assert st["break_k"] == 3
+    np.testing.assert_allclose(x, [-1, 1, -1, 1], rtol=1e-13)
+    np.testing.assert_allclose(x, np.linalg.solve(A, b), rtol=1e-13)
+
+
+def test_generated_iteration_counts(golden):
+    # FP64 breaks at k=4 (n=512) and k=3 (n=2048)
+    for tag, k64 in (("g3", 4), ("g4", 3)):
+        A, b, x0 = case_inputs(golden["cases"][tag])
+        x, st = O.conjugrad(A, b, x0)
+        assert st["break_k"] == k64
+        xs = np.linalg.solve(A, b)
+        assert np.linalg.norm(x - xs) / np.linalg.norm(xs) < 1e-7
+
+
+@pytest.mark.parametrize("n,ranks", [(2, 1), (2, 2), (4, 4), (512, 8), (2048, 4)])
+@pytest.mark.parametrize("prec", ["f64", "f32"])
+def test_oracle_vs_live_reference(n, ranks, prec):
+    if not (O.ref_available("serial", prec, n) and O.ref_available("parallel", prec, n)):
+        pytest.skip("oracle/_ref not built (needs /root/reference; run make -C oracle)")
+    dt = np.float64 if prec == "f64" else np.float32
+    rng = np.random.default_rng(n * 31 + ranks)
+    if n <= 4:
+        R = rng.random((n, n)); A = (0.5 * (R + R.T) + n * np.eye(n)).astype(dt)
+        b = rng.random(n).astype(dt); x0 = rng.random(n).astype(dt)
+    else:
+        A = O.gen_A(n, 777 + n).astype(dt); b = O.gen_b(n, 777 + n).astype(dt)
+        x0 = (0.01 * rng.random(n)).astype(dt)      # non-zero guess: exercises A*x0
+    x, _ = O.conjugrad(A, b, x0)
+    assert x.tobytes() == O.ref_conjugrad(A, b, x0).tobytes()
+    xs, _ = O.conjugrad(A, b, x0, ranks=ranks)
+    assert xs.tobytes() == O.ref_conjugrad(A, b, x0, ranks=ranks).tobytes()
+
+
+def test_threaded_team_equals_sequential_spmd():
+    n, seed = 512, 99
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    for P in (1, 2, 8):
+        xt, st = O.team_solve_generated(n, seed, P)
+        xs, ss = O.conjugrad(A, b, np.zeros(n), ranks=P)
+        assert xt.tobytes() == xs.tobytes()
+        assert st["iterations"] == ss["iterations"] and st["final_beta"] == ss["final_beta"]
+    with pytest.raises(ValueError):
+        O.team_solve_generated(510, seed, 4)       # parallel_cg.c:86-90
+
+
+def test_fixed_iteration_mode_keeps_iterating():
+    n, seed = 256, 5
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    x, st = O.conjugrad(A, b, np.zeros(n), max_iter=12, ignore_stop=True)
+    assert st["iterations"] == 12 and st["break_k"] == -1 and 0 <= st["first_hit_k"] < 12
+
+
+def test_generator_known_answers(golden):
+    g = golden["generator"]
+    seed = golden["seed"]
+    for k, hx in g["u"].items():
+        u = O.lib().orc_gen_sample_u(seed, int(k))
+        assert u.hex() == hx and 0.0 <= u < 1.0
+    assert O.gen_A(8, seed).ravel().tobytes() == unhex(g["A8"]).tobytes()
+    assert O.gen_b(8, seed).tobytes() == unhex(g["b8"]).tobytes()
+    assert O.gen_A(8, seed, O.GEN_ROUND4).ravel().tobytes() == unhex(g["A8_round4"]).tobytes()
+
+
+def test_generator_construction_matches_generateSPDmatrix():
+    # generateSPDmatrix.m:4-17: A = 0.5(R+R') + n I with R ~ U(0,1); b ~ U(0,1)
+    n, seed = 300, 4242
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    assert (A == A.T).all()
+    off = A[~np.eye(n, dtype=bool)]
+    assert off.min() > 0.0 and off.max() < 1.0 and abs(off.mean() - 0.5) < 0.01
+    d = np.diag(A)
+    assert d.min() >= n and d.max() < n + 1
+    assert b.min() >= 0.0 and b.max() < 1.0
+    w = np.linalg.eigvalsh(A)
+    assert w[0] > 0 and w[-1] / w[0] < 2.0          # kappa ~ 1.5
+    # row blocks generated independently agree with the whole matrix
+    assert (O.gen_A(n, seed, row0=100, m=50) == A[100:150]).all()
+    # the %.4f round trip of generateSPDmatrix.m:29
+    Ar = O.gen_A(n, seed, O.GEN_ROUND4)
+    assert np.abs(Ar - A).max() <= 0.5e-4 + 1e-12 and (Ar == Ar.T).all()
+    assert np.allclose(Ar * 1e4, np.rint(Ar * 1e4), atol=1e-6)
