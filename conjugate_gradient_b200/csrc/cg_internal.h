@@ -1,0 +1,46 @@
+/* cg_internal.h -- private to libcgb200.so (not installed). */
+#ifndef CG_INTERNAL_H
+#define CG_INTERNAL_H
+#include <cuda_runtime_api.h>
+#include <nccl.h>
+#include <stdint.h>
+#include "cg_kernels.h"
+
+struct cgb_graph_key {
+    int64_t n, m, max_iter;
+    double eps;
+    int ignore_stop, chunk;
+    cgk_gemv_plan plan;
+    const void *A;
+};
+
+struct cgb_ctx {
+    int device, rank, ranks, sm_count, has_comm, loaded;
+    char name[64];
+    cudaStream_t stream;
+    cudaEvent_t ev[3];
+    cudaEvent_t *gemv_ev;
+    int n_gemv_ev;
+    ncclComm_t comm;
+    /* problem (device) */
+    int64_t n, m, cap_n, cap_m;
+    double *A;              /* m x n row block, row-major                       */
+    double *b, *r, *Ap;     /* m                                                */
+    double *p_full;         /* n: gathered direction; own slice at rank*m       */
+    double *x_full;         /* n: x0 on entry; own slice updated; gathered at end */
+    double *partials_gemv;  /* one per gemv CTA                                 */
+    double *partials_vec;   /* one per vector-kernel CTA                        */
+    cgk_scalars *sc;        /* device scalars                                   */
+    cgk_scalars *h_sc;      /* pinned mirror                                    */
+    void *flush_buf;
+    cgk_gemv_plan plan;
+    cudaGraph_t graph;
+    cudaGraphExec_t graph_exec;
+    struct cgb_graph_key graph_key;
+    int64_t launches;
+    double h2d_seconds, d2h_seconds;
+};
+
+void cgb_set_error(const char *fmt, const char *a, const char *b, int line);
+
+#endif

@@ -1,0 +1,751 @@
+/* cg_kernels.cu -- hand-written sm_100a kernels for the dense FP64 CG iteration.
+ *
+ * Reference path replaced: the row-block matVec
+ * (parallel_cg.c:172-184), the dot products (parallel_cg.c:211-221) and the
+ * scale/add/sub vector passes (parallel_cg.c:200-245) as driven by conjugrad()
+ * (parallel_cg.c:283-323).  The hot kernel is a bandwidth-bound FP64 GEMV:
+ * single-vector, so no tensor cores; everything that matters is bytes in
+ * flight, coalescing and not re-reading A.
+ *
+ * Algorithmic bytes per launch: gemv 8*(m*n + n + m),
+ * xr_update 8*6m, p_update 8*3m.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "cg_kernels.h"
+#include "spd_gen.cuh"
+
+#define CGK_MAX_VEC_CTAS 592          /* 148 SMs x 4 */
+
+/* ------------------------------------------------------------------ loads */
+/* A is streamed exactly once per GEMV: read-only path, do not allocate in L1,
+ * evict-first in L2 (256-bit form) so the re-used direction vector stays hot. */
+template <int VW> struct Ld;
+template <> struct Ld<1> {
+    static __device__ __forceinline__ void stream(const double *p, double (&o)[1]) {
+        asm("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(o[0]) : "l"(p));
+    }
+    static __device__ __forceinline__ void keep(const double *p, double (&o)[1]) {
+        o[0] = __ldg(p);
+    }
+};
+template <> struct Ld<2> {
+    static __device__ __forceinline__ void stream(const double *p, double (&o)[2]) {
+        asm("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p));
+    }
+    static __device__ __forceinline__ void keep(const double *p, double (&o)[2]) {
+        asm("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p));
+    }
+};
+template <> struct Ld<4> {      /* 256-bit LDG: new on sm_100 */
+    static __device__ __forceinline__ void stream(const double *p, double (&o)[4]) {
+        unsigned long long a, b, c, d;
+        asm("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+        o[0] = __longlong_as_double(a); o[1] = __longlong_as_double(b);
+        o[2] = __longlong_as_double(c); o[3] = __longlong_as_double(d);
+    }
+    static __device__ __forceinline__ void keep(const double *p, double (&o)[4]) {
+        unsigned long long a, b, c, d;
+        asm("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+        o[0] = __longlong_as_double(a); o[1] = __longlong_as_double(b);
+        o[2] = __longlong_as_double(c); o[3] = __longlong_as_double(d);
+    }
+};
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+/* Fixed-order two-stage reduction of one partial per CTA: the last CTA to
+ * arrive (ticket) sums partials[0..grid) with a fixed thread->index mapping and
+ * a fixed tree, so the result is bitwise reproducible run to run (no FP64
+ * atomics).  `mine` is the CTA's partial, valid in thread 0. */
+template <int NT>
+__device__ __forceinline__ void cta_partials_finish(double mine, double *partials,
+                                                    double *out, unsigned int *ticket)
+{
+    __shared__ int s_last;
+    __shared__ double s_red[NT / 32];
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        partials[blockIdx.x] = mine;
+        __threadfence();
+        unsigned int t = atomicAdd(ticket, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double s = 0.0;
+    for (unsigned int i = tid; i < gridDim.x; i += NT) s += __ldcg(partials + i);
+    s = warp_sum(s);
+    if ((tid & 31) == 0) s_red[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < NT / 32; ++q) t += s_red[q];
+        *out = t;
+        *ticket = 0u;
+    }
+}
+
+/* ------------------------------------------------------------------ GEMV (LDG) */
+/* One CTA owns R adjacent rows (one contiguous R*n*8-byte panel of A) and walks
+ * all n columns; thread t of NT owns VW adjacent columns of every step, so a
+ * warp reads 32*VW*8 contiguous bytes per row per load and the CTA NT*VW*8.
+ * The direction-vector chunk is loaded once per step into registers and reused
+ * for the R rows (v traffic = 1/R of A traffic, served by L1/L2; v <= 1 MiB).
+ * U steps are issued back to back: R*U independent 128/256-bit loads in flight
+ * per thread.  Row sums: registers -> warp shuffle -> shared -> fixed-order add.
+ * Epilogue: y[row] and the CTA's partial of w.y (the fused p.Ap). */
+template <int R, int U, int NT, int VW>
+__global__ void __launch_bounds__(NT)
+gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
+                const double *__restrict__ w, double *__restrict__ y,
+                double *__restrict__ partials, double *__restrict__ dot_out,
+                cgk_scalars *__restrict__ sc, long long m, long long n)
+{
+    const int stop = *(volatile int *)&sc->stop_req;
+    if (stop) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
+        return;
+    }
+    constexpr int NW = NT / 32;
+    __shared__ double s_row[R][NW];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const long long row0 = (long long)blockIdx.x * R;
+
+    const double *a[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        long long row = row0 + r;
+        if (row > m - 1) row = m - 1;           /* clamp: reads stay in bounds, result dropped */
+        a[r] = A + row * n;
+    }
+    double acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.0;
+
+    constexpr long long STEP = (long long)NT * VW;
+    constexpr long long TILE = STEP * U;
+    const long long n_main = (n / TILE) * TILE;
+
+    for (long long c = (long long)tid * VW; c < n_main; c += TILE) {
+        double pv[U][VW];
+        double av[R][U][VW];
+#pragma unroll
+        for (int u = 0; u < U; ++u) Ld<VW>::keep(v + c + u * STEP, pv[u]);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int u = 0; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int e = 0; e < VW; ++e)
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u][e], pv[u][e], acc[r]);
+    }
+    /* column tail (n % VW == 0 is guaranteed by the plan) */
+    for (long long c = n_main + (long long)tid * VW; c < n; c += STEP) {
+        double pv[VW];
+        double av[R][VW];
+        Ld<VW>::keep(v + c, pv);
+#pragma unroll
+        for (int r = 0; r < R; ++r) Ld<VW>::stream(a[r] + c, av[r]);
+#pragma unroll
+        for (int e = 0; e < VW; ++e)
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = fma(av[r][e], pv[e], acc[r]);
+    }
+
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        acc[r] = warp_sum(acc[r]);
+        if (lane == 0) s_row[r][wid] = acc[r];
+    }
+    __syncthreads();
+    double contrib = 0.0;
+    if (tid < R) {
+        double s = 0.0;
+#pragma unroll
+        for (int q = 0; q < NW; ++q) s += s_row[tid][q];
+        const long long row = row0 + tid;
+        if (row < m) {
+            y[row] = s;
+            if (w != nullptr) contrib = s * w[row];
+        }
+    }
+    if (w == nullptr) return;
+    if (wid == 0) contrib = warp_sum(contrib);          /* lanes >= R hold 0 */
+    cta_partials_finish<NT>(contrib, partials, dot_out, &sc->ticket_gemv);
+}
+
+/* ------------------------------------------------------------------ GEMV (bulk-async ring) */
+/* Persistent, warp-specialised: one producer thread streams [R rows x C cols]
+ * tiles of A plus the matching C-column chunk of v into a STAGES-deep shared
+ * memory ring with cp.async.bulk (the TMA engine, SASS UBLKCP) completing on
+ * mbarriers; NT consumer threads drain the ring with conflict-free 128-bit
+ * LDS.  No registers are tied up by loads in flight: bytes in flight per SM =
+ * STAGES * (R+1) * C * 8, chosen from the latency-bandwidth product.  A CTA
+ * walks row panels blockIdx.x, blockIdx.x+grid, ... so the pipeline never
+ * drains between panels (the producer runs ahead into the next panel while the
+ * consumers reduce the previous one). */
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes,
+                                         uint64_t *bar, uint64_t policy)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+        ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+
+template <int R, int C, int STAGES, int NT>
+__global__ void __launch_bounds__(NT + 32)
+gemv_bulk_kernel(const double *__restrict__ A, const double *__restrict__ v,
+                 const double *__restrict__ w, double *__restrict__ y,
+                 double *__restrict__ partials, double *__restrict__ dot_out,
+                 cgk_scalars *__restrict__ sc, long long m, long long n)
+{
+    const int stop = *(volatile int *)&sc->stop_req;
+    if (stop) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
+        return;
+    }
+    constexpr int NW = NT / 32;
+    constexpr int STAGE_DOUBLES = (R + 1) * C;            /* R row segments + v chunk */
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *ring = reinterpret_cast<double *>(smem_raw);
+    uint64_t *full = reinterpret_cast<uint64_t *>(ring + (size_t)STAGES * STAGE_DOUBLES);
+    uint64_t *empty = full + STAGES;
+    __shared__ double s_row[R][NW];
+
+    const int tid = threadIdx.x;
+    const long long panels = (m + R - 1) / R;
+    const long long tiles = n / C;                        /* plan guarantees n % C == 0 */
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NW); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (tid >= NT) {
+        /* ---------------- producer warp: one elected lane issues the copies */
+        if (tid == NT) {
+            uint64_t pol_stream, pol_keep;
+            asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+            asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+            uint32_t it = 0;
+            for (long long pnl = blockIdx.x; pnl < panels; pnl += gridDim.x) {
+                const long long row0 = pnl * R;
+                for (long long t = 0; t < tiles; ++t, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1u;
+                    mbar_wait(&empty[s], ph ^ 1u);
+                    double *dst = ring + (size_t)s * STAGE_DOUBLES;
+                    mbar_expect_tx(&full[s], (uint32_t)(STAGE_DOUBLES * sizeof(double)));
+                    bulk_g2s(dst + (size_t)R * C, v + t * C, C * sizeof(double), &full[s], pol_keep);
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        long long row = row0 + r;
+                        if (row > m - 1) row = m - 1;
+                        bulk_g2s(dst + (size_t)r * C, A + row * n + t * C, C * sizeof(double),
+                                 &full[s], pol_stream);
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    /* ---------------- consumer warps */
+    const int lane = tid & 31, wid = tid >> 5;
+    constexpr int CH = C / (NT * 2);                      /* 16-byte chunks per thread per row */
+    static_assert(C % (NT * 2) == 0, "tile width must be a multiple of 2*NT");
+    uint32_t it = 0;
+    bool any_dot = false;
+    double cta_dot = 0.0;
+    for (long long pnl = blockIdx.x; pnl < panels; pnl += gridDim.x) {
+        const long long row0 = pnl * R;
+        double acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = 0.0;
+        for (long long t = 0; t < tiles; ++t, ++it) {
+            const int s = it % STAGES;
+            const uint32_t ph = (it / STAGES) & 1u;
+            mbar_wait(&full[s], ph);
+            const double2 *tile = reinterpret_cast<const double2 *>(ring + (size_t)s * STAGE_DOUBLES);
+            const double2 *vt = tile + (size_t)R * (C / 2);
+            double2 pv[CH];
+#pragma unroll
+            for (int k = 0; k < CH; ++k) pv[k] = vt[tid + k * NT];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+#pragma unroll
+                for (int k = 0; k < CH; ++k) {
+                    const double2 a2 = tile[(size_t)r * (C / 2) + tid + k * NT];
+                    acc[r] = fma(a2.x, pv[k].x, acc[r]);
+                    acc[r] = fma(a2.y, pv[k].y, acc[r]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+        }
+        /* panel reduction (consumers only: named barrier 1, NT threads) */
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            acc[r] = warp_sum(acc[r]);
+            if (lane == 0) s_row[r][wid] = acc[r];
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+        if (tid < R) {
+            double sum = 0.0;
+#pragma unroll
+            for (int q = 0; q < NW; ++q) sum += s_row[tid][q];
+            const long long row = row0 + tid;
+            double contrib = 0.0;
+            if (row < m) {
+                y[row] = sum;
+                if (w != nullptr) contrib = sum * w[row];
+            }
+            /* rows of one panel in fixed lane order, panels in visiting order */
+#pragma unroll
+            for (int o = R / 2; o > 0; o >>= 1) contrib += __shfl_xor_sync((1u << R) - 1u, contrib, o);
+            cta_dot += contrib;
+            any_dot = true;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+    }
+    (void)any_dot;
+    if (w == nullptr) return;
+    /* consumers-only finish: same fixed-order scheme as cta_partials_finish */
+    __shared__ int s_last;
+    __shared__ double s_red[NW];
+    if (tid == 0) {
+        partials[blockIdx.x] = cta_dot;
+        __threadfence();
+        unsigned int t = atomicAdd(&sc->ticket_gemv, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+    if (!s_last) return;
+    __threadfence();
+    double s = 0.0;
+    for (unsigned int i = tid; i < gridDim.x; i += NT) s += __ldcg(partials + i);
+    s = warp_sum(s);
+    if (lane == 0) s_red[wid] = s;
+    asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+    if (tid == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < NW; ++q) t += s_red[q];
+        *dot_out = t;
+        sc->ticket_gemv = 0u;
+    }
+}
+
+/* ------------------------------------------------------------------ vector phase */
+#define VEC_NT 256
+
+/* r = b - Ax0; p = b - Ax0 (the reference computes it twice, parallel_cg.c:284-285;
+ * same value); rr partial.  Not guarded by stop_req: runs before the loop. */
+__global__ void __launch_bounds__(VEC_NT)
+init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax,
+                     double *__restrict__ r, double *__restrict__ p_loc,
+                     double *__restrict__ partials, double *__restrict__ rr_out,
+                     cgk_scalars *__restrict__ sc, long long m)
+{
+    double s = 0.0;
+    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
+         i += (long long)gridDim.x * VEC_NT) {
+        const double ri = __dsub_rn(b[i], Ax[i]);
+        r[i] = ri;
+        p_loc[i] = ri;
+        s = fma(ri, ri, s);
+    }
+    __shared__ double s_w[VEC_NT / 32];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = s;
+    __syncthreads();
+    double mine = 0.0;
+    if (threadIdx.x == 0)
+        for (int q = 0; q < VEC_NT / 32; ++q) mine += s_w[q];
+    cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
+}
+
+/* alpha = rho / p.Ap (parallel_cg.c:298); x += alpha*p through a rounded
+ * product (scalarVec then vecAdd, :299,303); r -= alpha*Ap likewise (:304,308);
+ * partial r.r (:309).  __dmul_rn/__dadd_rn keep the reference's rounding
+ * points: no FMA contraction in the element-wise updates. */
+__global__ void __launch_bounds__(VEC_NT)
+xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
+                 const double *__restrict__ p_loc, const double *__restrict__ Ap,
+                 double *__restrict__ partials, double *__restrict__ rr_out,
+                 cgk_scalars *__restrict__ sc, int cur, long long m)
+{
+    if (*(volatile int *)&sc->stop_req) return;
+    const double alpha = sc->rr[cur] / sc->pAp;
+    double s = 0.0;
+    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
+         i += (long long)gridDim.x * VEC_NT) {
+        x[i] = __dadd_rn(x[i], __dmul_rn(p_loc[i], alpha));
+        const double ri = __dsub_rn(r[i], __dmul_rn(Ap[i], alpha));
+        r[i] = ri;
+        s = fma(ri, ri, s);
+    }
+    __shared__ double s_w[VEC_NT / 32];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = s;
+    __syncthreads();
+    double mine = 0.0;
+    if (threadIdx.x == 0)
+        for (int q = 0; q < VEC_NT / 32; ++q) mine += s_w[q];
+    cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
+}
+
+/* Stop rule and direction update (parallel_cg.c:314-323): if sqrt(beta) < eps the
+ * loop breaks BEFORE p is touched (x and r updated, p stale); otherwise
+ * p = r + (beta/rsold)*p via a rounded product, and rsold = beta (here: the
+ * rr[] ping-pong, parity `cur` baked into the launch).  Thread 0 of CTA 0 does
+ * the bookkeeping; every thread derives the same decision from beta. */
+__global__ void __launch_bounds__(VEC_NT)
+p_update_kernel(double *__restrict__ p_loc, const double *__restrict__ r,
+                cgk_scalars *__restrict__ sc, int cur, double eps, int ignore_stop,
+                long long max_iter, long long m)
+{
+    if (*(volatile int *)&sc->stopped) return;
+    const double rho = sc->rr[cur], beta = sc->rr[cur ^ 1];
+    const bool hit = sqrt(beta) < eps;
+    const bool brk = hit && !ignore_stop;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const long long k = sc->iters;
+        sc->iters = k + 1;
+        sc->final_beta = beta;
+        if (hit && sc->first_hit < 0) sc->first_hit = k;
+        if (brk) { sc->break_k = k; sc->stop_req = 1; }
+        else if (k + 1 >= max_iter) sc->stop_req = 2;
+    }
+    if (brk) return;
+    const double coef = beta / rho;
+    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
+         i += (long long)gridDim.x * VEC_NT)
+        p_loc[i] = __dadd_rn(r[i], __dmul_rn(p_loc[i], coef));
+}
+
+__global__ void reset_kernel(cgk_scalars *sc)
+{
+    sc->rr[0] = sc->rr[1] = 0.0;
+    sc->pAp = sc->pAp_local = sc->rr_local = 0.0;
+    sc->final_beta = 0.0; sc->rsold0 = 0.0;
+    sc->iters = 0; sc->first_hit = -1; sc->break_k = -1;
+    sc->stop_req = 0; sc->stopped = 0;
+    sc->ticket_gemv = 0u; sc->ticket_vec = 0u;
+}
+
+__global__ void after_init_kernel(cgk_scalars *sc)
+{
+    sc->rsold0 = sc->rr[0];
+    sc->final_beta = sc->rr[0];
+}
+
+/* ------------------------------------------------------------------ generator */
+__device__ __forceinline__ double gen_elem(uint64_t key, uint64_t n, uint64_t i, uint64_t j,
+                                           unsigned flags)
+{
+    double val = 0.5 * (cgb_gen_u(key, i * n + j) + cgb_gen_u(key, j * n + i));
+    if (i == j) val = __dadd_rn(val, (double)n);
+    if (flags & CGB_GEN_ROUND4) val = __ddiv_rn(rint(__dmul_rn(val, 1.0e4)), 1.0e4);
+    return val;
+}
+
+__global__ void __launch_bounds__(256)
+generate_A_kernel(double *__restrict__ A, long long n, long long row0, long long m,
+                  uint64_t key, unsigned flags)
+{
+    const long long total = m * n;
+    for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total;
+         e += (long long)gridDim.x * 256) {
+        const long long i = e / n, j = e - i * n;
+        A[e] = gen_elem(key, (uint64_t)n, (uint64_t)(row0 + i), (uint64_t)j, flags);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+generate_b_kernel(double *__restrict__ b, long long n, long long row0, long long m,
+                  uint64_t key, unsigned flags)
+{
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < m;
+         i += (long long)gridDim.x * 256) {
+        double val = cgb_gen_u(key, (uint64_t)n * (uint64_t)n + (uint64_t)(row0 + i));
+        if (flags & CGB_GEN_ROUND4) val = __ddiv_rn(rint(__dmul_rn(val, 1.0e4)), 1.0e4);
+        b[i] = val;
+    }
+}
+
+__global__ void __launch_bounds__(256) l2_flush_kernel(double2 *buf, long long n2)
+{
+    for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n2;
+         e += (long long)gridDim.x * 256) {
+        double2 t = buf[e];
+        t.x += 1.0; t.y -= 1.0;
+        buf[e] = t;
+    }
+}
+
+/* ------------------------------------------------------------------ launchers */
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+extern "C" int64_t cgk_gemv_max_ctas(int64_t m) { return m < 1 ? 1 : m; }
+extern "C" int64_t cgk_vec_max_ctas(int64_t m) { (void)m; return CGK_MAX_VEC_CTAS; }
+
+static int vec_grid(int64_t m)
+{
+    int64_t g = ceil_div(m, VEC_NT);
+    if (g < 1) g = 1;
+    if (g > CGK_MAX_VEC_CTAS) g = CGK_MAX_VEC_CTAS;
+    return (int)g;
+}
+
+typedef void (*gemv_fn)(const double *, const double *, const double *, double *, double *,
+                        double *, cgk_scalars *, long long, long long);
+
+template <int R, int U, int NT>
+static gemv_fn pick_ldg_vec(int vec)
+{
+    if (R * U * vec > 64) return nullptr;                    /* would spill: not instantiated */
+    switch (vec) {
+    case 4: if constexpr (R * U * 4 <= 64) return gemv_ldg_kernel<R, U, NT, 4>; else return nullptr;
+    case 2: if constexpr (R * U * 2 <= 64) return gemv_ldg_kernel<R, U, NT, 2>; else return nullptr;
+    default: return nullptr;
+    }
+}
+template <int R, int U>
+static gemv_fn pick_ldg_nt(int nt, int vec)
+{
+    switch (nt) {
+    case 128: return pick_ldg_vec<R, U, 128>(vec);
+    case 256: return pick_ldg_vec<R, U, 256>(vec);
+    case 512: return pick_ldg_vec<R, U, 512>(vec);
+    default: return nullptr;
+    }
+}
+template <int R>
+static gemv_fn pick_ldg_u(int u, int nt, int vec)
+{
+    switch (u) {
+    case 1: return pick_ldg_nt<R, 1>(nt, vec);
+    case 2: return pick_ldg_nt<R, 2>(nt, vec);
+    case 4: return pick_ldg_nt<R, 4>(nt, vec);
+    default: return nullptr;
+    }
+}
+static gemv_fn pick_ldg(int r, int u, int nt, int vec)
+{
+    if (vec == 1) return gemv_ldg_kernel<4, 1, 128, 1>;      /* odd n / unaligned: scalar loads */
+    switch (r) {
+    case 1: return pick_ldg_u<1>(u, nt, vec);
+    case 2: return pick_ldg_u<2>(u, nt, vec);
+    case 4: return pick_ldg_u<4>(u, nt, vec);
+    case 8: return pick_ldg_u<8>(u, nt, vec);
+    default: return nullptr;
+    }
+}
+
+/* bulk variants: (R, C, STAGES, NT) */
+struct bulk_cfg { int r, c, stages, nt; gemv_fn fn; };
+static const bulk_cfg k_bulk[] = {
+    {4, 512, 4, 128, gemv_bulk_kernel<4, 512, 4, 128>},
+    {4, 512, 8, 128, gemv_bulk_kernel<4, 512, 8, 128>},
+    {8, 512, 4, 128, gemv_bulk_kernel<8, 512, 4, 128>},
+    {8, 512, 5, 128, gemv_bulk_kernel<8, 512, 5, 128>},
+    {8, 256, 8, 128, gemv_bulk_kernel<8, 256, 8, 128>},
+    {4, 1024, 4, 256, gemv_bulk_kernel<4, 1024, 4, 256>},
+    {8, 1024, 2, 256, gemv_bulk_kernel<8, 1024, 2, 256>},
+    {8, 1024, 3, 256, gemv_bulk_kernel<8, 1024, 3, 256>},
+    {16, 256, 5, 128, gemv_bulk_kernel<16, 256, 5, 128>},
+    {16, 512, 3, 128, gemv_bulk_kernel<16, 512, 3, 128>},
+};
+static const bulk_cfg *find_bulk(int r, int c, int stages, int nt)
+{
+    for (const bulk_cfg &b : k_bulk)
+        if (b.r == r && b.c == c && b.stages == stages && b.nt == nt) return &b;
+    return nullptr;
+}
+static int bulk_smem(const bulk_cfg *b)
+{
+    return b->stages * (b->r + 1) * b->c * 8 + 2 * b->stages * 8;
+}
+
+extern "C" int cgk_gemv_make_plan(cgk_gemv_plan *plan, int64_t m, int64_t n, const void *A,
+                                  const void *v, int sm_count)
+{
+    if (!plan || m < 1 || n < 1) return (int)cudaErrorInvalidValue;
+    if (sm_count <= 0) sm_count = 148;
+    const uintptr_t pa = (uintptr_t)A, pv = (uintptr_t)v;
+    int maxvec = 1;
+    if (n % 4 == 0 && pa % 32 == 0 && pv % 32 == 0) maxvec = 4;
+    else if (n % 2 == 0 && pa % 16 == 0 && pv % 16 == 0) maxvec = 2;
+    int variant = plan->variant, rows = plan->rows_per_cta, unroll = plan->unroll;
+    int threads = plan->threads, vec = plan->vec;
+    if (vec == 0 || vec > maxvec) vec = maxvec;
+    if (vec == 3) vec = 2;
+    if (variant == CGK_GEMV_AUTO) variant = CGK_GEMV_LDG;
+
+    if (variant == CGK_GEMV_BULK) {
+        const int r = rows ? rows : 8, st = plan->stages ? plan->stages : 4;
+        const int nt = threads ? threads : 128, c = plan->tile_cols ? plan->tile_cols : 512;
+        const bulk_cfg *b = find_bulk(r, c, st, nt);
+        if (b && n % c == 0 && pa % 16 == 0 && pv % 16 == 0) {
+            plan->variant = CGK_GEMV_BULK;
+            plan->rows_per_cta = r; plan->unroll = 0; plan->threads = nt; plan->vec = 2;
+            plan->stages = st; plan->tile_cols = c; plan->smem_bytes = bulk_smem(b);
+            int occ = 1;
+            cudaFuncSetAttribute(b->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan->smem_bytes);
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b->fn, nt + 32, plan->smem_bytes) != cudaSuccess || occ < 1) {
+                (void)cudaGetLastError();
+                occ = 1;
+            }
+            const int64_t panels = ceil_div(m, r);
+            const int64_t g = (int64_t)sm_count * occ;
+            plan->grid = (int)(panels < g ? panels : g);
+            return 0;
+        }
+        rows = unroll = threads = 0;       /* shape not tileable: streaming-load kernel */
+    }
+
+    plan->variant = CGK_GEMV_LDG;
+    plan->stages = 0; plan->tile_cols = 0; plan->smem_bytes = 0;
+    if (vec == 1) {
+        plan->rows_per_cta = 4; plan->unroll = 1; plan->threads = 128; plan->vec = 1;
+    } else {
+        if (rows == 0) rows = 4;
+        if (threads == 0) threads = (n >= 8192) ? 256 : 128;
+        if (unroll == 0) unroll = 2;
+        while (rows > 1 && rows > m) rows >>= 1;
+        plan->rows_per_cta = rows; plan->unroll = unroll; plan->threads = threads; plan->vec = vec;
+    }
+    if (!pick_ldg(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec))
+        return (int)cudaErrorInvalidValue;
+    plan->grid = (int)ceil_div(m, plan->rows_per_cta);
+    return 0;
+}
+
+extern "C" int cgk_gemv(const cgk_gemv_plan *plan, const double *A, const double *v,
+                        const double *w, double *y, double *partials, double *dot_out,
+                        cgk_scalars *sc, int64_t m, int64_t n, void *stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    if (plan->variant == CGK_GEMV_BULK) {
+        const bulk_cfg *b = find_bulk(plan->rows_per_cta, plan->tile_cols, plan->stages, plan->threads);
+        if (!b) return (int)cudaErrorInvalidValue;
+        b->fn<<<plan->grid, plan->threads + 32, plan->smem_bytes, st>>>(A, v, w, y, partials, dot_out,
+                                                                        sc, (long long)m, (long long)n);
+        return (int)cudaGetLastError();
+    }
+    gemv_fn fn = pick_ldg(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec);
+    if (!fn) return (int)cudaErrorInvalidValue;
+    fn<<<plan->grid, plan->threads, 0, st>>>(A, v, w, y, partials, dot_out, sc, (long long)m, (long long)n);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_init_residual(const double *b, const double *Ax, double *r, double *p_loc,
+                                 double *partials, double *rr_out, cgk_scalars *sc, int64_t m,
+                                 void *stream)
+{
+    init_residual_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
+                                                                          rr_out, sc, (long long)m);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
+                             double *partials, double *rr_out, cgk_scalars *sc, int cur,
+                             int64_t m, void *stream)
+{
+    xr_update_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
+                                                                      sc, cur, (long long)m);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
+                            int ignore_stop, int64_t max_iter, int64_t m, void *stream)
+{
+    p_update_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
+                                                                     (long long)max_iter, (long long)m);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_reset(cgk_scalars *sc, void *stream)
+{
+    reset_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_after_init(cgk_scalars *sc, void *stream)
+{
+    after_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                              unsigned flags, void *stream)
+{
+    int64_t g = ceil_div(m * n, 256 * 8);
+    if (g < 1) g = 1;
+    if (g > 148 * 32) g = 148 * 32;
+    generate_A_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)row0,
+                                                               (long long)m, cgb_gen_key(seed), flags);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_generate_b(double *b, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                              unsigned flags, void *stream)
+{
+    int64_t g = ceil_div(m, 256);
+    if (g < 1) g = 1;
+    if (g > 592) g = 592;
+    generate_b_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(b, (long long)n, (long long)row0,
+                                                               (long long)m, cgb_gen_key(seed), flags);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_l2_flush(void *buf, int64_t bytes, void *stream)
+{
+    l2_flush_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>((double2 *)buf, (long long)(bytes / 16));
+    return (int)cudaGetLastError();
+}
+
+extern "C" const char *cgk_error_string(int err) { return cudaGetErrorString((cudaError_t)err); }

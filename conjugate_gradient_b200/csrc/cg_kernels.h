@@ -1,0 +1,105 @@
+/* cg_kernels.h -- the thin C layer between the C host solver (cg_solver.c) and
+ * the hand-written sm_100a kernels (cg_kernels.cu).  Plain C: device pointers,
+ * sizes and a stream; every launcher returns a cudaError_t as int.
+ *
+ * Reference functions each kernel replaces:
+ *   cgk_gemv          matVec   parallel_cg.c:172-184  (+ vecVec(p,Ap) :293 fused)
+ *   cgk_init_residual residual parallel_cg.c:188-196 twice (:284-285) + vecVec :286
+ *   cgk_xr_update     scalarVec+vecAdd (:299,303), scalarVec+vecSub (:304,308), vecVec :309
+ *   cgk_p_update      stop test :314-317, scalarVec+vecAdd :318,322, rsold=beta :323
+ *   cgk_generate      generateSPDmatrix.m:4-17
+ */
+#ifndef CG_KERNELS_H
+#define CG_KERNELS_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Device-resident solver scalars: nothing in an iteration returns to the host. */
+typedef struct cgk_scalars {
+    double rr[2];          /* rr[cur] = rho of the running iteration; rr[cur^1] receives beta */
+    double pAp;            /* all-reduced p.Ap                                              */
+    double pAp_local;      /* this rank's partial (all-reduce send buffer)                  */
+    double rr_local;       /* this rank's r.r partial (all-reduce send buffer)              */
+    double final_beta;     /* r.r after the last applied x/r update                         */
+    double rsold0;         /* initial r.r                                                   */
+    long long iters;       /* x/r updates applied                                           */
+    long long first_hit;   /* first loop index k with sqrt(beta) < eps, -1 if none          */
+    long long break_k;     /* loop index at which the stop rule fired, -1                   */
+    int stop_req;          /* written by ONE thread of cgk_p_update: 1 stop rule fired,      */
+                           /* 2 max_iter reached; read by gemv / xr_update of later iterations */
+    int stopped;           /* stop_req latched by the next gemv launch; read by p_update, so  */
+                           /* no kernel ever reads a flag that is written during its own run  */
+    unsigned int ticket_gemv;
+    unsigned int ticket_vec;
+} cgk_scalars;
+
+typedef struct cgk_gemv_plan {
+    int variant;           /* CGK_GEMV_*                                  */
+    int rows_per_cta;      /* R                                           */
+    int unroll;            /* U column chunks in flight per thread        */
+    int threads;           /* NT                                          */
+    int vec;               /* doubles per load: 1, 2 (128-bit), 4 (256-bit) */
+    int stages;            /* bulk-copy ring depth (variant BULK)         */
+    int tile_cols;         /* C: columns per ring stage (variant BULK)    */
+    int grid;              /* CTAs (resolved)                             */
+    int smem_bytes;        /* dynamic shared memory (resolved)            */
+} cgk_gemv_plan;
+
+enum { CGK_GEMV_AUTO = 0, CGK_GEMV_LDG = 1, CGK_GEMV_BULK = 2 };
+
+/* Upper bound on gemv CTAs for any plan (sizes the partials workspace). */
+int64_t cgk_gemv_max_ctas(int64_t m);
+int64_t cgk_vec_max_ctas(int64_t m);
+
+/* Resolves a launch plan for an m x n row block.  On entry the fields of
+ * *plan are the request (0 = choose for me); on return they are the resolved
+ * configuration.  Shapes the requested variant cannot tile (odd n, n not a
+ * multiple of the stage width, unaligned bases) fall back to the streaming-load
+ * kernel with the widest legal vector width -- always a CUDA kernel. */
+int cgk_gemv_make_plan(cgk_gemv_plan *plan, int64_t m, int64_t n, const void *A,
+                       const void *v, int sm_count);
+
+/* y = A v (m x n row block, row-major).  If w != NULL the CTA partials of
+ * sum_i w[i]*y[i] go to `partials` and the last CTA to finish sums them in a
+ * fixed order into *dot_out.  Returns immediately on device once sc->stop_req is set. */
+int cgk_gemv(const cgk_gemv_plan *plan, const double *A, const double *v, const double *w,
+             double *y, double *partials, double *dot_out, cgk_scalars *sc,
+             int64_t m, int64_t n, void *stream);
+
+/* r = b - Ax0, p_loc = b - Ax0, rr partials -> *rr_out (fixed-order sum). */
+int cgk_init_residual(const double *b, const double *Ax, double *r, double *p_loc,
+                      double *partials, double *rr_out, cgk_scalars *sc, int64_t m,
+                      void *stream);
+
+/* alpha = rr[cur]/pAp; x += alpha p; r -= alpha Ap; r.r partials -> *rr_out. */
+int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
+                  double *partials, double *rr_out, cgk_scalars *sc, int cur,
+                  int64_t m, void *stream);
+
+/* beta = rr[cur^1]: bookkeeping + stop rule on thread 0; p = r + (beta/rho) p. */
+int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
+                 int ignore_stop, int64_t max_iter, int64_t m, void *stream);
+
+/* Resets the scalars for a new solve (first kernel of the init phase). */
+int cgk_reset(cgk_scalars *sc, void *stream);
+/* rr[0] bookkeeping after the initial all-reduce. */
+int cgk_after_init(cgk_scalars *sc, void *stream);
+
+/* Rows [row0,row0+m) of the seeded SPD matrix into A (m x n); b rows likewise. */
+int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                   unsigned flags, void *stream);
+int cgk_generate_b(double *b, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                   unsigned flags, void *stream);
+
+/* Writes `bytes` of zeros-then-ones traffic over buf: evicts L2 between timed launches. */
+int cgk_l2_flush(void *buf, int64_t bytes, void *stream);
+
+const char *cgk_error_string(int err);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,198 @@
+/* cg_main.c -- the reference's command line, re-hosted on the B200 solver.
+ *
+ *   cg_b200 matrixA.txt vectorb.txt initialguess.txt [options]
+ *
+ * Same three positional files in the same order as the reference
+ * (serialConjugate.c:48-52,65-67; parallel_cg.c:105-107) and the same stdout
+ * lines.  The problem size, a compile-time macro in the
+ * reference (#define ROWS/COLS, serialConjugate.c:29-30), is read at run time
+ * from dimensions.txt (rows(A) cols(A) rows(b) cols(b), one per line).
+ *
+ * Options (none of them disturbs the positional form):
+ *   --dims FILE       dimensions file (default: ./dimensions.txt, else next to A,
+ *                     else inferred from the number of values in vectorb)
+ *   --gpus G          row-shard A over G GPUs (the reference's mpiexec -np G)
+ *   --eps E           stop tolerance (default 1e-6 = EPSILON)
+ *   --max-iter K      loop bound (default n = ROWS)
+ *   --print-x         print the solution in printer()'s format (the call is
+ *                     commented out in the reference: serialConjugate.c:252)
+ *   --write-x FILE    write x one value per line ("%.17g"): usable as initialguess
+ *   --gen N           no input files: seeded on-device SPD system of order N
+ *   --seed S          generator seed (default 20170209)   --round4  "%.4f" rounding
+ *   --bench-iters K   fixed-iteration timing mode (stop test recorded, not acted on)
+ *   --gemv V          1 = streaming loads, 2 = bulk-async ring
+ *   --stats           extra lines: iterations, residual, GEMV GB/s
+ */
+#define _GNU_SOURCE
+#include <math.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+#include <libgen.h>
+
+#include "../../include/cgb200.h"
+#include "cg_io.h"
+
+typedef struct {
+    const char *fileA, *fileB, *fileX, *dims, *write_x;
+    int gpus, print_x, stats, round4, gemv;
+    int64_t gen_n, max_iter, bench_iters;
+    uint64_t seed;
+    double eps;
+} cli_t;
+
+static int parse_cli(int argc, char **argv, cli_t *c)
+{
+    const char *pos[3] = {0, 0, 0};
+    int npos = 0;
+    memset(c, 0, sizeof *c);
+    c->gpus = 1; c->seed = 20170209ULL; c->eps = CGB_EPSILON;
+    for (int i = 1; i < argc; ++i) {
+        const char *a = argv[i];
+        const char *v = (i + 1 < argc) ? argv[i + 1] : NULL;
+        if (strncmp(a, "--", 2) != 0) { if (npos < 3) pos[npos] = a; ++npos; continue; }
+        if (!strcmp(a, "--print-x")) c->print_x = 1;
+        else if (!strcmp(a, "--stats")) c->stats = 1;
+        else if (!strcmp(a, "--round4")) c->round4 = 1;
+        else if (!v) { fprintf(stderr, "option %s needs a value\n", a); return -1; }
+        else if (!strcmp(a, "--dims")) { c->dims = v; ++i; }
+        else if (!strcmp(a, "--write-x")) { c->write_x = v; ++i; }
+        else if (!strcmp(a, "--gpus")) { c->gpus = atoi(v); ++i; }
+        else if (!strcmp(a, "--eps")) { c->eps = atof(v); ++i; }
+        else if (!strcmp(a, "--max-iter")) { c->max_iter = atoll(v); ++i; }
+        else if (!strcmp(a, "--gen")) { c->gen_n = atoll(v); ++i; }
+        else if (!strcmp(a, "--seed")) { c->seed = strtoull(v, NULL, 10); ++i; }
+        else if (!strcmp(a, "--bench-iters")) { c->bench_iters = atoll(v); ++i; }
+        else if (!strcmp(a, "--gemv")) { c->gemv = atoi(v); ++i; }
+        else { fprintf(stderr, "unknown option %s\n", a); return -1; }
+    }
+    c->fileA = pos[0]; c->fileB = pos[1]; c->fileX = pos[2];
+    if (c->gen_n > 0) return npos == 0 ? 0 : -1;
+    return npos == 3 ? 0 : -2;
+}
+
+/* dimensions.txt lookup: --dims, ./dimensions.txt, <dir of A>/dimensions.txt */
+static int find_dimensions(const cli_t *c, int64_t dims[4], int *inferred)
+{
+    *inferred = 0;
+    if (c->dims) return cgb_read_dimensions(c->dims, dims);
+    if (cgb_read_dimensions("dimensions.txt", dims) == CGB_OK) return CGB_OK;
+    char tmp[4096], path[4200];
+    snprintf(tmp, sizeof tmp, "%s", c->fileA);
+    snprintf(path, sizeof path, "%s/dimensions.txt", dirname(tmp));
+    if (cgb_read_dimensions(path, dims) == CGB_OK) return CGB_OK;
+    int64_t nb = cgb_count_values(c->fileB);
+    if (nb < 1) return CGB_ERR_IO;
+    dims[0] = dims[1] = dims[2] = nb; dims[3] = 1;
+    *inferred = 1;
+    return CGB_OK;
+}
+
+int main(int argc, char **argv)
+{
+    const clock_t c0 = clock();                      /* parallel_cg.c:75 */
+    cli_t cli;
+    int pc = parse_cli(argc, argv, &cli);
+    if (pc == -2) {
+        /* serialConjugate.c:48-52 (message kept, exit status made non-zero) */
+        printf("%s requires four (4) files \n", "cg_b200");
+        return 2;
+    }
+    if (pc != 0) return 2;
+
+    cgb_options opt;
+    cgb_default_options(&opt);
+    opt.eps = cli.eps;
+    opt.max_iter = cli.max_iter;
+    opt.gemv_variant = cli.gemv;
+    if (cli.bench_iters > 0) { opt.ignore_stop = 1; opt.max_iter = cli.bench_iters; }
+
+    cgb_stats st;
+    memset(&st, 0, sizeof st);
+    double *A = NULL, *b = NULL, *x = NULL;
+    int64_t n = 0;
+    int rc;
+
+    if (cli.gen_n > 0) {
+        n = cli.gen_n;
+        if (n % cli.gpus != 0) {                     /* parallel_cg.c:86-90 */
+            printf("%lld is not divisible by %d\n", (long long)n, cli.gpus);
+            return 1;
+        }
+        printf("Computing cg of matrix size : %lld\n", (long long)n * (long long)n);
+        x = malloc((size_t)n * sizeof(double));
+        if (!x) { printf("can't allocate memory for vector\n"); return 1; }
+        rc = cgb_solve_generated(n, cli.seed, cli.round4 ? CGB_GEN_ROUND4 : 0u, cli.gpus, &opt, x, &st);
+    } else {
+        int64_t dims[4];
+        int inferred = 0;
+        if (find_dimensions(&cli, dims, &inferred) != CGB_OK) {
+            printf("Could not open file\n");          /* serialConjugate.c:103 */
+            fprintf(stderr, "cg_b200: no usable dimensions.txt and cannot size %s\n", cli.fileB);
+            return 1;
+        }
+        if (inferred) fprintf(stderr, "cg_b200: dimensions.txt not found; n = %lld from %s\n", (long long)dims[0], cli.fileB);
+        if (dims[0] != dims[1]) {                     /* serialConjugate.c:53-57 */
+            printf("%lld and %lld must be same size\n", (long long)dims[0], (long long)dims[1]);
+            return 1;
+        }
+        n = dims[0];
+        if (dims[2] != n || dims[3] != 1) {
+            fprintf(stderr, "cg_b200: dimensions of b (%lld x %lld) do not match A\n", (long long)dims[2], (long long)dims[3]);
+            return 1;
+        }
+        if (n % cli.gpus != 0) {
+            printf("%lld is not divisible by %d\n", (long long)n, cli.gpus);
+            return 1;
+        }
+        printf("Computing cg of matrix size : %lld\n", (long long)n * (long long)n);   /* :58, 64-bit */
+        A = malloc((size_t)n * (size_t)n * sizeof(double));
+        b = malloc((size_t)n * sizeof(double));
+        x = malloc((size_t)n * sizeof(double));
+        if (!A || !b || !x) { printf("can't allocate memory for vector\n"); return 1; }  /* :80 */
+        const char *files[3] = {cli.fileA, cli.fileB, cli.fileX};
+        double *dst[3] = {A, b, x};
+        int64_t cnt[3] = {n * n, n, n};
+        for (int i = 0; i < 3; ++i) {
+            int64_t got = 0;
+            if (cgb_read_values(files[i], dst[i], cnt[i], &got) != CGB_OK) {
+                if (got == 0) printf("Could not open file\n");
+                fprintf(stderr, "cg_b200: %s: expected %lld values, found %lld\n", files[i], (long long)cnt[i], (long long)got);
+                return 1;
+            }
+        }
+        rc = cgb_conjugrad_host_opt(A, b, x, n, cli.gpus, &opt, &st);
+    }
+    if (rc != CGB_OK) {
+        fprintf(stderr, "cg_b200: %s\n", cgb_last_error());
+        return 1;
+    }
+    if (cli.print_x) cgb_print_vector(stdout, x, n, 1);
+    if (cli.gpus == 1) {
+        printf("average clock execution time in seconds: %f\n", st.solve_seconds);       /* serialConjugate.c:249-251 */
+    } else {
+        printf("cg method execution time in seconds: %f\n", st.solve_seconds);           /* parallel_cg.c:334-335 */
+        printf("collective data distribution time in seconds: %f\n", st.h2d_seconds);    /* :123-124 */
+        printf("clock execution time in seconds: %f\n", (double)(clock() - c0) / CLOCKS_PER_SEC); /* :125-126 */
+    }
+    if (cli.stats || cli.bench_iters > 0) {
+        printf("iterations: %lld\n", (long long)st.iterations);
+        printf("loop index at break: %lld\n", (long long)st.break_k);
+        printf("final residual sqrt(r.r): %.6e\n", st.final_residual);
+        if (st.iterations > 0 && st.loop_ms > 0.0) {
+            double it_s = 1.0e3 * (double)st.iterations / st.loop_ms;
+            printf("iterations per second: %.3f\n", it_s);
+            printf("iteration-level GEMV GB/s per GPU (8*(m*n+n+m) bytes / iteration time): %.1f\n",
+                   st.gemv_bytes * it_s * 1.0e-9);
+        }
+    }
+    if (cli.write_x && cgb_write_values(cli.write_x, x, n, -1) != CGB_OK) {
+        fprintf(stderr, "cg_b200: cannot write %s\n", cli.write_x);
+        return 1;
+    }
+    free(A); free(b); free(x);
+    cgb_shutdown();
+    return 0;
+}

@@ -1,0 +1,733 @@
+/* cg_solver.c -- host side of libcgb200.so, in C like the reference.
+ *
+ * Replaces conjugrad() of the reference (serialConjugate.c:180-259,
+ * parallel_cg.c:248-345): the per-rank solver state lives on one B200, the
+ * iteration is a short chain of hand-written kernels (cg_kernels.cu) plus, for
+ * ranks > 1, the three collectives of the reference re-expressed in NCCL over
+ * NVLink:  MPI_Allgather(p) parallel_cg.c:290-291 -> ncclAllGather,
+ *          MPI_Allreduce(p.Ap) :294 and MPI_Allreduce(r.r) :287,313 -> ncclAllReduce.
+ * All solver scalars stay in device memory; the host only replays a captured
+ * CUDA graph of `chunk` iterations and polls one flag between replays.
+ */
+#define _GNU_SOURCE
+#include <cuda_runtime_api.h>
+#include <nccl.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include "../../include/cgb200.h"
+#include "cg_kernels.h"
+#include "cg_internal.h"
+
+static __thread char tl_err[512];
+
+const char *cgb_last_error(void) { return tl_err; }
+int cgb_version(void) { return CGB_VERSION; }
+
+void cgb_set_error(const char *fmt, const char *a, const char *b, int line)
+{
+    snprintf(tl_err, sizeof tl_err, fmt, a, b, line);
+}
+
+#define CU(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            cgb_set_error("CUDA error: %s in `%s` (cg_solver.c:%d)", cudaGetErrorString(e_), #call, __LINE__); \
+            return CGB_ERR_CUDA;                                                         \
+        }                                                                                \
+    } while (0)
+#define KL(call)                                                                         \
+    do {                                                                                 \
+        int e_ = (call);                                                                 \
+        if (e_ != 0) {                                                                   \
+            cgb_set_error("kernel launch error: %s in `%s` (cg_solver.c:%d)", cgk_error_string(e_), #call, __LINE__); \
+            return CGB_ERR_CUDA;                                                         \
+        }                                                                                \
+    } while (0)
+#define NC(call)                                                                         \
+    do {                                                                                 \
+        ncclResult_t e_ = (call);                                                        \
+        if (e_ != ncclSuccess) {                                                         \
+            cgb_set_error("NCCL error: %s in `%s` (cg_solver.c:%d)", ncclGetErrorString(e_), #call, __LINE__); \
+            return CGB_ERR_NCCL;                                                         \
+        }                                                                                \
+    } while (0)
+#define FAIL(code, msg)                                                                  \
+    do {                                                                                 \
+        cgb_set_error("%s%s (cg_solver.c:%d)", msg, "", __LINE__);                       \
+        return (code);                                                                   \
+    } while (0)
+
+static double now_s(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+int cgb_device_count(void)
+{
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) { (void)cudaGetLastError(); return -1; }
+    return c;
+}
+
+void cgb_default_options(cgb_options *o)
+{
+    memset(o, 0, sizeof *o);
+    o->eps = CGB_EPSILON;
+    o->use_graph = 1;
+}
+
+/* ------------------------------------------------------------------ contexts */
+static int ctx_init_common(cgb_ctx *c, int device)
+{
+    struct cudaDeviceProp prop;
+    CU(cudaSetDevice(device));
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        snprintf(tl_err, sizeof tl_err,
+                 "device %d (%s, sm_%d%d) is not a Blackwell sm_100 GPU: libcgb200 has no other code path",
+                 device, prop.name, prop.major, prop.minor);
+        return CGB_ERR_CUDA;
+    }
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    snprintf(c->name, sizeof c->name, "%.63s", prop.name);
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev[0]));
+    CU(cudaEventCreate(&c->ev[1]));
+    CU(cudaEventCreate(&c->ev[2]));
+    CU(cudaMalloc((void **)&c->sc, sizeof(cgk_scalars)));
+    CU(cudaMemset(c->sc, 0, sizeof(cgk_scalars)));
+    CU(cudaHostAlloc((void **)&c->h_sc, sizeof(cgk_scalars), cudaHostAllocDefault));
+    CU(cudaMalloc((void **)&c->partials_vec, (size_t)cgk_vec_max_ctas(1) * sizeof(double)));
+    return CGB_OK;
+}
+
+int cgb_create(cgb_ctx **out, int device)
+{
+    if (!out) FAIL(CGB_ERR_ARG, "cgb_create: null output pointer");
+    cgb_ctx *c = calloc(1, sizeof *c);
+    if (!c) FAIL(CGB_ERR_NOMEM, "cgb_create: out of host memory");
+    c->rank = 0; c->ranks = 1;
+    int rc = ctx_init_common(c, device);
+    if (rc != CGB_OK) { cgb_destroy(c); return rc; }
+    *out = c;
+    return CGB_OK;
+}
+
+int cgb_unique_id(void *id128)
+{
+    if (!id128) FAIL(CGB_ERR_ARG, "cgb_unique_id: null buffer");
+    ncclUniqueId id;
+    NC(ncclGetUniqueId(&id));
+    memcpy(id128, &id, sizeof id);
+    return CGB_OK;
+}
+
+int cgb_create_rank(cgb_ctx **out, int device, int rank, int ranks, const void *id128)
+{
+    if (!out || ranks < 1 || rank < 0 || rank >= ranks) FAIL(CGB_ERR_ARG, "cgb_create_rank: bad rank/ranks");
+    if (ranks > 1 && !id128) FAIL(CGB_ERR_ARG, "cgb_create_rank: ranks > 1 needs a unique id");
+    cgb_ctx *c = calloc(1, sizeof *c);
+    if (!c) FAIL(CGB_ERR_NOMEM, "cgb_create_rank: out of host memory");
+    c->rank = rank; c->ranks = ranks;
+    int rc = ctx_init_common(c, device);
+    if (rc != CGB_OK) { cgb_destroy(c); return rc; }
+    if (ranks > 1) {
+        ncclUniqueId id;
+        memcpy(&id, id128, sizeof id);
+        ncclResult_t e = ncclCommInitRank(&c->comm, ranks, id, rank);
+        if (e != ncclSuccess) {
+            snprintf(tl_err, sizeof tl_err, "NCCL error: %s in ncclCommInitRank", ncclGetErrorString(e));
+            cgb_destroy(c);
+            return CGB_ERR_NCCL;
+        }
+        c->has_comm = 1;
+    }
+    *out = c;
+    return CGB_OK;
+}
+
+static void drop_graph(cgb_ctx *c)
+{
+    if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = NULL; }
+    if (c->graph) { cudaGraphDestroy(c->graph); c->graph = NULL; }
+    memset(&c->graph_key, 0, sizeof c->graph_key);
+}
+
+static void free_problem(cgb_ctx *c)
+{
+    drop_graph(c);
+    cudaFree(c->A); cudaFree(c->b); cudaFree(c->r); cudaFree(c->Ap);
+    cudaFree(c->p_full); cudaFree(c->x_full); cudaFree(c->partials_gemv);
+    c->A = c->b = c->r = c->Ap = c->p_full = c->x_full = c->partials_gemv = NULL;
+    c->n = c->m = 0; c->cap_n = c->cap_m = 0; c->loaded = 0;
+}
+
+int cgb_destroy(cgb_ctx *c)
+{
+    if (!c) return CGB_OK;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_problem(c);
+    if (c->has_comm) ncclCommDestroy(c->comm);
+    for (int i = 0; i < 3; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (int i = 0; i < c->n_gemv_ev; ++i) cudaEventDestroy(c->gemv_ev[i]);
+    free(c->gemv_ev);
+    cudaFree(c->sc); cudaFree(c->partials_vec); cudaFree(c->flush_buf);
+    if (c->h_sc) cudaFreeHost(c->h_sc);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    (void)cudaGetLastError();
+    free(c);
+    return CGB_OK;
+}
+
+int cgb_device_info(cgb_ctx *c, int *device, int *sm_count, int64_t *free_bytes,
+                    int64_t *total_bytes, char *name64)
+{
+    if (!c) FAIL(CGB_ERR_ARG, "cgb_device_info: null context");
+    size_t fr = 0, tot = 0;
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemGetInfo(&fr, &tot));
+    if (device) *device = c->device;
+    if (sm_count) *sm_count = c->sm_count;
+    if (free_bytes) *free_bytes = (int64_t)fr;
+    if (total_bytes) *total_bytes = (int64_t)tot;
+    if (name64) snprintf(name64, 64, "%s", c->name);
+    return CGB_OK;
+}
+
+/* ------------------------------------------------------------------ problem */
+static int ensure_problem(cgb_ctx *c, int64_t n)
+{
+    if (n < 1) FAIL(CGB_ERR_ARG, "matrix order must be >= 1");
+    if (n % c->ranks != 0) {
+        /* parallel_cg.c:86-90: "%d is not divisible by %d" */
+        snprintf(tl_err, sizeof tl_err, "%lld is not divisible by %d", (long long)n, c->ranks);
+        return CGB_ERR_NOT_DIVISIBLE;
+    }
+    const int64_t m = n / c->ranks;
+    CU(cudaSetDevice(c->device));
+    if (n != c->cap_n || m != c->cap_m) {
+        free_problem(c);
+        const size_t abytes = (size_t)m * (size_t)n * sizeof(double);
+        cudaError_t e = cudaMalloc((void **)&c->A, abytes);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            snprintf(tl_err, sizeof tl_err, "can't allocate memory for matrix block: %zu bytes on GPU %d (%s)",
+                     abytes, c->device, cudaGetErrorString(e));
+            return CGB_ERR_NOMEM;
+        }
+        CU(cudaMalloc((void **)&c->b, (size_t)m * sizeof(double)));
+        CU(cudaMalloc((void **)&c->r, (size_t)m * sizeof(double)));
+        CU(cudaMalloc((void **)&c->Ap, (size_t)m * sizeof(double)));
+        CU(cudaMalloc((void **)&c->p_full, (size_t)n * sizeof(double)));
+        CU(cudaMalloc((void **)&c->x_full, (size_t)n * sizeof(double)));
+        CU(cudaMalloc((void **)&c->partials_gemv, (size_t)cgk_gemv_max_ctas(m) * sizeof(double)));
+        c->cap_n = n; c->cap_m = m;
+    }
+    c->n = n; c->m = m;
+    return CGB_OK;
+}
+
+int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows,
+                  const double *x0_full)
+{
+    if (!c || !A_rows || !b_rows || !x0_full) FAIL(CGB_ERR_ARG, "cgb_load_host: null argument");
+    int rc = ensure_problem(c, n);
+    if (rc != CGB_OK) return rc;
+    const int64_t m = c->m;
+    double t0 = now_s();
+    CU(cudaMemcpyAsync(c->x_full, x0_full, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->b, b_rows, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    /* A in slabs so that pageable sources pipeline through the driver's staging */
+    const size_t total = (size_t)m * (size_t)n * sizeof(double), slab = (size_t)256 << 20;
+    for (size_t off = 0; off < total; off += slab) {
+        size_t len = total - off < slab ? total - off : slab;
+        CU(cudaMemcpyAsync((char *)c->A + off, (const char *)A_rows + off, len, cudaMemcpyHostToDevice, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    c->h2d_seconds = now_s() - t0;
+    c->loaded = 1;
+    return CGB_OK;
+}
+
+int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
+{
+    if (!c) FAIL(CGB_ERR_ARG, "cgb_generate: null context");
+    int rc = ensure_problem(c, n);
+    if (rc != CGB_OK) return rc;
+    const int64_t row0 = (int64_t)c->rank * c->m;
+    KL(cgk_generate_A(c->A, n, row0, c->m, seed, flags, c->stream));
+    KL(cgk_generate_b(c->b, n, row0, c->m, seed, flags, c->stream));
+    CU(cudaMemsetAsync(c->x_full, 0, (size_t)n * sizeof(double), c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->h2d_seconds = 0.0;
+    c->loaded = 1;
+    return CGB_OK;
+}
+
+int cgb_set_x0(cgb_ctx *c, const double *x0_full)
+{
+    if (!c || !x0_full) FAIL(CGB_ERR_ARG, "cgb_set_x0: null argument");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_set_x0: no problem loaded");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(c->x_full, x0_full, (size_t)c->n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return CGB_OK;
+}
+
+int cgb_read_x(cgb_ctx *c, double *x_full)
+{
+    if (!c || !x_full) FAIL(CGB_ERR_ARG, "cgb_read_x: null argument");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_read_x: no problem loaded");
+    CU(cudaSetDevice(c->device));
+    double t0 = now_s();
+    CU(cudaMemcpyAsync(x_full, c->x_full, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->d2h_seconds = now_s() - t0;
+    return CGB_OK;
+}
+
+int cgb_debug_read(cgb_ctx *c, int what, int64_t offset, int64_t count, double *dst)
+{
+    if (!c || !dst || offset < 0 || count < 0) FAIL(CGB_ERR_ARG, "cgb_debug_read: bad argument");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_debug_read: no problem loaded");
+    const double *src = NULL; int64_t lim = 0;
+    switch (what) {
+    case 0: src = c->A; lim = c->m * c->n; break;
+    case 1: src = c->b; lim = c->m; break;
+    case 2: src = c->x_full; lim = c->n; break;
+    case 3: src = c->r; lim = c->m; break;
+    case 4: src = c->p_full; lim = c->n; break;
+    case 5: src = c->Ap; lim = c->m; break;
+    default: FAIL(CGB_ERR_ARG, "cgb_debug_read: unknown array");
+    }
+    if (offset + count > lim) FAIL(CGB_ERR_ARG, "cgb_debug_read: range out of bounds");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(dst, src + offset, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return CGB_OK;
+}
+
+/* ------------------------------------------------------------------ solver */
+static void plan_request_from_options(cgk_gemv_plan *p, const cgb_options *o)
+{
+    memset(p, 0, sizeof *p);
+    p->variant = o->gemv_variant; p->rows_per_cta = o->gemv_rows; p->unroll = o->gemv_unroll;
+    p->threads = o->gemv_threads; p->vec = o->gemv_vec; p->stages = o->gemv_stages;
+    p->tile_cols = o->gemv_tile_cols;
+}
+
+/* One CG iteration on the solver stream; `cur` is the parity of the loop index
+ * (selects which rr[] slot is rho).  Mirrors parallel_cg.c:290-323. */
+static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int cur,
+                             cudaEvent_t ev_a, cudaEvent_t ev_b)
+{
+    const int multi = c->ranks > 1;
+    double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
+    double *x_loc = c->x_full + (size_t)c->rank * (size_t)c->m;
+    cudaStream_t st = c->stream;
+    if (multi)                                                   /* MPI_Allgather(p), :290-291 */
+        NC(ncclAllGather(p_loc, c->p_full, (size_t)c->m, ncclDouble, c->comm, st));
+    if (ev_a) CU(cudaEventRecord(ev_a, st));
+    KL(cgk_gemv(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv,
+                multi ? &c->sc->pAp_local : &c->sc->pAp, c->sc, c->m, c->n, st));   /* :292-293 */
+    if (ev_b) CU(cudaEventRecord(ev_b, st));
+    if (multi)                                                   /* MPI_Allreduce(alpha), :294 */
+        NC(ncclAllReduce(&c->sc->pAp_local, &c->sc->pAp, 1, ncclDouble, ncclSum, c->comm, st));
+    KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec,
+                     multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, c->m, st)); /* :298-309 */
+    if (multi)                                                   /* MPI_Allreduce(beta), :313 */
+        NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[cur ^ 1], 1, ncclDouble, ncclSum, c->comm, st));
+    KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, st)); /* :314-323 */
+    c->launches += 3;
+    return CGB_OK;
+}
+
+static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int chunk)
+{
+    struct cgb_graph_key key;
+    memset(&key, 0, sizeof key);
+    key.n = c->n; key.m = c->m; key.max_iter = max_iter; key.eps = o->eps;
+    key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan;
+    key.A = c->A;
+    if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
+    drop_graph(c);
+    const int64_t before = c->launches;
+    CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = CGB_OK;
+    for (int k = 0; k < chunk && rc == CGB_OK; ++k)
+        rc = enqueue_iteration(c, o, max_iter, k & 1, NULL, NULL);
+    cudaError_t e = cudaStreamEndCapture(c->stream, &c->graph);
+    c->launches = before;
+    if (rc != CGB_OK) { if (c->graph) { cudaGraphDestroy(c->graph); c->graph = NULL; } return rc; }
+    CU(e);
+    CU(cudaGraphInstantiate(&c->graph_exec, c->graph, 0));
+    c->graph_key = key;
+    return CGB_OK;
+}
+
+static int pick_chunk(const cgb_ctx *c, const cgb_options *o)
+{
+    int chunk = o->check_every;
+    if (chunk <= 0) {
+        /* keep the host poll (~20 us) under ~10 % of a replay: estimate the
+         * iteration from the GEMV's bytes at ~6 TB/s plus ~6 us of launch gaps */
+        double t_iter = 8.0 * (double)c->m * (double)c->n / 6.0e12 + 6.0e-6;
+        chunk = (int)ceil(200.0e-6 / t_iter);
+        if (chunk > 64) chunk = 64;
+    }
+    if (chunk < 2) chunk = 2;
+    if (chunk & 1) ++chunk;
+    return chunk;
+}
+
+static int ensure_gemv_events(cgb_ctx *c, int pairs)
+{
+    if (pairs * 2 <= c->n_gemv_ev) return CGB_OK;
+    cudaEvent_t *ne = realloc(c->gemv_ev, (size_t)pairs * 2 * sizeof *ne);
+    if (!ne) FAIL(CGB_ERR_NOMEM, "out of host memory for events");
+    c->gemv_ev = ne;
+    while (c->n_gemv_ev < pairs * 2) {
+        CU(cudaEventCreate(&c->gemv_ev[c->n_gemv_ev]));
+        c->n_gemv_ev++;
+    }
+    return CGB_OK;
+}
+
+int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
+{
+    if (!c) FAIL(CGB_ERR_ARG, "cgb_solve: null context");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_solve: no problem loaded (cgb_load_host / cgb_generate first)");
+    cgb_options o;
+    if (opt) o = *opt; else cgb_default_options(&o);
+    if (!(o.eps > 0.0)) o.eps = CGB_EPSILON;
+    const int64_t max_iter = o.max_iter > 0 ? o.max_iter : c->n;      /* parallel_cg.c:288 */
+    const int multi = c->ranks > 1;
+    cudaStream_t st = c->stream;
+    CU(cudaSetDevice(c->device));
+
+    cgk_gemv_plan req;
+    plan_request_from_options(&req, &o);
+    c->plan = req;
+    KL(cgk_gemv_make_plan(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
+    if ((int64_t)c->plan.grid > cgk_gemv_max_ctas(c->m)) FAIL(CGB_ERR_STATE, "gemv grid exceeds workspace");
+
+    double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
+    const int use_graph = o.use_graph && !o.time_gemv;
+    int chunk = 0;
+    if (use_graph) {
+        chunk = pick_chunk(c, &o);
+        int rc = build_graph(c, &o, max_iter, chunk);
+        if (rc != CGB_OK) return rc;
+    }
+    int timed_pairs = 0;
+    if (o.time_gemv) {
+        timed_pairs = max_iter < 1024 ? (int)max_iter : 1024;
+        int rc = ensure_gemv_events(c, timed_pairs);
+        if (rc != CGB_OK) return rc;
+    }
+
+    c->launches = 0;
+    CU(cudaStreamSynchronize(st));
+    const double t0 = now_s();
+    CU(cudaEventRecord(c->ev[0], st));
+    /* ---- init: Ax0, r = p = b - Ax0, rho = r.r   (parallel_cg.c:283-287) */
+    KL(cgk_reset(c->sc, st));
+    {
+        cgk_gemv_plan ip = req;                     /* same request, v = x0 */
+        KL(cgk_gemv_make_plan(&ip, c->m, c->n, c->A, c->x_full, c->sm_count));
+        KL(cgk_gemv(&ip, c->A, c->x_full, NULL, c->Ap, c->partials_gemv, NULL, c->sc, c->m, c->n, st));
+    }
+    KL(cgk_init_residual(c->b, c->Ap, c->r, p_loc, c->partials_vec,
+                         multi ? &c->sc->rr_local : &c->sc->rr[0], c->sc, c->m, st));
+    if (multi)
+        NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[0], 1, ncclDouble, ncclSum, c->comm, st));
+    KL(cgk_after_init(c->sc, st));
+    c->launches += 4;
+    CU(cudaEventRecord(c->ev[1], st));
+
+    /* ---- loop */
+    int64_t issued = 0;
+    int gemv_pairs_used = 0;
+    for (;;) {
+        if (use_graph) {
+            CU(cudaGraphLaunch(c->graph_exec, st));
+            issued += chunk;
+            c->launches += 3 * (int64_t)chunk;
+        } else {
+            /* stream mode: two iterations per poll keeps the rr[] parity aligned */
+            for (int k = 0; k < 2; ++k) {
+                cudaEvent_t ea = NULL, eb = NULL;
+                if (o.time_gemv && gemv_pairs_used < timed_pairs) {
+                    ea = c->gemv_ev[2 * gemv_pairs_used]; eb = c->gemv_ev[2 * gemv_pairs_used + 1];
+                }
+                int rc = enqueue_iteration(c, &o, max_iter, (int)((issued + k) & 1), ea, eb);
+                if (rc != CGB_OK) return rc;
+                if (ea && issued + k < max_iter) gemv_pairs_used++;
+            }
+            issued += 2;
+        }
+        if (o.ignore_stop && issued < max_iter) continue;      /* fixed-iteration mode: no polling */
+        CU(cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (c->h_sc->stop_req != 0) break;
+        if (issued > max_iter + 4) FAIL(CGB_ERR_STATE, "solver loop did not terminate");
+    }
+    CU(cudaEventRecord(c->ev[2], st));
+    /* every rank returns the full x, as the reference's replicated x (parallel_cg.c:299-303) */
+    if (multi)
+        NC(ncclAllGather(c->x_full + (size_t)c->rank * (size_t)c->m, c->x_full, (size_t)c->m, ncclDouble, c->comm, st));
+    CU(cudaStreamSynchronize(st));
+    const double t1 = now_s();
+
+    if (stats) {
+        float ms_init = 0.f, ms_loop = 0.f;
+        CU(cudaEventElapsedTime(&ms_init, c->ev[0], c->ev[1]));
+        CU(cudaEventElapsedTime(&ms_loop, c->ev[1], c->ev[2]));
+        memset(stats, 0, sizeof *stats);
+        stats->n = c->n; stats->m = c->m; stats->rank = c->rank; stats->ranks = c->ranks;
+        stats->iterations = c->h_sc->iters;
+        stats->break_k = c->h_sc->break_k;
+        stats->first_hit_k = c->h_sc->first_hit;
+        stats->final_beta = c->h_sc->final_beta;
+        stats->final_residual = sqrt(c->h_sc->final_beta);
+        stats->rsold0 = c->h_sc->rsold0;
+        stats->solve_seconds = t1 - t0;
+        stats->loop_ms = ms_loop; stats->init_ms = ms_init;
+        stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds;
+        stats->gemv_bytes = 8.0 * ((double)c->m * (double)c->n + (double)c->n + (double)c->m);
+        stats->kernel_launches = c->launches;
+        stats->gemv_variant = c->plan.variant; stats->gemv_rows = c->plan.rows_per_cta;
+        stats->gemv_unroll = c->plan.unroll; stats->gemv_threads = c->plan.threads;
+        stats->gemv_vec = c->plan.vec; stats->gemv_stages = c->plan.stages;
+        stats->gemv_tile_cols = c->plan.tile_cols; stats->gemv_grid = c->plan.grid;
+        stats->graph_chunk = chunk;
+        if (gemv_pairs_used > 0) {
+            double sum = 0.0, mn = 1e300;
+            for (int i = 0; i < gemv_pairs_used; ++i) {
+                float ms = 0.f;
+                CU(cudaEventElapsedTime(&ms, c->gemv_ev[2 * i], c->gemv_ev[2 * i + 1]));
+                sum += ms; if (ms < mn) mn = ms;
+            }
+            stats->gemv_ms_avg = sum / gemv_pairs_used;
+            stats->gemv_ms_min = mn;
+            stats->gemv_timed = gemv_pairs_used;
+        }
+    }
+    return CGB_OK;
+}
+
+int cgb_conjugrad_rank(cgb_ctx *c, const double *local_A, const double *local_b,
+                       double *local_x, int64_t local_row, const cgb_options *opt,
+                       cgb_stats *stats)
+{
+    if (!c || !local_A || !local_b || !local_x || local_row < 1)
+        FAIL(CGB_ERR_ARG, "cgb_conjugrad_rank: bad argument");
+    const int64_t n = local_row * c->ranks;
+    int rc = cgb_load_host(c, n, local_A, local_b, local_x);
+    if (rc != CGB_OK) return rc;
+    rc = cgb_solve(c, opt, stats);
+    if (rc != CGB_OK) return rc;
+    rc = cgb_read_x(c, local_x);
+    if (rc == CGB_OK && stats) { stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds; }
+    return rc;
+}
+
+/* ------------------------------------------------------------------ measurement */
+int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int flush_l2,
+                  double *ms_avg, double *ms_min)
+{
+    if (!c || reps < 1) FAIL(CGB_ERR_ARG, "cgb_time_gemv: bad argument");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_time_gemv: no problem loaded");
+    cgb_options o;
+    if (opt) o = *opt; else cgb_default_options(&o);
+    CU(cudaSetDevice(c->device));
+    cgk_gemv_plan plan;
+    plan_request_from_options(&plan, &o);
+    KL(cgk_gemv_make_plan(&plan, c->m, c->n, c->A, c->p_full, c->sm_count));
+    cudaStream_t st = c->stream;
+    const size_t flush_bytes = (size_t)512 << 20;
+    if (flush_l2 && !c->flush_buf) {
+        CU(cudaMalloc(&c->flush_buf, flush_bytes));
+        CU(cudaMemsetAsync(c->flush_buf, 0, flush_bytes, st));
+    }
+    KL(cgk_reset(c->sc, st));
+    double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
+    for (int i = 0; i < warmup; ++i)
+        KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
+    double sum = 0.0, mn = 1e300;
+    for (int i = 0; i < reps; ++i) {
+        if (flush_l2) KL(cgk_l2_flush(c->flush_buf, (int64_t)flush_bytes, st));
+        CU(cudaEventRecord(c->ev[0], st));
+        KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
+        CU(cudaEventRecord(c->ev[1], st));
+        CU(cudaEventSynchronize(c->ev[1]));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+        sum += ms; if (ms < mn) mn = ms;
+    }
+    if (ms_avg) *ms_avg = sum / reps;
+    if (ms_min) *ms_min = mn;
+    c->plan = plan;
+    return CGB_OK;
+}
+
+/* ------------------------------------------------------------------ single-kernel operators */
+static int dev_dup(double **d, const double *h, int64_t count, cudaStream_t st)
+{
+    CU(cudaMalloc((void **)d, (size_t)(count > 0 ? count : 1) * sizeof(double)));
+    if (h) CU(cudaMemcpyAsync(*d, h, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, st));
+    return CGB_OK;
+}
+
+int cgb_op_matvec(cgb_ctx *c, const double *A, const double *v, const double *w, double *y,
+                  double *dot, int64_t m, int64_t n, const cgb_options *opt)
+{
+    if (!c || !A || !v || !y || m < 1 || n < 1) FAIL(CGB_ERR_ARG, "cgb_op_matvec: bad argument");
+    cgb_options o;
+    if (opt) o = *opt; else cgb_default_options(&o);
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    double *dA = NULL, *dv = NULL, *dw = NULL, *dy = NULL, *dpart = NULL;
+    int rc;
+    if ((rc = dev_dup(&dA, A, m * n, st)) || (rc = dev_dup(&dv, v, n, st)) ||
+        (rc = dev_dup(&dy, NULL, m, st)) || (rc = dev_dup(&dpart, NULL, cgk_gemv_max_ctas(m), st)))
+        goto out;
+    if (w && (rc = dev_dup(&dw, w, m, st))) goto out;
+    cgk_gemv_plan plan;
+    plan_request_from_options(&plan, &o);
+    rc = CGB_ERR_CUDA;
+    if (cgk_gemv_make_plan(&plan, m, n, dA, dv, c->sm_count) != 0) { cgb_set_error("%s%s (cg_solver.c:%d)", "no gemv plan for this shape", "", __LINE__); goto out; }
+    if (cgk_reset(c->sc, st) != 0) goto out;
+    if (cgk_gemv(&plan, dA, dv, dw, dy, dpart, &c->sc->pAp, c->sc, m, n, st) != 0) {
+        cgb_set_error("%s%s (cg_solver.c:%d)", "gemv launch failed: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
+        goto out;
+    }
+    if (cudaMemcpyAsync(y, dy, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    {
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { cgb_set_error("CUDA error: %s in `%s` (cg_solver.c:%d)", cudaGetErrorString(e), "gemv", __LINE__); goto out; }
+    }
+    if (dot) *dot = w ? c->h_sc->pAp : 0.0;
+    c->plan = plan;
+    rc = CGB_OK;
+out:
+    cudaFree(dA); cudaFree(dv); cudaFree(dw); cudaFree(dy); cudaFree(dpart);
+    return rc;
+}
+
+int cgb_op_init_residual(cgb_ctx *c, const double *b, const double *Ax, double *r, double *p,
+                         double *rr, int64_t m)
+{
+    if (!c || !b || !Ax || !r || !p || m < 1) FAIL(CGB_ERR_ARG, "cgb_op_init_residual: bad argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    double *db = NULL, *dAx = NULL, *dr = NULL, *dp = NULL;
+    int rc;
+    if ((rc = dev_dup(&db, b, m, st)) || (rc = dev_dup(&dAx, Ax, m, st)) ||
+        (rc = dev_dup(&dr, NULL, m, st)) || (rc = dev_dup(&dp, NULL, m, st)))
+        goto out;
+    rc = CGB_ERR_CUDA;
+    if (cgk_reset(c->sc, st) != 0) goto out;
+    if (cgk_init_residual(db, dAx, dr, dp, c->partials_vec, &c->sc->rr[0], c->sc, m, st) != 0) goto out;
+    if (cudaMemcpyAsync(r, dr, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaMemcpyAsync(p, dp, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaStreamSynchronize(st) != cudaSuccess) goto out;
+    if (rr) *rr = c->h_sc->rr[0];
+    rc = CGB_OK;
+out:
+    if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in init_residual op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
+    cudaFree(db); cudaFree(dAx); cudaFree(dr); cudaFree(dp);
+    return rc;
+}
+
+int cgb_op_xr_update(cgb_ctx *c, double rho, double pAp, double *x, double *r, const double *p,
+                     const double *Ap, double *rr, int64_t m)
+{
+    if (!c || !x || !r || !p || !Ap || m < 1) FAIL(CGB_ERR_ARG, "cgb_op_xr_update: bad argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    double *dx = NULL, *dr = NULL, *dp = NULL, *dAp = NULL;
+    int rc;
+    if ((rc = dev_dup(&dx, x, m, st)) || (rc = dev_dup(&dr, r, m, st)) ||
+        (rc = dev_dup(&dp, p, m, st)) || (rc = dev_dup(&dAp, Ap, m, st)))
+        goto out;
+    rc = CGB_ERR_CUDA;
+    if (cgk_reset(c->sc, st) != 0) goto out;
+    memset(c->h_sc, 0, sizeof *c->h_sc);
+    c->h_sc->rr[0] = rho; c->h_sc->pAp = pAp; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
+    if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
+    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, m, st) != 0) goto out;
+    if (cudaMemcpyAsync(x, dx, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaMemcpyAsync(r, dr, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaStreamSynchronize(st) != cudaSuccess) goto out;
+    if (rr) *rr = c->h_sc->rr[1];
+    rc = CGB_OK;
+out:
+    if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in xr_update op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
+    cudaFree(dx); cudaFree(dr); cudaFree(dp); cudaFree(dAp);
+    return rc;
+}
+
+int cgb_op_p_update(cgb_ctx *c, double rho, double beta, double eps, double *p, const double *r,
+                    int *stopped, int64_t m)
+{
+    if (!c || !p || !r || m < 1) FAIL(CGB_ERR_ARG, "cgb_op_p_update: bad argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    double *dp = NULL, *dr = NULL;
+    int rc;
+    if ((rc = dev_dup(&dp, p, m, st)) || (rc = dev_dup(&dr, r, m, st))) goto out;
+    rc = CGB_ERR_CUDA;
+    memset(c->h_sc, 0, sizeof *c->h_sc);
+    c->h_sc->rr[0] = rho; c->h_sc->rr[1] = beta; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
+    if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
+    if (cgk_p_update(dp, dr, c->sc, 0, eps, 0, (int64_t)1 << 40, m, st) != 0) goto out;
+    if (cudaMemcpyAsync(p, dp, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    if (cudaStreamSynchronize(st) != cudaSuccess) goto out;
+    if (stopped) *stopped = c->h_sc->stop_req == 1;
+    rc = CGB_OK;
+out:
+    if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in p_update op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
+    cudaFree(dp); cudaFree(dr);
+    return rc;
+}
+
+int cgb_op_generate(cgb_ctx *c, int64_t n, int64_t row0, int64_t m, uint64_t seed, unsigned flags,
+                    double *A_rows, double *b_rows)
+{
+    if (!c || n < 1 || m < 1 || row0 < 0 || row0 + m > n) FAIL(CGB_ERR_ARG, "cgb_op_generate: bad argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    double *dA = NULL, *db = NULL;
+    int rc = CGB_OK;
+    if (A_rows) {
+        if ((rc = dev_dup(&dA, NULL, m * n, st))) goto out;
+        rc = CGB_ERR_CUDA;
+        if (cgk_generate_A(dA, n, row0, m, seed, flags, st) != 0) goto out;
+        if (cudaMemcpyAsync(A_rows, dA, (size_t)m * (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    }
+    if (b_rows) {
+        if ((rc = dev_dup(&db, NULL, m, st))) goto out;
+        rc = CGB_ERR_CUDA;
+        if (cgk_generate_b(db, n, row0, m, seed, flags, st) != 0) goto out;
+        if (cudaMemcpyAsync(b_rows, db, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
+    }
+    rc = cudaStreamSynchronize(st) == cudaSuccess ? CGB_OK : CGB_ERR_CUDA;
+out:
+    if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in generate op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
+    cudaFree(dA); cudaFree(db);
+    return rc;
+}

@@ -1,0 +1,233 @@
+/* cgb200.h -- C ABI of libcgb200.so: a B200-native (sm_100a) dense FP64
+ * conjugate-gradient solver behind the drop-in surface of
+ * mawunyega/conjugate_gradient.
+ *
+ * The reference has no plugin/FFI layer: its boundary is a C function,
+ * conjugrad(), compiled into each program, plus a three-file CLI.  Every entry
+ * point below states the reference interface it replaces (file:line are into
+ * the reference repository).  Plain C: pointers, sizes, POD structs; no C++ or
+ * torch types cross this boundary.  There is no CPU fallback: every call that
+ * computes needs a CUDA device and fails with CGB_ERR_CUDA otherwise.
+ *
+ * Element type: the reference is `float` throughout (serialConjugate.c:33-41,
+ * parallel_cg.c:34-52); this library is `double` (the FP64 target of the
+ * north star).  Problem size: the reference bakes n in as `#define ROWS/COLS`
+ * (serialConjugate.c:29-30, parallel_cg.c:30-31); here n is a run-time
+ * argument (or dimensions.txt for the CLI).
+ */
+#ifndef CGB200_H
+#define CGB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CGB_VERSION 100
+
+/* status codes (the reference returns nothing and exit(0)s / MPI_Aborts on
+ * failure, serialConjugate.c:48-57,78-82, parallel_cg.c:76-95; a library must not) */
+#define CGB_OK                 0
+#define CGB_ERR_ARG           -1   /* bad argument / null pointer / n < 1            */
+#define CGB_ERR_CUDA          -2   /* CUDA runtime error or no device                 */
+#define CGB_ERR_NCCL          -3   /* NCCL error                                      */
+#define CGB_ERR_NOT_DIVISIBLE -4   /* n % ranks != 0   (parallel_cg.c:86-90)          */
+#define CGB_ERR_NOMEM         -5   /* host or device allocation failed (:140-144)     */
+#define CGB_ERR_STATE         -6   /* no problem loaded / wrong call order            */
+#define CGB_ERR_IO            -7   /* text input missing, short or malformed          */
+
+#define CGB_EPSILON 1.0e-6         /* serialConjugate.c:28, parallel_cg.c:29          */
+
+/* generator flags */
+#define CGB_GEN_ROUND4 1u          /* mimic generateSPDmatrix.m's "%.4f" round trip   */
+
+/* GEMV kernel selection (0 = library default) */
+#define CGB_GEMV_AUTO 0
+#define CGB_GEMV_LDG  1            /* 128/256-bit streaming loads, registers          */
+#define CGB_GEMV_BULK 2            /* cp.async.bulk (TMA engine) shared-memory ring   */
+
+typedef struct cgb_ctx cgb_ctx;    /* one per rank (= per GPU); owns all device state */
+
+typedef struct cgb_options {
+    double  eps;           /* stop when sqrt(r.r) < eps; <= 0 -> CGB_EPSILON (parallel_cg.c:314)  */
+    int64_t max_iter;      /* <= 0 -> n, the reference's loop bound (parallel_cg.c:288)            */
+    int     ignore_stop;   /* 1: fixed-iteration timing mode, the test is evaluated and recorded   */
+                           /*    but not acted on (not in the reference)         */
+    int     use_graph;     /* 1 (default): iterations are replayed from a captured CUDA graph      */
+    int     check_every;   /* iterations per graph launch between host polls of the stop flag;     */
+                           /* 0 -> chosen from the estimated iteration time; rounded up to even    */
+    int     time_gemv;     /* 1: stream mode with a CUDA-event pair around every GEMV launch       */
+    int     gemv_variant;  /* CGB_GEMV_*                                                           */
+    int     gemv_rows;     /* rows per CTA (0 auto)                                                */
+    int     gemv_unroll;   /* LDG: load steps in flight per thread (0 auto)                        */
+    int     gemv_threads;  /* threads per CTA (0 auto)                                             */
+    int     gemv_vec;      /* LDG: doubles per load 1/2/4 (0 auto)                                 */
+    int     gemv_stages;   /* BULK: ring depth (0 auto)                                            */
+    int     gemv_tile_cols;/* BULK: columns per stage (0 auto)                                     */
+    int     reserved[4];
+} cgb_options;
+
+typedef struct cgb_stats {
+    int64_t n, m;              /* order; rows owned by this rank (n / ranks, parallel_cg.c:83)     */
+    int     rank, ranks;
+    int64_t iterations;        /* x/r updates applied = loop index at break + 1                    */
+    int64_t break_k;           /* 0-based loop index at `break` (parallel_cg.c:314-317), -1 if the */
+                               /* loop ran out                                                     */
+    int64_t first_hit_k;       /* first k at which sqrt(beta) < eps held, -1 if never              */
+    double  final_beta;        /* last r.r                                                         */
+    double  final_residual;    /* sqrt(final_beta): what the stop rule compares with eps           */
+    double  rsold0;            /* initial r.r                                                      */
+    double  solve_seconds;     /* host wall clock around the solver region, where the reference    */
+                               /* times it (serialConjugate.c:208,249; parallel_cg.c:278-279,328-329) */
+    double  loop_ms;           /* CUDA-event time of the iteration loop on the solver stream       */
+    double  init_ms;           /* CUDA-event time of A*x0, residual, initial r.r                   */
+    double  h2d_seconds;       /* last cgb_load_host                                               */
+    double  d2h_seconds;       /* last cgb_read_x                                                  */
+    double  gemv_ms_avg;       /* time_gemv=1: mean / min CUDA-event duration of the loop's GEMVs  */
+    double  gemv_ms_min;
+    int64_t gemv_timed;        /* number of GEMV launches in that mean                             */
+    double  gemv_bytes;        /* algorithmic bytes per GEMV launch on this rank: 8*(m*n + n + m)  */
+    int64_t kernel_launches;   /* kernels of this library enqueued by the last solve (incl. those  */
+                               /* replayed from graphs; NCCL kernels not counted)                  */
+    int     gemv_variant, gemv_rows, gemv_unroll, gemv_threads, gemv_vec, gemv_stages,
+            gemv_tile_cols, gemv_grid;
+    int     graph_chunk;       /* iterations per captured graph (0: stream mode)                   */
+    int     reserved[3];
+} cgb_stats;
+
+/* ---- library / device ------------------------------------------------------ */
+int         cgb_version(void);
+int         cgb_device_count(void);               /* < 0: CUDA unusable                */
+const char *cgb_last_error(void);                 /* message of this thread's last failure */
+void        cgb_default_options(cgb_options *o);
+
+/* ---- contexts -------------------------------------------------------------- */
+/* One rank on one GPU, no communicator: the serial program (serialConjugate.c). */
+int cgb_create(cgb_ctx **out, int device);
+/* SPMD rank `rank` of `ranks` on GPU `device` (parallel_cg.c:81-83: MPI_Comm_rank /
+ * MPI_Comm_size).  `id` is the 128-byte NCCL unique id made by cgb_unique_id() on
+ * one rank and handed to all others by the caller's launcher (torchrun, MPI, a
+ * file, threads).  Collective: every rank must call it. */
+int cgb_unique_id(void *id128);
+int cgb_create_rank(cgb_ctx **out, int device, int rank, int ranks, const void *id128);
+int cgb_destroy(cgb_ctx *ctx);
+
+/* ---- problem set-up -------------------------------------------------------- */
+/* What MPI_Bcast(x0) + MPI_Scatter(A) + MPI_Scatter(b) deliver to a rank
+ * (parallel_cg.c:111-115): the rank's m = n/ranks rows of A (row-major, m x n),
+ * its m entries of b, and the FULL initial guess x0 (n).  Host buffers,
+ * caller-owned, copied to the GPU (pinned buffers copy at PCIe rate). */
+int cgb_load_host(cgb_ctx *ctx, int64_t n, const double *A_rows, const double *b_rows,
+                  const double *x0_full);
+/* North-star item 4: the rank's rows of the seeded SPD system generated in place
+ * on the GPU (generateSPDmatrix.m:4-17): A = 0.5(R+R') + nI, b = rand, x0 = 0. */
+int cgb_generate(cgb_ctx *ctx, int64_t n, uint64_t seed, unsigned flags);
+/* Replace only the initial guess (n doubles, host) of a loaded problem, e.g. to
+ * restart from a previous solution (the reference's x0 file is its restart input). */
+int cgb_set_x0(cgb_ctx *ctx, const double *x0_full);
+
+/* ---- the solver ------------------------------------------------------------ */
+/* conjugrad() on the resident problem (serialConjugate.c:180-259 /
+ * parallel_cg.c:248-345): r = p = b - A x0; loop { Ap; alpha = rho/(p.Ap);
+ * x += alpha p; r -= alpha Ap; beta = r.r; if sqrt(beta) < eps break;
+ * p = r + (beta/rho) p; rho = beta }.  Collective over the ranks.  x stays on
+ * the device (replicated on every rank on return, as in the reference). */
+int cgb_solve(cgb_ctx *ctx, const cgb_options *opt, cgb_stats *stats);
+/* Full solution vector (n doubles) to a host buffer. */
+int cgb_read_x(cgb_ctx *ctx, double *x_full);
+
+/* ---- one-call drop-ins ----------------------------------------------------- */
+/* Runtime-n equivalent of `void conjugrad(float *matrixA, float *vectorB, float
+ * *vectorX)` (serialConjugate.c:40,180): host A (n x n), b, x; x is the initial
+ * guess on entry and the solution on exit.  `gpus` > 1 row-shards A over that
+ * many GPUs of this node from one process (one host thread per GPU). */
+int cgb_conjugrad_host(const double *A, const double *b, double *x, int64_t n,
+                       double eps, int64_t max_iter, int gpus, cgb_stats *stats);
+/* Same, with the full option block (fixed-iteration mode, kernel selection). */
+int cgb_conjugrad_host_opt(const double *A, const double *b, double *x, int64_t n, int gpus,
+                           const cgb_options *opt, cgb_stats *stats);
+/* North-star item 4 end to end: generate the seeded SPD system of order n on
+ * `gpus` GPUs (each its own row block, generateSPDmatrix.m:4-17), solve, and
+ * return x (n doubles, may be NULL).  No text files, no host copy of A. */
+int cgb_solve_generated(int64_t n, uint64_t seed, unsigned flags, int gpus,
+                        const cgb_options *opt, double *x, cgb_stats *stats);
+/* Releases the contexts cached by the one-call entry points (GPU memory, NCCL
+ * communicators, graphs).  The reference frees its temporaries at the end of
+ * every conjugrad() (serialConjugate.c:253-258); here it is explicit. */
+int cgb_shutdown(void);
+/* Same for a rank of an SPMD program, replacing `void conjugrad(float
+ * *local_matrixA, float *local_vectorB, float *local_vectorX, int local_row, int
+ * myrank, int procsnum)` (parallel_cg.c:46-48,248-250) on an existing rank
+ * context: local_x is the FULL vector (n = local_row * ranks), in/out. */
+int cgb_conjugrad_rank(cgb_ctx *ctx, const double *local_A, const double *local_b,
+                       double *local_x, int64_t local_row, const cgb_options *opt,
+                       cgb_stats *stats);
+
+/* Source-compatible wrappers with the reference's exact names and argument
+ * lists (element type double).  n comes from cgb_set_dimension(), the run-time
+ * replacement of `#define ROWS` (or from dimensions.txt through the CLI).
+ * They print what the reference prints from inside conjugrad():
+ *   "average clock execution time in seconds: %f\n"  (serialConjugate.c:249-251)
+ *   "cg method execution time in seconds: %f\n"      (parallel_cg.c:334-335, rank 0)
+ * and report failures on stderr (the reference would exit/abort). */
+void cgb_set_dimension(int64_t n);
+void conjugrad(double *matrixA, double *vectorB, double *vectorX);
+void conjugrad_mpi(double *local_matrixA, double *local_vectorB, double *local_vectorX,
+                   int local_row, int myrank, int procsnum);
+/* Stats of the calling thread's last conjugrad()/conjugrad_mpi() call. */
+int  cgb_last_stats(cgb_stats *out);
+/* Releases the calling thread's conjugrad_mpi() rank context (collective). */
+int  cgb_release_rank(void);
+
+/* ---- text inputs and output of the reference CLI --------------------------- */
+/* dimensions.txt: shipped by the reference (dimensions.txt:1-4) but opened by
+ * none of its programs; here it is the run-time ROWS/COLS: four integers, one
+ * per line: rows(A) cols(A) rows(b) cols(b). */
+int     cgb_read_dimensions(const char *path, int64_t dims[4]);
+/* initialize() (serialConjugate.c:85-105, parallel_cg.c:147-168): `count`
+ * numbers, row-major, "%f%*c" token rules (any whitespace or one separator
+ * character between numbers; a UTF-8 BOM is skipped).  Unlike the reference,
+ * a missing file or a short file is an error (CGB_ERR_IO), not garbage. */
+int     cgb_read_values(const char *path, double *dst, int64_t count, int64_t *got);
+int64_t cgb_count_values(const char *path);      /* numeric tokens in a file, < 0 on error */
+/* generateSPDmatrix.m:28-43 file format: one value per line, "%.<d>f"
+ * (4 for A and b, 1 for x0); decimals < 0 writes round-trippable "%.17g". */
+int     cgb_write_values(const char *path, const double *v, int64_t count, int decimals);
+
+/* ---- kernel-level operators (parity tests, profiling) ---------------------- */
+/* Each runs ONE product kernel on host data: upload, launch, download. */
+/* matVec (parallel_cg.c:172-184) with the fused vecVec(w, y) (:293):
+ * y = A v for an m x n block; if w != NULL *dot = sum_i w[i]*y[i]. */
+int cgb_op_matvec(cgb_ctx *ctx, const double *A, const double *v, const double *w,
+                  double *y, double *dot, int64_t m, int64_t n, const cgb_options *opt);
+/* residual twice + vecVec (parallel_cg.c:284-286): r = p = b - Ax, *rr = r.r */
+int cgb_op_init_residual(cgb_ctx *ctx, const double *b, const double *Ax, double *r,
+                         double *p, double *rr, int64_t m);
+/* scalarVec/vecAdd/vecSub/vecVec (parallel_cg.c:298-309): alpha = rho/pAp,
+ * x += alpha p, r -= alpha Ap, *rr = r.r (x, r in/out). */
+int cgb_op_xr_update(cgb_ctx *ctx, double rho, double pAp, double *x, double *r,
+                     const double *p, const double *Ap, double *rr, int64_t m);
+/* stop rule + scalarVec/vecAdd (parallel_cg.c:314-322): returns *stopped = 1 and
+ * leaves p untouched if sqrt(beta) < eps, else p = r + (beta/rho) p (p in/out). */
+int cgb_op_p_update(cgb_ctx *ctx, double rho, double beta, double eps, double *p,
+                    const double *r, int *stopped, int64_t m);
+/* Rows [row0,row0+m) of the generated A (m x n) and b to host buffers (either may be NULL). */
+int cgb_op_generate(cgb_ctx *ctx, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                    unsigned flags, double *A_rows, double *b_rows);
+
+/* ---- measurement helpers --------------------------------------------------- */
+/* Times `reps` back-to-back launches of the GEMV on the resident problem
+ * (v = current direction vector) with CUDA events on the solver stream, after
+ * `warmup` launches; A must exceed L2 or flush_l2 != 0.  Outputs ms per launch. */
+int cgb_time_gemv(cgb_ctx *ctx, const cgb_options *opt, int warmup, int reps, int flush_l2,
+                  double *ms_avg, double *ms_min);
+/* Copies rows/entries of resident device arrays to the host (tests).
+ * what: 0 A rows, 1 b, 2 x (full), 3 r, 4 p (full), 5 Ap. */
+int cgb_debug_read(cgb_ctx *ctx, int what, int64_t offset, int64_t count, double *dst);
+int cgb_device_info(cgb_ctx *ctx, int *device, int *sm_count, int64_t *free_bytes,
+                    int64_t *total_bytes, char *name64);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

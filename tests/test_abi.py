@@ -1,0 +1,87 @@
+"""CPU-only checks of the drop-in boundary: the C-ABI library loads, exports
+every symbol include/cgb200.h declares, the host-side text I/O behaves like the
+reference's initialize()/printer(), and every computing entry point fails
+loudly (no fallback) when there is no GPU."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import conjugate_gradient_b200 as cg
+from conjugate_gradient_b200 import _binding as B
+
+
+def test_library_exports_every_declared_symbol():
+    L = cg.lib()
+    assert len(cg.HEADER_SYMBOLS) >= 30
+    missing = [s for s in cg.HEADER_SYMBOLS if not hasattr(L, s)]
+    assert not missing, missing
+    assert L.cgb_version() == 100
+
+
+def test_struct_layouts_match_header():
+    # sizeof as the C compiler sees them (a tiny probe compiled against the header)
+    src = '#include <stdio.h>\n#include "cgb200.h"\nint main(){printf("%zu %zu\\n", sizeof(cgb_options), sizeof(cgb_stats));return 0;}\n'
+    exe = "/tmp/cgb_sizeof_probe"
+    subprocess.run(["gcc", "-x", "c", "-", "-I", os.path.join(B.ROOT, "include"), "-o", exe],
+                   input=src.encode(), check=True)
+    so, ss = map(int, subprocess.run([exe], capture_output=True, check=True).stdout.split())
+    assert so == C.sizeof(cg.Options) and ss == C.sizeof(cg.Stats)
+
+
+def test_no_oracle_in_product():
+    # the product must not link, import or execute anything under oracle/
+    out = subprocess.run(["ldd", cg.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out
+    for root, _, files in os.walk(os.path.join(B.ROOT, "conjugate_gradient_b200")):
+        for f in files:
+            if f.endswith((".py", ".c", ".cu", ".h", ".cuh", "Makefile")):
+                txt = open(os.path.join(root, f), errors="ignore").read()
+                assert "liboracle" not in txt and "_oracle" not in txt and "oracle/" not in txt, f
+
+
+def test_text_inputs(tmp_path, golden_dir):
+    assert cg.read_dimensions(os.path.join(golden_dir, "g1_dimensions.txt")) == (2, 2, 2, 1)
+    v = cg.read_values(os.path.join(golden_dir, "g2_matrixA.txt"), 16)
+    assert v[0] == 7.0 and v[7] == -4.0 and v[15] == 6.0
+    # separators "%f%*c" tolerates, CRLF, a BOM (the reference's initialguess1.txt has one)
+    p = tmp_path / "mixed.txt"
+    p.write_bytes(b"1.5,2.5;3e0\r\n-4.25 \t5\n\xef\xbb\xbf6.0\n")
+    np.testing.assert_array_equal(cg.read_values(str(p), 6), [1.5, 2.5, 3.0, -4.25, 5.0, 6.0])
+    with pytest.raises(cg.CgbError):           # short file: reported, not silently garbage
+        cg.read_values(str(p), 7)
+    with pytest.raises(cg.CgbError):           # missing file ("Could not open file")
+        cg.read_values(str(tmp_path / "nope.txt"), 1)
+    q = tmp_path / "bad.txt"
+    q.write_text("1.0\nabc\n")
+    with pytest.raises(cg.CgbError):
+        cg.read_values(str(q), 2)
+    # generateSPDmatrix.m:28-43 format round trip
+    w = tmp_path / "w.txt"
+    cg.write_values(str(w), [0.12344, 2048.5], 4)
+    assert w.read_text() == "0.1234\n2048.5000\n"
+    cg.write_values(str(w), [1 / 3], -1)
+    assert cg.read_values(str(w), 1)[0] == 1 / 3
+
+
+def test_cli_messages_without_gpu(golden_dir):
+    exe = B.CLI_PATH
+    r = subprocess.run([exe, "a", "b"], capture_output=True, text=True)
+    assert r.returncode != 0 and "requires four (4) files" in r.stdout      # serialConjugate.c:50
+    r = subprocess.run([exe, os.path.join(golden_dir, "g2_matrixA.txt"), os.path.join(golden_dir, "g2_vectorb.txt"),
+                        os.path.join(golden_dir, "g2_x0.txt"), "--dims", os.path.join(golden_dir, "g2_dimensions.txt"),
+                        "--gpus", "3"], capture_output=True, text=True)
+    assert r.returncode != 0 and "4 is not divisible by 3" in r.stdout       # parallel_cg.c:88
+    r = subprocess.run([exe, "/nonexistent/A.txt", "/nonexistent/b.txt", "/nonexistent/x.txt"], capture_output=True, text=True)
+    assert r.returncode != 0 and "Could not open file" in r.stdout           # serialConjugate.c:103
+
+
+def test_compute_fails_loudly_without_gpu():
+    if cg.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(cg.CgbError):
+        cg.Context(0)
+    with pytest.raises(cg.CgbError):
+        cg.conjugrad_host(np.eye(2), np.ones(2), np.zeros(2))

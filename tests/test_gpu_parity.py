@@ -1,0 +1,233 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libcgb200.so),
+against the CPU oracle and the golden vectors of the real reference.
+
+Tolerances (north star): relative solution error <= 1e-10 against the FP64
+reference's own final iterate, iteration count within +-1, final residual below
+the reference's tolerance (1e-6).  Integer / bit-level items (generator,
+element-wise updates with the reference's rounding points) are bit-exact.
+"""
+import numpy as np
+import pytest
+
+import _oracle as O
+from conftest import unhex
+
+pytestmark = pytest.mark.gpu
+EPS = 1.0e-6
+RTOL_X = 1.0e-10
+
+
+@pytest.fixture(scope="module")
+def cg():
+    import conjugate_gradient_b200 as m
+    assert m.device_count() >= 1, "no CUDA device: the product has no CPU fallback"
+    return m
+
+
+@pytest.fixture(scope="module")
+def ctx(cg):
+    with cg.Context(0) as c:
+        yield c
+
+
+def relerr(x, ref):
+    return np.linalg.norm(x - ref) / max(np.linalg.norm(ref), 1e-300)
+
+
+def case_inputs(c):
+    n = c["n"]
+    if "A" in c:
+        return unhex(c["A"]).reshape(n, n), unhex(c["b"]), unhex(c["x0"])
+    return O.gen_A(n, c["seed"], c["flags"]), O.gen_b(n, c["seed"], c["flags"]), np.zeros(n)
+
+
+# ----------------------------------------------------------------- generator
+@pytest.mark.parametrize("n,row0,m,flags", [(8, 0, 8, 0), (300, 0, 300, 0), (1024, 512, 256, 0),
+                                            (513, 7, 100, 0), (256, 0, 256, 1)])
+def test_generator_bit_identical_to_cpu_twin(ctx, golden, n, row0, m, flags):
+    seed = golden["seed"]
+    A, b = ctx.op_generate(n, seed, flags, row0, m)
+    assert A.tobytes() == O.gen_A(n, seed, flags, row0, m).tobytes()
+    assert b.tobytes() == O.gen_b(n, seed, flags, row0, m).tobytes()
+    if n == 8 and flags == 0:
+        assert A.ravel().tobytes() == unhex(golden["generator"]["A8"]).tobytes()
+
+
+def test_generator_large_indices(ctx):
+    # 64-bit index arithmetic: element indices beyond 2^32 (n = 70000 -> n*n = 4.9e9)
+    n, seed = 70000, 11
+    A, b = ctx.op_generate(n, seed, 0, row0=69990, m=4)
+    assert A.tobytes() == O.gen_A(n, seed, 0, 69990, 4).tobytes()
+    assert b.tobytes() == O.gen_b(n, seed, 0, 69990, 4).tobytes()
+
+
+# ----------------------------------------------------------------- single kernels
+GEMV_CFGS = [dict(), dict(gemv_variant=1, gemv_vec=2), dict(gemv_variant=1, gemv_rows=8, gemv_unroll=1, gemv_threads=128),
+             dict(gemv_variant=1, gemv_rows=2, gemv_unroll=4, gemv_threads=256),
+             dict(gemv_variant=2), dict(gemv_variant=2, gemv_rows=4, gemv_stages=4, gemv_tile_cols=512),
+             dict(gemv_variant=2, gemv_rows=8, gemv_stages=3, gemv_tile_cols=1024, gemv_threads=256)]
+
+
+@pytest.mark.parametrize("m,n", [(1, 1), (2, 2), (4, 4), (3, 5), (7, 33), (64, 1000), (130, 1026),
+                                 (257, 2048), (512, 4096), (100, 8192), (2048, 2048)])
+@pytest.mark.parametrize("cfg", range(len(GEMV_CFGS)))
+def test_matvec_and_fused_dot(ctx, m, n, cfg):
+    rng = np.random.default_rng(m * 7919 + n)
+    A = rng.standard_normal((m, n)); v = rng.standard_normal(n); w = rng.standard_normal(m)
+    y, dot = ctx.op_matvec(A, v, w, **GEMV_CFGS[cfg])
+    y_ref = O.matvec(A, v)                                   # parallel_cg.c:172-184 order
+    scale = np.abs(A) @ np.abs(v)                            # rounding-error scale per row
+    assert np.all(np.abs(y - y_ref) <= 1e-15 * np.sqrt(n) * scale + 1e-300)
+    dot_ref = O.vecvec(w, y_ref)
+    assert abs(dot - dot_ref) <= 1e-13 * (np.abs(w) @ np.abs(y_ref)) + 1e-300
+    y2 = ctx.op_matvec(A, v, None, **GEMV_CFGS[cfg])         # w == NULL path (A*x0 at init)
+    assert y2.tobytes() == y.tobytes()                       # deterministic, same order
+
+
+def test_matvec_is_run_to_run_deterministic(ctx):
+    rng = np.random.default_rng(5)
+    A = rng.standard_normal((1000, 4096)); v = rng.standard_normal(4096); w = rng.standard_normal(1000)
+    for cfg in (dict(), dict(gemv_variant=2)):
+        outs = [ctx.op_matvec(A, v, w, **cfg) for _ in range(3)]
+        assert all(o[0].tobytes() == outs[0][0].tobytes() and o[1] == outs[0][1] for o in outs)
+
+
+@pytest.mark.parametrize("m", [1, 2, 5, 255, 256, 257, 4096, 100003])
+def test_vector_kernels_keep_reference_rounding_points(ctx, m):
+    rng = np.random.default_rng(m)
+    b = rng.standard_normal(m); Ax = rng.standard_normal(m)
+    r, p, rr = ctx.op_init_residual(b, Ax)                   # parallel_cg.c:284-286
+    assert r.tobytes() == (b - Ax).tobytes() and p.tobytes() == r.tobytes()
+    assert abs(rr - O.vecvec(r, r)) <= 1e-13 * rr
+    x = rng.standard_normal(m); Ap = rng.standard_normal(m)
+    rho, pAp = 3.25, 7.5
+    alpha = rho / pAp
+    x2, r2, rr2 = ctx.op_xr_update(rho, pAp, x, r, p, Ap)    # parallel_cg.c:298-309
+    assert x2.tobytes() == (x + p * alpha).tobytes()         # product rounded, then add: no FMA
+    assert r2.tobytes() == (r - Ap * alpha).tobytes()
+    assert abs(rr2 - O.vecvec(r2, r2)) <= 1e-13 * rr2
+    p2, stopped = ctx.op_p_update(rho, 1.5, EPS, p, r2)      # parallel_cg.c:314-322
+    assert not stopped and p2.tobytes() == (r2 + p * (1.5 / rho)).tobytes()
+    p3, stopped = ctx.op_p_update(rho, 0.9e-12, EPS, p, r2)  # sqrt(beta) < eps: break, p untouched
+    assert stopped and p3.tobytes() == p.tobytes()
+    p4, stopped = ctx.op_p_update(rho, 1.0e-12, EPS, p, r2)  # sqrt(beta) == eps is NOT < eps
+    assert not stopped
+
+
+# ----------------------------------------------------------------- whole solves
+@pytest.mark.parametrize("tag", ["g1", "g2", "g3", "g4"])
+@pytest.mark.parametrize("variant", [1, 2])
+def test_solve_matches_reference_golden(cg, golden, tag, variant):
+    c = golden["cases"][tag]
+    A, b, x0 = case_inputs(c)
+    x, st = cg.conjugrad_host(A, b, x0, gpus=1, gemv_variant=variant)
+    want = unhex(c["x"]["serial_f64"])                       # the REAL reference, float->double build
+    xo, so = O.conjugrad(A, b, x0)
+    assert relerr(x, want) <= RTOL_X
+    assert abs(st["iterations"] - so["iterations"]) <= 1
+    assert st["final_residual"] < EPS
+    # FP32 reference as shipped: loose cross-check
+    assert relerr(x, unhex(c["x"]["serial_f32"])) <= 2e-5
+
+
+def test_known_answers_of_shipped_fixtures(cg, golden):
+    A, b, x0 = case_inputs(golden["cases"]["g1"])
+    x, st = cg.conjugrad_host(A, b, x0)
+    np.testing.assert_allclose(x, [2 / 3, 1 / 3], rtol=1e-14)
+    assert st["break_k"] == 1 and st["iterations"] == 2
+    A, b, x0 = case_inputs(golden["cases"]["g2"])
+    x, st = cg.conjugrad_host(A, b, x0)
+    np.testing.assert_allclose(x, [-1, 1, -1, 1], rtol=1e-12)
+    assert st["break_k"] == 3
+
+
+@pytest.mark.parametrize("n,graph,chunk", [(96, 1, 0), (1000, 1, 2), (1001, 1, 8), (1536, 0, 0), (4096, 1, 0)])
+def test_generated_solve_vs_oracle(ctx, n, graph, chunk):
+    seed = 1234 + n
+    ctx.generate(n, seed)
+    st = ctx.solve(use_graph=graph, check_every=chunk)
+    x = ctx.read_x()
+    xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n))
+    assert relerr(x, xo) <= RTOL_X
+    assert abs(st["iterations"] - so["iterations"]) <= 1 and st["break_k"] == st["iterations"] - 1
+    assert st["final_residual"] < EPS
+    assert abs(st["rsold0"] - so["rsold0"]) <= 1e-12 * so["rsold0"]
+
+
+def test_nonzero_initial_guess_and_restart(ctx):
+    n, seed = 768, 9
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    x0 = np.random.default_rng(1).standard_normal(n)
+    ctx.load_host(A, b, x0)
+    st = ctx.solve()
+    x = ctx.read_x()
+    xo, so = O.conjugrad(A, b, x0)
+    assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    # the solution fed back as initial guess (the reference's restart input): already converged
+    ctx.set_x0(x)
+    st2 = ctx.solve()
+    xo2, so2 = O.conjugrad(A, b, x)
+    assert st2["iterations"] <= 2 and abs(st2["iterations"] - so2["iterations"]) <= 1
+    assert relerr(ctx.read_x(), xo2) <= RTOL_X
+
+
+def test_fixed_iteration_mode_matches_oracle_iterates(ctx):
+    # bench mode: stop rule evaluated, not acted on; compare at equal iteration counts
+    n, seed, K = 512, 77, 3
+    ctx.generate(n, seed)
+    st = ctx.solve(ignore_stop=1, max_iter=K)
+    xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n), max_iter=K, ignore_stop=True)
+    assert st["iterations"] == K == so["iterations"] and st["break_k"] == -1
+    assert relerr(ctx.read_x(), xo) <= RTOL_X
+    assert abs(st["final_beta"] - so["final_beta"]) <= 1e-6 * so["final_beta"] + 1e-30
+
+
+def test_max_iter_bound_and_odd_counts(ctx):
+    n, seed = 400, 3
+    ctx.generate(n, seed)
+    for K in (1, 2, 3):
+        st = ctx.solve(max_iter=K, eps=1e-300)
+        xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n), eps=1e-300, max_iter=K)
+        assert st["iterations"] == K and st["break_k"] == -1
+        assert relerr(ctx.read_x(), xo) <= RTOL_X
+        ctx.set_x0(np.zeros(n))
+
+
+def test_exact_initial_guess_mirrors_reference_nan_behaviour(ctx):
+    # x0 already exact: rho = 0 -> alpha = 0/0; the reference has no guard and
+    # iterates NaNs to the loop bound; mirrored, bounded here.
+    A = np.array([[2.0, 0.0], [0.0, 2.0]]); b = np.array([2.0, 4.0]); x0 = np.array([1.0, 2.0])
+    ctx.load_host(A, b, x0)
+    st = ctx.solve()
+    xo, so = O.conjugrad(A, b, x0)
+    assert st["iterations"] == so["iterations"] == 2 and st["break_k"] == -1
+    assert np.isnan(ctx.read_x()).all() and np.isnan(xo).all()
+
+
+def test_errors(cg, ctx):
+    with pytest.raises(cg.CgbError) as e:
+        cg.conjugrad_host(np.eye(6), np.ones(6), np.zeros(6), gpus=4)
+    assert e.value.code in (-4, -2)          # "6 is not divisible by 4" (or < 4 GPUs on the box)
+    with cg.Context(0) as c2:
+        with pytest.raises(cg.CgbError) as e:
+            c2.solve()
+        assert e.value.code == -6
+
+
+# ----------------------------------------------------------------- full-size properties
+def test_full_size_gemv_properties(ctx):
+    """n = 16384 (config 3): linearity and symmetry checks that need no oracle pass,
+    plus an oracle check on a sample of rows."""
+    n, seed = 16384, 20170209
+    ctx.generate(n, seed)
+    st = ctx.solve()
+    x = ctx.read_x()
+    assert st["final_residual"] < EPS and 2 <= st["iterations"] <= 8
+    # residual recomputed on the CPU for sampled rows: b_i - A_i x small
+    rows = [0, 1, 777, 8191, 16383]
+    for i in rows:
+        Ai = O.gen_A(n, seed, 0, i, 1)[0]
+        assert abs(O.gen_b(n, seed, 0, i, 1)[0] - Ai @ x) < 1e-6
+    # oracle iterate at the same iteration count on this size takes ~1 s per matVec
+    xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n))
+    assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
