@@ -34,6 +34,7 @@ typedef struct {
     double  rsold0;       /* initial r.r                                             */
     double  seconds;      /* wall time of the solver region, where the reference     */
                           /* times it (serialConjugate.c:208,249; parallel_cg.c:278-279,328-329) */
+    double  loop_seconds; /* the iteration loop alone (after the initial A*x0 / r.r) */
 } orc_stats;
 
 static void *orc_alloc(size_t bytes)
@@ -148,6 +149,7 @@ static void *team_rank_main(void *arg)
     orc_residual_f64(tm->ploc + o, tm->b + o, tm->Ap + o, m);
     rsold = team_allreduce(tm, g, orc_vecvec_f64(tm->r + o, tm->r + o, m));
     double rs0 = rsold;
+    const double tl0 = orc_now();
     for (k = 0; k < tm->max_iter; ++k) {
         memcpy(tm->pall + o, tm->ploc + o, (size_t)m * sizeof(double));
         pthread_barrier_wait(&tm->bar);                      /* allgather done */
@@ -173,6 +175,7 @@ static void *team_rank_main(void *arg)
     pthread_barrier_wait(&tm->bar);
     if (g == 0) {
         tm->st.seconds = orc_now() - t0;
+        tm->st.loop_seconds = orc_now() - tl0;
         tm->st.iterations = done_iters;
         tm->st.break_k = break_k;
         tm->st.first_hit_k = first_hit;

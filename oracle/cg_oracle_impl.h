@@ -95,6 +95,7 @@ void ORC_FN(orc_conjugrad)(const REAL *A, const REAL *b, REAL *x, int64_t n,
     ORC_FN(orc_residual)(p, b, Ap, n);
     rsold = ORC_FN(orc_vecvec)(r, r, n);
     if (st) st->rsold0 = (double)rsold;
+    const double tl0 = orc_now();
     for (k = 0; k < max_iter; ++k) {
         ORC_FN(orc_matvec)(Ap, A, p, n, n);
         alpha = ORC_FN(orc_vecvec)(p, Ap, n);
@@ -115,6 +116,7 @@ void ORC_FN(orc_conjugrad)(const REAL *A, const REAL *b, REAL *x, int64_t n,
     }
     if (st) {
         st->seconds = orc_now() - t0;
+        st->loop_seconds = orc_now() - tl0;
         st->iterations = done_iters;
         st->break_k = break_k;
         st->first_hit_k = first_hit;
@@ -156,6 +158,7 @@ void ORC_FN(orc_conjugrad_spmd)(const REAL *A, const REAL *b, REAL *x, int64_t n
         rsold = (g == 0) ? part : rsold + part;
     }
     if (st) st->rsold0 = (double)rsold;
+    const double tl0 = orc_now();
     for (k = 0; k < max_iter; ++k) {
         memcpy(pall, ploc, (size_t)n * sizeof(REAL));          /* allgather */
         alpha = (REAL)0.0;
@@ -187,6 +190,7 @@ void ORC_FN(orc_conjugrad_spmd)(const REAL *A, const REAL *b, REAL *x, int64_t n
     }
     if (st) {
         st->seconds = orc_now() - t0;
+        st->loop_seconds = orc_now() - tl0;
         st->iterations = done_iters;
         st->break_k = break_k;
         st->first_hit_k = first_hit;

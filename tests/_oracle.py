@@ -16,7 +16,8 @@ GEN_ROUND4 = 1
 class OrcStats(C.Structure):
     _fields_ = [("iterations", C.c_int64), ("break_k", C.c_int64),
                 ("first_hit_k", C.c_int64), ("final_beta", C.c_double),
-                ("rsold0", C.c_double), ("seconds", C.c_double)]
+                ("rsold0", C.c_double), ("seconds", C.c_double),
+                ("loop_seconds", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
