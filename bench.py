@@ -74,7 +74,7 @@ def gemv_bytes(m, n):
 
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
@@ -84,10 +84,23 @@ class ClockSampler:
         if shutil.which("nvidia-smi"):
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=self.f, stderr=subprocess.DEVNULL)
+            t_end = time.time() + 10.0                  # nvidia-smi takes ~1 s to deliver its first sample
+            while time.time() < t_end and os.path.getsize(self.path) == 0:
+                time.sleep(0.05)
+                self.f.flush()
 
-    def stop(self):
+    @staticmethod
+    def _ts(s):
+        import datetime
+        return datetime.datetime.strptime(s.strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+
+    def mark(self):
+        """Wall-clock mark; samples between two marks are the ones taken during the timed region."""
+        return time.time()
+
+    def stop(self, t_lo=None, t_hi=None):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if not self.proc:
             return out
@@ -101,13 +114,16 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in open(self.path):
             parts = [t.strip() for t in line.split(",")]
-            if len(parts) < 7:
+            if len(parts) < 8:
                 continue
             try:
-                sm.append(float(parts[0])); mx.append(float(parts[1]))
+                ts = self._ts(parts[0])
+                if t_lo is not None and not (t_lo - 0.03 <= ts <= t_hi + 0.03):
+                    continue
+                sm.append(float(parts[1])); mx.append(float(parts[2]))
             except ValueError:
                 continue
-            for nm, val in zip(names, parts[3:7]):
+            for nm, val in zip(names, parts[4:8]):
                 if val.lower().startswith("active"):
                     reasons.add(nm)
         if sm:
@@ -223,11 +239,13 @@ def b200_arm(args):
         ctx.solve(ignore_stop=1, max_iter=W, time_gemv=1, **gopts)
         ctx.set_x0(np.zeros(n))
     # ---- timed region: exactly K iterations, device-resident, event pair around every GEMV
-    barrier()
     sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    t_lo = time.time()
     st = ctx.solve(ignore_stop=1, max_iter=K, time_gemv=1, **gopts)
     barrier()
-    clocks = sampler.stop() if sampler else None
+    t_hi = time.time()
+    clocks = sampler.stop(t_lo, t_hi) if sampler else None
     loop_ms = max_over_ranks(st["loop_ms"])
     gemv_ms = max_over_ranks(st["gemv_ms_avg"])
     value = K / (loop_ms * 1e-3)
