@@ -93,6 +93,8 @@ static int find_dimensions(const cli_t *c, int64_t dims[4], int *inferred)
 int main(int argc, char **argv)
 {
     const clock_t c0 = clock();                      /* parallel_cg.c:75 */
+    /* stdout carries the reference's lines only: NCCL's banner (NCCL_DEBUG=VERSION/INFO) goes to stderr */
+    setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0);
     cli_t cli;
     int pc = parse_cli(argc, argv, &cli);
     if (pc == -2) {

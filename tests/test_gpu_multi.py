@@ -1,0 +1,100 @@
+"""Multi-GPU parity (row-sharded A, NCCL all-gather of p + all-reduce of the dot scalars,
+replacing parallel_cg.c:287-313).  Skipped on boxes with fewer GPUs than the case needs."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import _oracle as O
+from conftest import unhex
+
+pytestmark = pytest.mark.gpu
+EPS, RTOL_X = 1.0e-6, 1.0e-10
+
+
+@pytest.fixture(scope="module")
+def cg():
+    import conjugate_gradient_b200 as m
+    return m
+
+
+def need(cg, g):
+    if cg.device_count() < g:
+        pytest.skip(f"needs {g} GPUs")
+
+
+def relerr(x, ref):
+    return np.linalg.norm(x - ref) / np.linalg.norm(ref)
+
+
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+@pytest.mark.parametrize("tag", ["g2", "g3", "g4"])
+def test_sharded_solve_matches_reference_mpi_golden(cg, golden, gpus, tag):
+    need(cg, gpus)
+    c = golden["cases"][tag]
+    n = c["n"]
+    if n % gpus or gpus not in c["ranks"]:
+        pytest.skip("rank count not in the golden set")
+    if "A" in c:
+        A, b, x0 = unhex(c["A"]).reshape(n, n), unhex(c["b"]), unhex(c["x0"])
+    else:
+        A, b, x0 = O.gen_A(n, c["seed"]), O.gen_b(n, c["seed"]), np.zeros(n)
+    x, st = cg.conjugrad_host(A, b, x0, gpus=gpus)
+    want = unhex(c["x"][f"spmd{gpus}_f64"])       # the REAL parallel_cg.c (double build) over the MPI shim
+    xo, so = O.conjugrad(A, b, x0, ranks=gpus)
+    assert relerr(x, want) <= RTOL_X
+    assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
+    assert st["ranks"] == gpus and st["m"] == n // gpus
+
+
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_generated_sharded_solve(cg, gpus):
+    need(cg, gpus)
+    n, seed = 4096, 31
+    x, st = cg.solve_generated(n, seed, gpus=gpus)
+    xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n), ranks=gpus)
+    assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    x1, st1 = cg.solve_generated(n, seed, gpus=1)
+    assert relerr(x, x1) <= RTOL_X
+    # fixed-iteration mode across ranks: every rank stops at the same count
+    x, st = cg.solve_generated(n, seed, gpus=gpus, ignore_stop=1, max_iter=7)
+    assert st["iterations"] == 7
+
+
+def test_not_divisible(cg):
+    need(cg, 2)
+    with pytest.raises(cg.CgbError) as e:
+        cg.conjugrad_host(np.eye(5), np.ones(5), np.zeros(5), gpus=2)
+    assert e.value.code == -4 and "5 is not divisible by 2" in str(e.value)    # parallel_cg.c:88
+
+
+def test_cli_two_gpus(cg, golden_dir):
+    need(cg, 2)
+    from conjugate_gradient_b200 import _binding as B
+    g = golden_dir
+    r = subprocess.run([B.CLI_PATH, f"{g}/g2_matrixA.txt", f"{g}/g2_vectorb.txt", f"{g}/g2_x0.txt",
+                        "--dims", f"{g}/g2_dimensions.txt", "--gpus", "2", "--print-x"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.splitlines()
+    assert lines[0] == "Computing cg of matrix size : 16"
+    xs = [float(l) for l in lines[1:5]]
+    np.testing.assert_allclose(xs, [-1, 1, -1, 1], atol=1e-6)
+    assert lines[5].startswith("cg method execution time in seconds: ")
+    assert lines[6].startswith("collective data distribution time in seconds: ")
+    assert lines[7].startswith("clock execution time in seconds: ")
+
+
+def test_torchrun_bench_two_ranks(cg):
+    need(cg, 2)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(root, "bench.py"),
+                        "--gpus", "2", "--steps", "4", "--warmup", "3", "--n", "8192"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    import json
+    line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["n_gpus"] == 2 and line["value"] > 0 and line["e2e"]["value"] > 0

@@ -231,3 +231,33 @@ def test_full_size_gemv_properties(ctx):
     # oracle iterate at the same iteration count on this size takes ~1 s per matVec
     xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n))
     assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+
+
+def test_cli_on_shipped_fixture(cg, golden_dir):
+    """The reference CLI surface: prog A.txt b.txt x0.txt + dimensions.txt; stdout lines of
+    serialConjugate.c:58,249-251 and printer()'s format behind --print-x."""
+    import subprocess
+    from conjugate_gradient_b200 import _binding as B
+    g = golden_dir
+    r = subprocess.run([B.CLI_PATH, f"{g}/g1_matrixA.txt", f"{g}/g1_vectorb.txt", f"{g}/g1_x0.txt",
+                        "--dims", f"{g}/g1_dimensions.txt", "--print-x", "--stats"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.splitlines()
+    assert lines[0] == "Computing cg of matrix size : 4"
+    assert lines[1] == "0.666667  " and lines[2] == "0.333333  "
+    assert lines[3].startswith("average clock execution time in seconds: ")
+    assert "iterations: 2" in lines[4]
+
+
+def test_cli_generated_and_restart_file(cg, tmp_path):
+    import subprocess
+    from conjugate_gradient_b200 import _binding as B
+    xf = tmp_path / "x.txt"
+    r = subprocess.run([B.CLI_PATH, "--gen", "1024", "--seed", "5", "--write-x", str(xf), "--stats"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    x = cg.read_values(str(xf), 1024)
+    xo, so = O.conjugrad(O.gen_A(1024, 5), O.gen_b(1024, 5), np.zeros(1024))
+    assert relerr(x, xo) <= RTOL_X
+    assert f"iterations: {so['iterations']}" in r.stdout
