@@ -652,6 +652,14 @@ extern "C" int cgk_gemv_make_plan(cgk_gemv_plan *plan, int64_t m, int64_t n, con
     if (vec == 1) {
         plan->rows_per_cta = 4; plan->unroll = 1; plan->threads = 128; plan->vec = 1;
     } else {
+        /* defaults from the B200 sweep (tools/tune_gemv.py, profiles/r01_tune_gemv.md): every
+         * reasonable shape sits within ~1 % of the same plateau (7.4 TB/s at n = 65536); the
+         * picks below are the fastest measured per size class */
+        if (rows == 0 && unroll == 0 && threads == 0) {
+            if (n >= 32768 && m >= 8192 && vec == 4) { rows = 8; unroll = 2; threads = 512; }
+            else if (n >= 8192) { rows = 2; unroll = 1; threads = 256; }
+            else { rows = 4; unroll = 1; threads = 128; }
+        }
         if (rows == 0) rows = 4;
         if (threads == 0) threads = (n >= 8192) ? 256 : 128;
         if (unroll == 0) unroll = 2;
