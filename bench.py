@@ -49,7 +49,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=int(os.environ.get("CGB_BENCH_N", 65536)))
+    ap.add_argument("--matrix-n", dest="n", type=int, default=int(os.environ.get("CGB_BENCH_N", 65536)))
     ap.add_argument("--gemv", type=int, default=int(os.environ.get("CGB_BENCH_GEMV", 0)))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -92,7 +92,7 @@ def test_torchrun_bench_two_ranks(cg):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                         "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(root, "bench.py"),
-                        "--gpus", "2", "--steps", "4", "--warmup", "3", "--n", "8192"],
+                        "--gpus", "2", "--steps", "4", "--warmup", "3", "--matrix-n", "8192"],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     import json
