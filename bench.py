@@ -51,6 +51,11 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--matrix-n", dest="n", type=int, default=int(os.environ.get("CGB_BENCH_N", 65536)))
     ap.add_argument("--gemv", type=int, default=int(os.environ.get("CGB_BENCH_GEMV", 0)))
+    ap.add_argument("--comm", default=os.environ.get("CGB_BENCH_COMM", "auto"), choices=["auto", "nccl", "peer"],
+                    help="N > 1: per-iteration exchange (auto = fused peer-memory pushes when the GPUs map each other)")
+    ap.add_argument("--rows", type=int, default=0, help="GEMV rows per CTA (0 = library default)")
+    ap.add_argument("--unroll", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
@@ -232,7 +237,8 @@ def b200_arm(args):
     ctx = cg.Context(device=local, rank=rank, ranks=world, uid=uid)
     info = ctx.device_info()
     ctx.generate(n, SEED)                                   # each GPU writes its own row block in HBM
-    gopts = dict(gemv_variant=args.gemv)
+    gopts = dict(gemv_variant=args.gemv, comm={"auto": 0, "nccl": 1, "peer": 2}[args.comm],
+                 gemv_rows=args.rows, gemv_unroll=args.unroll, gemv_threads=args.threads)
 
     # ---- warm-up: W untimed iterations (also builds plans, first-touches everything)
     if W > 0:
@@ -270,6 +276,8 @@ def b200_arm(args):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"seeded synthetic SPD n={n} FP64, fixed-iteration CG (configs[3])", "n": n,
                    "seed": SEED, "rows_per_gpu": m, "parallelism": f"row-block x{world}" if world > 1 else "single GPU",
+                   "exchange": {0: "none (one rank)", 1: "nccl all-gather + 2 all-reduce per iteration",
+                                2: "fused peer-memory pushes over NVLink inside the solver kernels"}[st["comm"]],
                    "l2": f"A block is {8.0 * m * n / 1e9:.2f} GB per GPU, far larger than the 126 MB L2: no flush needed",
                    "gemv_kernel": {k: st[k] for k in ("gemv_variant", "gemv_rows", "gemv_unroll", "gemv_threads",
                                                       "gemv_vec", "gemv_stages", "gemv_tile_cols", "gemv_grid")}},

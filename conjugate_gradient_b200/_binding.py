@@ -15,6 +15,7 @@ HEADER = os.path.join(ROOT, "include", "cgb200.h")
 CGB_EPSILON = 1.0e-6          # serialConjugate.c:28
 GEN_ROUND4 = 1
 GEMV_AUTO, GEMV_LDG, GEMV_BULK = 0, 1, 2
+COMM_AUTO, COMM_NCCL, COMM_PEER = 0, 1, 2
 
 
 class CgbError(RuntimeError):
@@ -28,7 +29,7 @@ class Options(C.Structure):
                 ("use_graph", C.c_int), ("check_every", C.c_int), ("time_gemv", C.c_int),
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
-                ("gemv_tile_cols", C.c_int), ("reserved", C.c_int * 4)]
+                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("reserved", C.c_int * 3)]
 
 
 class Stats(C.Structure):
@@ -42,7 +43,7 @@ class Stats(C.Structure):
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
                 ("gemv_tile_cols", C.c_int), ("gemv_grid", C.c_int), ("graph_chunk", C.c_int),
-                ("reserved", C.c_int * 3)]
+                ("comm", C.c_int), ("reserved", C.c_int * 2)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

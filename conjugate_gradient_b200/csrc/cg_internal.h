@@ -12,6 +12,8 @@ struct cgb_graph_key {
     int ignore_stop, chunk;
     cgk_gemv_plan plan;
     const void *A;
+    const void *win;        /* peer window the captured kernels point into */
+    int comm, pad_;
 };
 
 struct cgb_ctx {
@@ -26,7 +28,8 @@ struct cgb_ctx {
     int64_t n, m, cap_n, cap_m;
     double *A;              /* m x n row block, row-major                       */
     double *b, *r, *Ap;     /* m                                                */
-    double *p_full;         /* n: gathered direction; own slice at rank*m       */
+    double *p_full;         /* n: gathered direction; own slice at rank*m; with ranks > 1 it
+                             * lives inside `win`, the window the peers map       */
     double *x_full;         /* n: x0 on entry; own slice updated; gathered at end */
     double *partials_gemv;  /* one per gemv CTA                                 */
     double *partials_vec;   /* one per vector-kernel CTA                        */
@@ -39,6 +42,17 @@ struct cgb_ctx {
     struct cgb_graph_key graph_key;
     int64_t launches;
     double h2d_seconds, d2h_seconds;
+    /* peer-memory exchange (ranks > 1): this rank's window [cgk_mailbox | p_full], the peers'
+     * windows as mapped here (same-process peer access or CUDA IPC), and the table the kernels get */
+    void *win;
+    size_t win_bytes;
+    void *peer_win[CGK_MAX_RANKS];
+    int peer_ipc[CGK_MAX_RANKS];      /* 1: opened with cudaIpcOpenMemHandle (close it)  */
+    int peer_ok;                      /* every rank mapped every window                  */
+    cgk_peers peers;
+    unsigned int gen;                 /* solve generation, in lockstep on all ranks      */
+    int comm_mode;                    /* CGB_COMM_* in use by the current / last solve   */
+    char peer_why[160];               /* why peer_ok == 0                                */
 };
 
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);

@@ -3,8 +3,13 @@
 #include "cg_io.h"
 #include "../../include/cgb200.h"
 #include <errno.h>
+#include <fcntl.h>
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 static char *slurp(const char *path, size_t *len)
 {
@@ -64,26 +69,224 @@ static int64_t parse_all(const char *buf, size_t len, double *dst, int64_t cap, 
     return k;
 }
 
+/* ---- parallel ingest (text parsing is >95 % of the reference's wall time,
+ * fscanf("%f%*c") at ~4 M values/s, serialConjugate.c:92-98).  The file is cut at separator
+ * characters into one span per thread; every thread converts its tokens with Clinger's exact
+ * fast path -- an integer mantissa below 2^53 times or divided by a power of ten up to 1e22
+ * is ONE correctly rounded IEEE operation, hence the same double strtod returns -- and hands
+ * anything else (more than 15 digits, large exponents, inf/nan, hex) to strtod itself.  Files
+ * whose tokens are not plain numbers fall back to the sequential strtod loop above, so the
+ * accepted grammar and the error behaviour are exactly those of parse_all(). */
+static const double k_pow10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
+                                   1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+
+static inline int is_sep_byte(unsigned char ch)
+{
+    return ch == ' ' || ch == '\t' || ch == '\n' || ch == '\r' || ch == ',' || ch == ';' || ch == '\f' || ch == '\v';
+}
+
+/* One token [p, e): returns 1 and *out if it is a plain decimal number, else 0. */
+static int token_to_double(const char *p, const char *e, double *out)
+{
+    const char *s = p;
+    int neg = 0;
+    if (s < e && (*s == '+' || *s == '-')) { neg = (*s == '-'); ++s; }
+    uint64_t w = 0;
+    int digits = 0, sig = 0, exp10 = 0, seen_point = 0;
+    for (; s < e; ++s) {
+        const unsigned d = (unsigned)(*s - '0');
+        if (d <= 9u) {
+            ++digits;
+            if (w != 0 || d != 0) {
+                if (++sig > 19) goto slow;
+                w = w * 10u + d;
+            }
+            if (seen_point) --exp10;
+        } else if (*s == '.' && !seen_point) seen_point = 1;
+        else break;
+    }
+    if (digits == 0) goto slow;
+    if (s < e && (*s == 'e' || *s == 'E')) {
+        const char *t = s + 1;
+        int eneg = 0, ev = 0, ed = 0;
+        if (t < e && (*t == '+' || *t == '-')) { eneg = (*t == '-'); ++t; }
+        for (; t < e && (unsigned)(*t - '0') <= 9u; ++t) { if (ev < 10000) ev = ev * 10 + (*t - '0'); ++ed; }
+        if (ed == 0) goto slow;
+        exp10 += eneg ? -ev : ev;
+        s = t;
+    }
+    if (s != e) goto slow;                                 /* trailing characters: not a plain number */
+    if (w == 0) { *out = neg ? -0.0 : 0.0; return 1; }
+    if (sig <= 15 && exp10 >= -22 && exp10 <= 22) {
+        double v = (double)w;                              /* exact: w < 10^15 < 2^53 */
+        v = exp10 < 0 ? v / k_pow10[-exp10] : v * k_pow10[exp10];
+        *out = neg ? -v : v;
+        return 1;
+    }
+slow: {
+        char tmp[80];
+        const size_t len = (size_t)(e - p);
+        if (len == 0 || len >= sizeof tmp) return 0;
+        memcpy(tmp, p, len);
+        tmp[len] = '\0';
+        char *q;
+        const double v = strtod(tmp, &q);
+        if (q != tmp + len) return 0;                      /* strtod would stop inside the token */
+        *out = v;
+        return 1;
+    }
+}
+
+typedef struct {
+    const char *beg, *end;
+    double *dst;              /* NULL: count only */
+    int64_t count, offset, cap;
+    int irregular;
+} span_job;
+
+static void *span_count(void *arg)
+{
+    span_job *j = arg;
+    int64_t k = 0;
+    int in_tok = 0;
+    for (const char *p = j->beg; p < j->end; ++p) {
+        const unsigned char ch = (unsigned char)*p;
+        const int sep = is_sep_byte(ch);
+        if (ch >= 0x80) j->irregular = 1;                  /* BOM or junk: sequential path decides */
+        if (!sep && !in_tok) ++k;
+        in_tok = !sep;
+    }
+    j->count = k;
+    return NULL;
+}
+
+static void *span_parse(void *arg)
+{
+    span_job *j = arg;
+    const char *p = j->beg;
+    int64_t k = j->offset;
+    while (p < j->end) {
+        while (p < j->end && is_sep_byte((unsigned char)*p)) ++p;
+        if (p >= j->end) break;
+        const char *e = p;
+        while (e < j->end && !is_sep_byte((unsigned char)*e)) ++e;
+        if (k >= j->cap) break;                            /* caller wanted only the first `cap` values */
+        if (!token_to_double(p, e, &j->dst[k])) { j->irregular = 1; return NULL; }
+        ++k;
+        p = e;
+    }
+    return NULL;
+}
+
+#define IO_MAX_THREADS 64
+static int io_threads(size_t len)
+{
+    long nc = sysconf(_SC_NPROCESSORS_ONLN);
+    const char *e = getenv("CGB_IO_THREADS");
+    if (e && *e) nc = atol(e);
+    if (nc < 1) nc = 1;
+    if (nc > IO_MAX_THREADS) nc = IO_MAX_THREADS;
+    size_t by_size = len / ((size_t)1 << 20) + 1;          /* >= 1 MiB of text per thread */
+    return (int)((size_t)nc < by_size ? (size_t)nc : by_size);
+}
+
+/* Returns the number of values, or -1 when the file needs the sequential path. */
+static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t cap)
+{
+    const int T = io_threads(len);
+    span_job job[IO_MAX_THREADS];
+    pthread_t th[IO_MAX_THREADS];
+    const char *end = buf + len, *cut = buf;
+    for (int t = 0; t < T; ++t) {
+        const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
+        if (nxt < cut) nxt = cut;
+        while (nxt < end && !is_sep_byte((unsigned char)*nxt)) ++nxt;     /* cut only at a separator */
+        memset(&job[t], 0, sizeof job[t]);
+        job[t].beg = cut; job[t].end = nxt;
+        cut = nxt;
+    }
+    for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, span_count, &job[t]);
+    span_count(&job[0]);
+    for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+    int64_t total = 0;
+    for (int t = 0; t < T; ++t) {
+        if (job[t].irregular) return -1;
+        job[t].offset = total;
+        total += job[t].count;
+    }
+    if (!dst) return total;
+    for (int t = 0; t < T; ++t) { job[t].dst = dst; job[t].cap = cap; }
+    for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, span_parse, &job[t]);
+    span_parse(&job[0]);
+    for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+    for (int t = 0; t < T; ++t)
+        if (job[t].irregular) return -1;
+    return total;
+}
+
+/* Whole file, read-only: mmap when possible (no copy of a multi-GB text), else slurp. */
+typedef struct { char *p; size_t len; int mapped; } text_t;
+
+static int text_open(const char *path, text_t *t)
+{
+    memset(t, 0, sizeof *t);
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) return -1;
+    struct stat sb;
+    if (fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0) {
+        void *m = mmap(NULL, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (m != MAP_FAILED) {
+            (void)madvise(m, (size_t)sb.st_size, MADV_SEQUENTIAL);
+            t->p = m; t->len = (size_t)sb.st_size; t->mapped = 1;
+            close(fd);
+            return 0;
+        }
+    }
+    close(fd);
+    t->p = slurp(path, &t->len);
+    return t->p ? 0 : -1;
+}
+
+static void text_close(text_t *t)
+{
+    if (t->mapped) munmap(t->p, t->len); else free(t->p);
+    t->p = NULL;
+}
+
 int cgb_read_values(const char *path, double *dst, int64_t count, int64_t *got)
 {
-    size_t len = 0;
-    char *buf = slurp(path, &len);
+    text_t tx;
     if (got) *got = 0;
-    if (!buf) return CGB_ERR_IO;
+    if (text_open(path, &tx) != 0) return CGB_ERR_IO;
+    int64_t k = parse_parallel(tx.p, tx.len, dst, count);
     int bad = 0;
-    int64_t k = parse_all(buf, len, dst, count, &bad);
-    free(buf);
+    if (k < 0) {                                           /* irregular tokens: exact sequential semantics */
+        text_close(&tx);
+        size_t len = 0;
+        char *buf = slurp(path, &len);
+        if (!buf) return CGB_ERR_IO;
+        k = parse_all(buf, len, dst, count, &bad);
+        free(buf);
+    } else {
+        text_close(&tx);
+        if (k > count) k = count;                          /* parse_all stops after `count` values too */
+    }
     if (got) *got = k;
     return (k == count && !bad) ? CGB_OK : CGB_ERR_IO;
 }
 
 int64_t cgb_count_values(const char *path)
 {
+    text_t tx;
+    if (text_open(path, &tx) != 0) return -1;
+    int64_t k = parse_parallel(tx.p, tx.len, NULL, 0);
+    text_close(&tx);
+    if (k >= 0) return k;
     size_t len = 0;
     char *buf = slurp(path, &len);
     if (!buf) return -1;
     int bad = 0;
-    int64_t k = parse_all(buf, len, NULL, 0, &bad);
+    k = parse_all(buf, len, NULL, 0, &bad);
     free(buf);
     return bad ? -1 : k;
 }
@@ -109,13 +312,54 @@ void cgb_print_vector(FILE *out, const double *v, int64_t rows, int64_t cols)
         }
 }
 
+/* generateSPDmatrix.m:28-43 writes one "%.4f\n" per value with fprintf; the same bytes are
+ * produced here by one formatter thread per slice and written in order. */
+typedef struct { const double *v; int64_t count; int decimals; char *buf; size_t len; int fail; } fmt_job;
+
+static void *fmt_main(void *arg)
+{
+    fmt_job *j = arg;
+    size_t cap = (size_t)j->count * 28 + 64, n = 0;
+    j->buf = malloc(cap);
+    if (!j->buf) { j->fail = 1; return NULL; }
+    for (int64_t i = 0; i < j->count; ++i) {
+        if (cap - n < 400) {                               /* "%.4f" of 1e308 is 314 characters */
+            cap = cap * 2 + 512;
+            char *nb = realloc(j->buf, cap);
+            if (!nb) { j->fail = 1; return NULL; }
+            j->buf = nb;
+        }
+        n += (size_t)(j->decimals >= 0 ? snprintf(j->buf + n, cap - n, "%.*f\n", j->decimals, j->v[i])
+                                       : snprintf(j->buf + n, cap - n, "%.17g\n", j->v[i]));
+    }
+    j->len = n;
+    return NULL;
+}
+
 int cgb_write_values(const char *path, const double *v, int64_t count, int fmt_decimals)
 {
     FILE *f = fopen(path, "w");
     if (!f) return CGB_ERR_IO;
-    for (int64_t i = 0; i < count; ++i) {
-        if (fmt_decimals >= 0) fprintf(f, "%.*f\n", fmt_decimals, v[i]);
-        else fprintf(f, "%.17g\n", v[i]);
+    int rc = CGB_OK;
+    const int64_t slab = (int64_t)1 << 22;                 /* values per round: bounds the buffers */
+    for (int64_t base = 0; base < count && rc == CGB_OK; base += slab) {
+        const int64_t cnt = count - base < slab ? count - base : slab;
+        int T = io_threads((size_t)cnt * 16);
+        fmt_job job[IO_MAX_THREADS];
+        pthread_t th[IO_MAX_THREADS];
+        for (int t = 0; t < T; ++t) {
+            const int64_t lo = cnt * t / T, hi = cnt * (t + 1) / T;
+            memset(&job[t], 0, sizeof job[t]);
+            job[t].v = v + base + lo; job[t].count = hi - lo; job[t].decimals = fmt_decimals;
+        }
+        for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, fmt_main, &job[t]);
+        fmt_main(&job[0]);
+        for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+        for (int t = 0; t < T; ++t) {
+            if (job[t].fail || (job[t].len && fwrite(job[t].buf, 1, job[t].len, f) != job[t].len)) rc = CGB_ERR_IO;
+            free(job[t].buf);
+        }
     }
-    return fclose(f) == 0 ? CGB_OK : CGB_ERR_IO;
+    if (fclose(f) != 0) rc = CGB_ERR_IO;
+    return rc;
 }

@@ -28,6 +28,9 @@ template <> struct Ld<1> {
     static __device__ __forceinline__ void keep(const double *p, double (&o)[1]) {
         o[0] = __ldg(p);
     }
+    static __device__ __forceinline__ void coherent(const double *p, double (&o)[1]) {
+        asm volatile("ld.global.f64 %0, [%1];" : "=d"(o[0]) : "l"(p) : "memory");
+    }
 };
 template <> struct Ld<2> {
     static __device__ __forceinline__ void stream(const double *p, double (&o)[2]) {
@@ -35,6 +38,9 @@ template <> struct Ld<2> {
     }
     static __device__ __forceinline__ void keep(const double *p, double (&o)[2]) {
         asm("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p));
+    }
+    static __device__ __forceinline__ void coherent(const double *p, double (&o)[2]) {
+        asm volatile("ld.global.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p) : "memory");
     }
 };
 template <> struct Ld<4> {      /* 256-bit LDG: new on sm_100 */
@@ -49,6 +55,15 @@ template <> struct Ld<4> {      /* 256-bit LDG: new on sm_100 */
         unsigned long long a, b, c, d;
         asm("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];"
             : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+        o[0] = __longlong_as_double(a); o[1] = __longlong_as_double(b);
+        o[2] = __longlong_as_double(c); o[3] = __longlong_as_double(d);
+    }
+    /* the direction vector while peers are still writing other parts of it: an ordinary
+     * (coherent) load, ordered after the acquire that observed the peer's flag */
+    static __device__ __forceinline__ void coherent(const double *p, double (&o)[4]) {
+        unsigned long long a, b, c, d;
+        asm volatile("ld.global.v4.b64 {%0,%1,%2,%3}, [%4];"
+                     : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p) : "memory");
         o[0] = __longlong_as_double(a); o[1] = __longlong_as_double(b);
         o[2] = __longlong_as_double(c); o[3] = __longlong_as_double(d);
     }
@@ -95,6 +110,151 @@ __device__ __forceinline__ void cta_partials_finish(double mine, double *partial
     }
 }
 
+/* ------------------------------------------------------------------ peer exchange */
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns(void)
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+/* tag of exchange event e of solve generation gen (never 0 for gen & 0x3ff != 0) */
+__device__ __forceinline__ unsigned int cgk_tag(unsigned int gen, unsigned int e)
+{
+    return ((gen & 0x3ffu) << 22) | (e & 0x3fffffu);
+}
+/* Called every 1024 failed polls: gives up once any waiter has given up or the peer has been
+ * silent for CGK_SPIN_TIMEOUT_NS, so a dead rank becomes an error code instead of a hung GPU. */
+__device__ __noinline__ bool spin_give_up(unsigned long long *t0, cgk_scalars *sc)
+{
+    if (*(volatile int *)&sc->comm_error) return true;
+    const unsigned long long now = global_ns();
+    if (*t0 == 0ull) { *t0 = now; return false; }
+    if (now - *t0 > CGK_SPIN_TIMEOUT_NS) {
+        *(volatile int *)&sc->comm_error = 1;
+        __threadfence();
+        return true;
+    }
+    return false;
+}
+/* LL-style scalar: two 8-byte words, each {32 bits of the double | tag << 32}; 8-byte stores
+ * are single NVLink writes, so a reader that sees the tag in both words has the value. */
+__device__ __forceinline__ void ll_send(unsigned long long *slot, double v, unsigned int tag)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    const unsigned long long t = (unsigned long long)tag << 32;
+    st_relaxed_sys(slot, (b & 0xffffffffull) | t);
+    st_relaxed_sys(slot + 1, (b >> 32) | t);
+}
+/* All threads call it.  Threads g < G poll the LOCAL slots[g][2] until both words carry `tag`;
+ * thread 0 adds the G values in rank order -- every rank computes the same bits. */
+__device__ __forceinline__ double ll_gather_sum(const unsigned long long *slots, int G,
+                                                unsigned int tag, cgk_scalars *sc)
+{
+    __shared__ double s_val[CGK_MAX_RANKS];
+    __shared__ double s_sum;
+    if ((int)threadIdx.x < G) {
+        const unsigned long long *s = slots + 2 * threadIdx.x;
+        unsigned long long w0, w1, t0 = 0ull;
+        unsigned int polls = 0;
+        for (;;) {
+            w0 = ld_relaxed_sys(s);
+            w1 = ld_relaxed_sys(s + 1);
+            if ((unsigned int)(w0 >> 32) == tag && (unsigned int)(w1 >> 32) == tag) break;
+            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
+        }
+        s_val[threadIdx.x] = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int g = 0; g < G; ++g) t += s_val[g];
+        s_sum = t;
+    }
+    __syncthreads();
+    return s_sum;
+}
+/* Threads g < G (g != rank) wait until peer g's p slice of event `tag` has landed here. */
+__device__ __forceinline__ void wait_p_flags(const cgk_peers &peers, unsigned int tag, cgk_scalars *sc)
+{
+    const int g = threadIdx.x;
+    if (g < peers.ranks && g != peers.rank) {
+        const unsigned long long *f = &peers.mbox[peers.rank]->p_flag[g];
+        unsigned long long t0 = 0ull;
+        unsigned int polls = 0;
+        while (ld_relaxed_sys(f) != (unsigned long long)tag)
+            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
+        (void)ld_acquire_sys(f);
+    }
+    __syncthreads();
+}
+/* Warp-level form for use inside a streaming loop: no CTA barrier, the warps stay decoupled. */
+__device__ __forceinline__ void warp_wait_p_flags(const cgk_peers &peers, unsigned int tag, cgk_scalars *sc)
+{
+    const int g = threadIdx.x & 31;
+    if (g < peers.ranks && g != peers.rank) {
+        const unsigned long long *f = &peers.mbox[peers.rank]->p_flag[g];
+        unsigned long long t0 = 0ull;
+        unsigned int polls = 0;
+        /* poll relaxed (no L1 invalidation per poll), then acquire once */
+        while (ld_relaxed_sys(f) != (unsigned long long)tag)
+            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
+        (void)ld_acquire_sys(f);
+    }
+    __syncwarp();
+}
+/* cta_partials_finish for kernels that stored into peer memory: thread 0's fence is
+ * system-scope and cumulative over the CTA's stores (all before the preceding barrier), so
+ * whatever the last CTA posts afterwards is ordered behind every CTA's peer stores.  Returns
+ * true in all threads of the last CTA; *total is valid in its thread 0. */
+template <int NT>
+__device__ __forceinline__ bool cta_partials_finish_sys(double mine, double *partials, double *out,
+                                                        unsigned int *ticket, double *total)
+{
+    __shared__ int s_last;
+    __shared__ double s_red[NT / 32];
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        partials[blockIdx.x] = mine;
+        __threadfence_system();
+        unsigned int t = atomicAdd(ticket, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return false;
+    __threadfence();
+    double s = 0.0;
+    for (unsigned int i = tid; i < gridDim.x; i += NT) s += __ldcg(partials + i);
+    s = warp_sum(s);
+    if ((tid & 31) == 0) s_red[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < NT / 32; ++q) t += s_red[q];
+        *out = t;
+        *total = t;
+        *ticket = 0u;
+        __threadfence_system();
+    }
+    return true;
+}
+
 /* ------------------------------------------------------------------ GEMV (LDG) */
 /* One CTA owns R adjacent rows (one contiguous R*n*8-byte panel of A) and walks
  * all n columns; thread t of NT owns VW adjacent columns of every step, so a
@@ -104,6 +264,51 @@ __device__ __forceinline__ void cta_partials_finish(double mine, double *partial
  * U steps are issued back to back: R*U independent 128/256-bit loads in flight
  * per thread.  Row sums: registers -> warp shuffle -> shared -> fixed-order add.
  * Epilogue: y[row] and the CTA's partial of w.y (the fused p.Ap). */
+/* Columns [cb, ce) of the CTA's R rows: acc[r] += sum_c a[r][c] * v[c].  cb, ce are multiples
+ * of VW.  COH selects ordinary coherent loads of v (peers write other parts of it meanwhile). */
+template <int R, int U, int NT, int VW, bool COH>
+__device__ __forceinline__ void gemv_accumulate(double (&acc)[R], const double *const (&a)[R],
+                                                const double *__restrict__ v, long long cb,
+                                                long long ce, int tid)
+{
+    constexpr long long STEP = (long long)NT * VW;
+    constexpr long long TILE = STEP * U;
+    const long long main_end = cb + ((ce - cb) / TILE) * TILE;
+
+    for (long long c = cb + (long long)tid * VW; c < main_end; c += TILE) {
+        double pv[U][VW];
+        double av[R][U][VW];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if constexpr (COH) Ld<VW>::coherent(v + c + u * STEP, pv[u]);
+            else Ld<VW>::keep(v + c + u * STEP, pv[u]);
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int u = 0; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int e = 0; e < VW; ++e)
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u][e], pv[u][e], acc[r]);
+    }
+    /* column tail */
+    for (long long c = main_end + (long long)tid * VW; c < ce; c += STEP) {
+        double pv[VW];
+        double av[R][VW];
+        if constexpr (COH) Ld<VW>::coherent(v + c, pv);
+        else Ld<VW>::keep(v + c, pv);
+#pragma unroll
+        for (int r = 0; r < R; ++r) Ld<VW>::stream(a[r] + c, av[r]);
+#pragma unroll
+        for (int e = 0; e < VW; ++e)
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = fma(av[r][e], pv[e], acc[r]);
+    }
+}
+
 template <int R, int U, int NT, int VW>
 __global__ void __launch_bounds__(NT)
 gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
@@ -132,38 +337,7 @@ gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
 #pragma unroll
     for (int r = 0; r < R; ++r) acc[r] = 0.0;
 
-    constexpr long long STEP = (long long)NT * VW;
-    constexpr long long TILE = STEP * U;
-    const long long n_main = (n / TILE) * TILE;
-
-    for (long long c = (long long)tid * VW; c < n_main; c += TILE) {
-        double pv[U][VW];
-        double av[R][U][VW];
-#pragma unroll
-        for (int u = 0; u < U; ++u) Ld<VW>::keep(v + c + u * STEP, pv[u]);
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int u = 0; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u]);
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-#pragma unroll
-            for (int e = 0; e < VW; ++e)
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u][e], pv[u][e], acc[r]);
-    }
-    /* column tail (n % VW == 0 is guaranteed by the plan) */
-    for (long long c = n_main + (long long)tid * VW; c < n; c += STEP) {
-        double pv[VW];
-        double av[R][VW];
-        Ld<VW>::keep(v + c, pv);
-#pragma unroll
-        for (int r = 0; r < R; ++r) Ld<VW>::stream(a[r] + c, av[r]);
-#pragma unroll
-        for (int e = 0; e < VW; ++e)
-#pragma unroll
-            for (int r = 0; r < R; ++r) acc[r] = fma(av[r][e], pv[e], acc[r]);
-    }
+    gemv_accumulate<R, U, NT, VW, false>(acc, a, v, 0, n, tid);   /* n % VW == 0 by the plan */
 
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -185,6 +359,110 @@ gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
     if (w == nullptr) return;
     if (wid == 0) contrib = warp_sum(contrib);          /* lanes >= R hold 0 */
     cta_partials_finish<NT>(contrib, partials, dot_out, &sc->ticket_gemv);
+}
+
+/* The same product with the p exchange fused in (row-sharded A, ranks > 1; replaces
+ * MPI_Allgather + matVec + vecVec + MPI_Allreduce, parallel_cg.c:290-294).  Order of work in
+ * a CTA: (1) the rank's own column block, whose slice of p this GPU's p-update kernel wrote
+ * before this launch; (2) wait until every peer's slice of event ep has landed in the local
+ * p_full (flags in the local mailbox); (3) the remote column blocks.  CTAs of the first wave
+ * hide the exchange behind (1); later waves find the flags already set.  The last CTA pushes
+ * the rank's p.Ap partial into every rank's mailbox and advances the epoch. */
+template <int R, int U, int NT, int VW>
+__global__ void __launch_bounds__(NT)
+gemv_ldg_comm_kernel(const double *__restrict__ A, const double *v,
+                     const double *w, double *__restrict__ y,
+                     double *__restrict__ partials, double *__restrict__ dot_out,
+                     cgk_scalars *sc, long long m, long long n, const cgk_peers peers)
+{
+    const int stop = *(volatile int *)&sc->stop_req;
+    if (stop) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
+        return;
+    }
+    const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
+    const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+    constexpr int NW = NT / 32;
+    __shared__ double s_row[R][NW];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const long long row0 = (long long)blockIdx.x * R;
+
+    const double *a[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        long long row = row0 + r;
+        if (row > m - 1) row = m - 1;
+        a[r] = A + row * n;
+    }
+    double acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.0;
+
+    const long long lo = (long long)peers.rank * m, hi = lo + m;
+    const unsigned int tag = cgk_tag(gen, ep);
+    constexpr long long STEP = (long long)NT * VW;
+    constexpr long long TILE = STEP * U;
+    if (m % TILE == 0) {
+        /* One uninterrupted loop over the columns in wrapped order lo, lo+TILE, ..., n-TILE,
+         * 0, ..., lo-TILE: tiles never straddle a block boundary.  The flag check sits AFTER
+         * the tile's loads of A are issued (A is local and never waits) and before its loads
+         * of p, so it costs nothing once the flags are there (every CTA but the first wave)
+         * and the first wave polls with its loads in flight.  Warp-level: lanes g < G poll,
+         * __syncwarp orders the other lanes behind the acquire. */
+        const long long tiles = n / TILE;
+        const long long local_tiles = m / TILE;
+        long long c = lo + (long long)tid * VW;
+        for (long long k = 0; k < tiles; ++k) {
+            double pv[U][VW];
+            double av[R][U][VW];
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+#pragma unroll
+                for (int u = 0; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u]);
+            if (k == local_tiles) warp_wait_p_flags(peers, tag, sc);
+#pragma unroll
+            for (int u = 0; u < U; ++u) Ld<VW>::coherent(v + c + u * STEP, pv[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int e = 0; e < VW; ++e)
+#pragma unroll
+                    for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u][e], pv[u][e], acc[r]);
+            c += TILE;
+            if (c >= n) c -= n;
+        }
+    } else {
+        /* any shape: own block, wait, the two remote ranges */
+        gemv_accumulate<R, U, NT, VW, true>(acc, a, v, lo, hi, tid);
+        wait_p_flags(peers, tag, sc);
+        gemv_accumulate<R, U, NT, VW, true>(acc, a, v, 0, lo, tid);
+        gemv_accumulate<R, U, NT, VW, true>(acc, a, v, hi, n, tid);
+    }
+
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        acc[r] = warp_sum(acc[r]);
+        if (lane == 0) s_row[r][wid] = acc[r];
+    }
+    __syncthreads();
+    double contrib = 0.0;
+    if (tid < R) {
+        double s = 0.0;
+#pragma unroll
+        for (int q = 0; q < NW; ++q) s += s_row[tid][q];
+        const long long row = row0 + tid;
+        if (row < m) {
+            y[row] = s;
+            contrib = s * w[row];
+        }
+    }
+    if (wid == 0) contrib = warp_sum(contrib);
+    double total = 0.0;
+    if (cta_partials_finish_sys<NT>(contrib, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {
+        for (int g = 0; g < peers.ranks; ++g)
+            ll_send(&peers.mbox[g]->dot[0][ep & 1u][peers.rank][0], total, tag);
+        sc->ep_gemv = ep + 1u;
+    }
 }
 
 /* ------------------------------------------------------------------ GEMV (bulk-async ring) */
@@ -381,22 +659,9 @@ gemv_bulk_kernel(const double *__restrict__ A, const double *__restrict__ v,
 /* ------------------------------------------------------------------ vector phase */
 #define VEC_NT 256
 
-/* r = b - Ax0; p = b - Ax0 (the reference computes it twice, parallel_cg.c:284-285;
- * same value); rr partial.  Not guarded by stop_req: runs before the loop. */
-__global__ void __launch_bounds__(VEC_NT)
-init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax,
-                     double *__restrict__ r, double *__restrict__ p_loc,
-                     double *__restrict__ partials, double *__restrict__ rr_out,
-                     cgk_scalars *__restrict__ sc, long long m)
+/* CTA-level sum of one value per thread -> valid in thread 0 (fixed tree). */
+__device__ __forceinline__ double vec_cta_sum(double s)
 {
-    double s = 0.0;
-    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
-         i += (long long)gridDim.x * VEC_NT) {
-        const double ri = __dsub_rn(b[i], Ax[i]);
-        r[i] = ri;
-        p_loc[i] = ri;
-        s = fma(ri, ri, s);
-    }
     __shared__ double s_w[VEC_NT / 32];
     s = warp_sum(s);
     if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = s;
@@ -404,21 +669,80 @@ init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax
     double mine = 0.0;
     if (threadIdx.x == 0)
         for (int q = 0; q < VEC_NT / 32; ++q) mine += s_w[q];
-    cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
+    return mine;
+}
+
+/* Thread 0 of the last CTA of a kernel that pushed a p slice: post the slice's tag to every
+ * peer (the system fence in cta_partials_finish_sys / below orders it behind the slice). */
+__device__ __forceinline__ void post_p_flags(const cgk_peers &peers, unsigned int tag)
+{
+    for (int g = 0; g < peers.ranks; ++g)
+        if (g != peers.rank) st_relaxed_sys(&peers.mbox[g]->p_flag[peers.rank], (unsigned long long)tag);
+}
+
+/* r = b - Ax0; p = b - Ax0 (the reference computes it twice, parallel_cg.c:284-285;
+ * same value); rr partial.  Not guarded by stop_req: runs before the loop.
+ * COMM: the p slice also goes to every peer's p_full (event 0 of the all-gather,
+ * parallel_cg.c:290) and the r.r partial to every mailbox (the all-reduce of :287). */
+template <bool COMM>
+__global__ void __launch_bounds__(VEC_NT)
+init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax,
+                     double *__restrict__ r, double *p_loc,
+                     double *__restrict__ partials, double *__restrict__ rr_out,
+                     cgk_scalars *sc, long long m, const cgk_peers peers)
+{
+    double s = 0.0;
+    const long long lo = COMM ? (long long)peers.rank * m : 0;
+    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
+         i += (long long)gridDim.x * VEC_NT) {
+        const double ri = __dsub_rn(b[i], Ax[i]);
+        r[i] = ri;
+        p_loc[i] = ri;
+        if constexpr (COMM) {
+            for (int g = 0; g < peers.ranks; ++g)
+                if (g != peers.rank) peers.p_full[g][lo + i] = ri;
+        }
+        s = fma(ri, ri, s);
+    }
+    const double mine = vec_cta_sum(s);
+    if constexpr (COMM) {
+        const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+        double total = 0.0;
+        if (cta_partials_finish_sys<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec, &total) && threadIdx.x == 0) {
+            const unsigned int tag = cgk_tag(gen, 0u);
+            for (int g = 0; g < peers.ranks; ++g)
+                ll_send(&peers.mbox[g]->dot[1][0][peers.rank][0], total, tag);
+            post_p_flags(peers, tag);
+        }
+    } else {
+        cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
+    }
 }
 
 /* alpha = rho / p.Ap (parallel_cg.c:298); x += alpha*p through a rounded
  * product (scalarVec then vecAdd, :299,303); r -= alpha*Ap likewise (:304,308);
  * partial r.r (:309).  __dmul_rn/__dadd_rn keep the reference's rounding
- * points: no FMA contraction in the element-wise updates. */
+ * points: no FMA contraction in the element-wise updates.
+ * COMM: p.Ap is the rank-ordered sum of the G partials the GEMVs pushed into the local
+ * mailbox (MPI_Allreduce :294); the r.r partial is pushed to every mailbox (:313). */
+template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
 xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
-                 const double *__restrict__ p_loc, const double *__restrict__ Ap,
+                 const double *p_loc, const double *__restrict__ Ap,
                  double *__restrict__ partials, double *__restrict__ rr_out,
-                 cgk_scalars *__restrict__ sc, int cur, long long m)
+                 cgk_scalars *sc, int cur, long long m, const cgk_peers peers)
 {
     if (*(volatile int *)&sc->stop_req) return;
-    const double alpha = sc->rr[cur] / sc->pAp;
+    unsigned int ep = 0u, gen = 0u;
+    double pAp;
+    if constexpr (COMM) {
+        ep = *(volatile unsigned int *)&sc->ep_xr;
+        gen = *(volatile unsigned int *)&sc->gen;
+        pAp = ll_gather_sum(&peers.mbox[peers.rank]->dot[0][ep & 1u][0][0], peers.ranks, cgk_tag(gen, ep), sc);
+    } else {
+        pAp = sc->pAp;
+    }
+    const double alpha = sc->rr[cur] / pAp;
     double s = 0.0;
     for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
          i += (long long)gridDim.x * VEC_NT) {
@@ -427,46 +751,87 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
         r[i] = ri;
         s = fma(ri, ri, s);
     }
-    __shared__ double s_w[VEC_NT / 32];
-    s = warp_sum(s);
-    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = s;
-    __syncthreads();
-    double mine = 0.0;
-    if (threadIdx.x == 0)
-        for (int q = 0; q < VEC_NT / 32; ++q) mine += s_w[q];
-    cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
+    const double mine = vec_cta_sum(s);
+    if constexpr (COMM) {
+        double total = 0.0;
+        if (cta_partials_finish_sys<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec, &total) && threadIdx.x == 0) {
+            const unsigned int e = ep + 1u;                       /* r.r events: 0 = init, k+1 = iteration k */
+            for (int g = 0; g < peers.ranks; ++g)
+                ll_send(&peers.mbox[g]->dot[1][e & 1u][peers.rank][0], total, cgk_tag(gen, e));
+            sc->pAp = pAp;
+            sc->ep_xr = e;
+        }
+    } else {
+        cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
+    }
 }
 
 /* Stop rule and direction update (parallel_cg.c:314-323): if sqrt(beta) < eps the
  * loop breaks BEFORE p is touched (x and r updated, p stale); otherwise
  * p = r + (beta/rsold)*p via a rounded product, and rsold = beta (here: the
  * rr[] ping-pong, parity `cur` baked into the launch).  Thread 0 of CTA 0 does
- * the bookkeeping; every thread derives the same decision from beta. */
+ * the bookkeeping; every thread derives the same decision from beta.
+ * COMM: beta is the rank-ordered sum of the mailbox partials (same bits on every rank, so
+ * every rank takes the same branch); the new slice of p is stored into every peer's p_full
+ * as it is computed and the last CTA posts the tag the peers' next GEMV waits for. */
+template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
-p_update_kernel(double *__restrict__ p_loc, const double *__restrict__ r,
-                cgk_scalars *__restrict__ sc, int cur, double eps, int ignore_stop,
-                long long max_iter, long long m)
+p_update_kernel(double *p_loc, const double *__restrict__ r,
+                cgk_scalars *sc, int cur, double eps, int ignore_stop,
+                long long max_iter, long long m, const cgk_peers peers)
 {
     if (*(volatile int *)&sc->stopped) return;
-    const double rho = sc->rr[cur], beta = sc->rr[cur ^ 1];
+    unsigned int ep = 0u, gen = 0u;
+    const double rho = sc->rr[cur];
+    double beta;
+    if constexpr (COMM) {
+        ep = *(volatile unsigned int *)&sc->ep_p;
+        gen = *(volatile unsigned int *)&sc->gen;
+        const unsigned int e = ep + 1u;
+        beta = ll_gather_sum(&peers.mbox[peers.rank]->dot[1][e & 1u][0][0], peers.ranks, cgk_tag(gen, e), sc);
+    } else {
+        beta = sc->rr[cur ^ 1];
+    }
     const bool hit = sqrt(beta) < eps;
     const bool brk = hit && !ignore_stop;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         const long long k = sc->iters;
         sc->iters = k + 1;
         sc->final_beta = beta;
+        if constexpr (COMM) sc->rr[cur ^ 1] = beta;       /* read as rho by the NEXT iteration only */
         if (hit && sc->first_hit < 0) sc->first_hit = k;
         if (brk) { sc->break_k = k; sc->stop_req = 1; }
         else if (k + 1 >= max_iter) sc->stop_req = 2;
     }
     if (brk) return;
     const double coef = beta / rho;
+    const long long lo = COMM ? (long long)peers.rank * m : 0;
     for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
-         i += (long long)gridDim.x * VEC_NT)
-        p_loc[i] = __dadd_rn(r[i], __dmul_rn(p_loc[i], coef));
+         i += (long long)gridDim.x * VEC_NT) {
+        const double pi = __dadd_rn(r[i], __dmul_rn(p_loc[i], coef));
+        p_loc[i] = pi;
+        if constexpr (COMM) {
+            for (int g = 0; g < peers.ranks; ++g)
+                if (g != peers.rank) peers.p_full[g][lo + i] = pi;
+        }
+    }
+    if constexpr (COMM) {
+        __shared__ int s_last;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();                 /* cumulative over the CTA's peer stores */
+            s_last = (atomicAdd(&sc->ticket_vec, 1u) == gridDim.x - 1);
+            if (s_last) {
+                __threadfence_system();
+                post_p_flags(peers, cgk_tag(gen, ep + 1u));
+                sc->ticket_vec = 0u;
+                sc->ep_p = ep + 1u;
+            }
+        }
+    }
 }
 
-__global__ void reset_kernel(cgk_scalars *sc)
+__global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
 {
     sc->rr[0] = sc->rr[1] = 0.0;
     sc->pAp = sc->pAp_local = sc->rr_local = 0.0;
@@ -474,12 +839,23 @@ __global__ void reset_kernel(cgk_scalars *sc)
     sc->iters = 0; sc->first_hit = -1; sc->break_k = -1;
     sc->stop_req = 0; sc->stopped = 0;
     sc->ticket_gemv = 0u; sc->ticket_vec = 0u;
+    sc->gen = gen; sc->ep_gemv = sc->ep_xr = sc->ep_p = 0u;
+    sc->comm_error = 0;
 }
 
-__global__ void after_init_kernel(cgk_scalars *sc)
+template <bool COMM>
+__global__ void after_init_kernel(cgk_scalars *sc, const cgk_peers peers)
 {
-    sc->rsold0 = sc->rr[0];
-    sc->final_beta = sc->rr[0];
+    if constexpr (COMM) {
+        const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+        const double rr0 = ll_gather_sum(&peers.mbox[peers.rank]->dot[1][0][0][0], peers.ranks, cgk_tag(gen, 0u), sc);
+        if (threadIdx.x == 0) sc->rr[0] = rr0;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        sc->rsold0 = sc->rr[0];
+        sc->final_beta = sc->rr[0];
+    }
 }
 
 /* ------------------------------------------------------------------ generator */
@@ -690,41 +1066,118 @@ extern "C" int cgk_gemv(const cgk_gemv_plan *plan, const double *A, const double
     return (int)cudaGetLastError();
 }
 
+static const cgk_peers k_no_peers = {};
+
+/* comm variants: the size-class defaults of the plain kernel plus narrower-load fallbacks */
+typedef void (*gemv_comm_fn)(const double *, const double *, const double *, double *, double *,
+                             double *, cgk_scalars *, long long, long long, const cgk_peers);
+struct comm_cfg { int r, u, nt, vec; gemv_comm_fn fn; };
+static const comm_cfg k_comm[] = {
+    {4, 2, 256, 4, gemv_ldg_comm_kernel<4, 2, 256, 4>},
+    {2, 1, 256, 4, gemv_ldg_comm_kernel<2, 1, 256, 4>},
+    {2, 2, 256, 4, gemv_ldg_comm_kernel<2, 2, 256, 4>},
+    {4, 1, 128, 4, gemv_ldg_comm_kernel<4, 1, 128, 4>},
+    {4, 2, 128, 2, gemv_ldg_comm_kernel<4, 2, 128, 2>},
+    {4, 1, 128, 1, gemv_ldg_comm_kernel<4, 1, 128, 1>},
+};
+static const comm_cfg *find_comm(int r, int u, int nt, int vec)
+{
+    for (const comm_cfg &c : k_comm)
+        if (c.r == r && c.u == u && c.nt == nt && c.vec == vec) return &c;
+    return nullptr;
+}
+
+extern "C" int cgk_gemv_make_plan_comm(cgk_gemv_plan *plan, int64_t m, int64_t n, const void *A,
+                                       const void *v, int sm_count)
+{
+    (void)sm_count;
+    if (!plan || m < 1 || n < 1) return (int)cudaErrorInvalidValue;
+    const uintptr_t pa = (uintptr_t)A, pv = (uintptr_t)v;
+    int vec = 1;                       /* block boundaries are multiples of m */
+    if (n % 4 == 0 && m % 4 == 0 && pa % 32 == 0 && pv % 32 == 0) vec = 4;
+    else if (n % 2 == 0 && m % 2 == 0 && pa % 16 == 0 && pv % 16 == 0) vec = 2;
+    if (plan->vec != 0 && plan->vec < vec) vec = plan->vec == 3 ? 2 : plan->vec;
+    const comm_cfg *c = nullptr;
+    if (plan->rows_per_cta && plan->unroll && plan->threads)
+        c = find_comm(plan->rows_per_cta, plan->unroll, plan->threads, vec);
+    if (!c) {
+        if (vec == 4) {
+            /* (8,2,512): all 64 doubles of A in flight before the flag check do not fit 128
+             * registers; (4,2,256) keeps 2 CTAs per SM and no spill */
+            if (n >= 8192) c = find_comm(4, 2, 256, 4);     /* measured on 2 GPUs: beats (2,1,256) at n = 16384 */
+            else c = find_comm(4, 1, 128, 4);
+        } else if (vec == 2) c = find_comm(4, 2, 128, 2);
+        else c = find_comm(4, 1, 128, 1);
+    }
+    if (!c) return (int)cudaErrorInvalidValue;
+    plan->variant = CGK_GEMV_LDG;
+    plan->rows_per_cta = c->r; plan->unroll = c->u; plan->threads = c->nt; plan->vec = c->vec;
+    plan->stages = 0; plan->tile_cols = 0; plan->smem_bytes = 0;
+    plan->grid = (int)ceil_div(m, c->r);
+    return 0;
+}
+
+extern "C" int cgk_gemv_comm(const cgk_gemv_plan *plan, const double *A, const double *v,
+                             const double *w, double *y, double *partials, double *dot_out,
+                             cgk_scalars *sc, int64_t m, int64_t n, const cgk_peers *peers,
+                             void *stream)
+{
+    const comm_cfg *c = find_comm(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec);
+    if (!c || !peers || !w) return (int)cudaErrorInvalidValue;
+    c->fn<<<plan->grid, plan->threads, 0, (cudaStream_t)stream>>>(A, v, w, y, partials, dot_out, sc,
+                                                                  (long long)m, (long long)n, *peers);
+    return (int)cudaGetLastError();
+}
+
 extern "C" int cgk_init_residual(const double *b, const double *Ax, double *r, double *p_loc,
                                  double *partials, double *rr_out, cgk_scalars *sc, int64_t m,
-                                 void *stream)
+                                 const cgk_peers *peers, void *stream)
 {
-    init_residual_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
-                                                                          rr_out, sc, (long long)m);
+    if (peers)
+        init_residual_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
+                                                                                    rr_out, sc, (long long)m, *peers);
+    else
+        init_residual_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
+                                                                                     rr_out, sc, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
 
 extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
                              double *partials, double *rr_out, cgk_scalars *sc, int cur,
-                             int64_t m, void *stream)
+                             int64_t m, const cgk_peers *peers, void *stream)
 {
-    xr_update_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                      sc, cur, (long long)m);
+    if (peers)
+        xr_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
+                                                                                sc, cur, (long long)m, *peers);
+    else
+        xr_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
+                                                                                 sc, cur, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
 
 extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
-                            int ignore_stop, int64_t max_iter, int64_t m, void *stream)
+                            int ignore_stop, int64_t max_iter, int64_t m, const cgk_peers *peers,
+                            void *stream)
 {
-    p_update_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
-                                                                     (long long)max_iter, (long long)m);
+    if (peers)
+        p_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
+                                                                               (long long)max_iter, (long long)m, *peers);
+    else
+        p_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
+                                                                                (long long)max_iter, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
 
-extern "C" int cgk_reset(cgk_scalars *sc, void *stream)
+extern "C" int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream)
 {
-    reset_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc);
+    reset_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc, gen);
     return (int)cudaGetLastError();
 }
 
-extern "C" int cgk_after_init(cgk_scalars *sc, void *stream)
+extern "C" int cgk_after_init(cgk_scalars *sc, const cgk_peers *peers, void *stream)
 {
-    after_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc);
+    if (peers) after_init_kernel<true><<<1, 32, 0, (cudaStream_t)stream>>>(sc, *peers);
+    else after_init_kernel<false><<<1, 32, 0, (cudaStream_t)stream>>>(sc, k_no_peers);
     return (int)cudaGetLastError();
 }
 

@@ -34,7 +34,38 @@ typedef struct cgk_scalars {
                            /* no kernel ever reads a flag that is written during its own run  */
     unsigned int ticket_gemv;
     unsigned int ticket_vec;
+    /* peer-memory exchange (cgk_peers): per-kernel epoch counters, advanced by the last CTA of
+     * each non-stopped launch, so a replayed graph needs no per-iteration launch argument */
+    unsigned int gen;      /* solve generation: high bits of every tag, set by cgk_reset      */
+    unsigned int ep_gemv, ep_xr, ep_p;
+    int comm_error;        /* a spin on a peer's flag ran into CGK_SPIN_TIMEOUT_NS            */
+    int pad_;
 } cgk_scalars;
+
+/* ---- peer-memory exchange over NVLink (replaces MPI_Allgather(p) parallel_cg.c:290-291 and the
+ * MPI_Allreduce of the two dot scalars :294,313 inside the solver kernels themselves).
+ * Every rank owns a window [cgk_mailbox | p_full(n)] that all ranks of the node map (CUDA IPC or
+ * same-process peer access).  Producers PUSH: the p-update kernel stores its slice of the new
+ * direction straight into every peer's p_full and then posts an epoch tag into the peers'
+ * p_flag[rank]; the last CTA of the GEMV / xr-update kernels stores the rank's dot partial into
+ * every peer's dot[][][rank] slot in NCCL-LL style (two 8-byte words, each {32 data bits, 32-bit
+ * tag}, so data and flag arrive atomically without a fence).  Consumers only ever read LOCAL
+ * memory: the next kernel spins on its own mailbox and adds the G partials in rank order, so all
+ * ranks get bit-identical sums and take the same `break` (as parallel_cg.c:313-317 relies on). */
+#define CGK_MAX_RANKS 8
+#define CGK_SPIN_TIMEOUT_NS 20000000000ull      /* 20 s: a dead peer ends the solve with an error */
+#define CGK_WINDOW_HEADER_BYTES 4096            /* mailbox at offset 0, p_full at this offset     */
+
+typedef struct cgk_mailbox {
+    unsigned long long p_flag[CGK_MAX_RANKS];             /* tag of the last p slice rank g pushed */
+    unsigned long long dot[2][2][CGK_MAX_RANKS][2];       /* [0 p.Ap | 1 r.r][parity][src][LL word] */
+} cgk_mailbox;
+
+typedef struct cgk_peers {
+    int rank, ranks;
+    double *p_full[CGK_MAX_RANKS];      /* every rank's gathered-direction vector, peer-mapped */
+    cgk_mailbox *mbox[CGK_MAX_RANKS];   /* every rank's mailbox; mbox[rank] is local           */
+} cgk_peers;
 
 typedef struct cgk_gemv_plan {
     int variant;           /* CGK_GEMV_*                                  */
@@ -61,6 +92,10 @@ int64_t cgk_vec_max_ctas(int64_t m);
  * kernel with the widest legal vector width -- always a CUDA kernel. */
 int cgk_gemv_make_plan(cgk_gemv_plan *plan, int64_t m, int64_t n, const void *A,
                        const void *v, int sm_count);
+/* Plan for cgk_gemv_comm: streaming-load kernel only, vector width limited by the alignment of
+ * the column-block boundaries (multiples of m). */
+int cgk_gemv_make_plan_comm(cgk_gemv_plan *plan, int64_t m, int64_t n, const void *A,
+                            const void *v, int sm_count);
 
 /* y = A v (m x n row block, row-major).  If w != NULL the CTA partials of
  * sum_i w[i]*y[i] go to `partials` and the last CTA to finish sums them in a
@@ -68,25 +103,35 @@ int cgk_gemv_make_plan(cgk_gemv_plan *plan, int64_t m, int64_t n, const void *A,
 int cgk_gemv(const cgk_gemv_plan *plan, const double *A, const double *v, const double *w,
              double *y, double *partials, double *dot_out, cgk_scalars *sc,
              int64_t m, int64_t n, void *stream);
+/* Same product with the exchange fused in (ranks > 1, peer windows): the CTA first walks the
+ * rank's own column block [rank*m, (rank+1)*m) -- which needs only the slice of p this GPU
+ * wrote itself -- then waits for the peers' p_flag tags and walks the remote columns, so the
+ * p exchange overlaps the local-block product; the last CTA pushes the p.Ap partial to all
+ * peers.  v must be peers->p_full[rank], w the rank's own slice of it. */
+int cgk_gemv_comm(const cgk_gemv_plan *plan, const double *A, const double *v, const double *w,
+                  double *y, double *partials, double *dot_out, cgk_scalars *sc,
+                  int64_t m, int64_t n, const cgk_peers *peers, void *stream);
 
 /* r = b - Ax0, p_loc = b - Ax0, rr partials -> *rr_out (fixed-order sum). */
 int cgk_init_residual(const double *b, const double *Ax, double *r, double *p_loc,
                       double *partials, double *rr_out, cgk_scalars *sc, int64_t m,
-                      void *stream);
+                      const cgk_peers *peers, void *stream);
 
 /* alpha = rr[cur]/pAp; x += alpha p; r -= alpha Ap; r.r partials -> *rr_out. */
 int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
                   double *partials, double *rr_out, cgk_scalars *sc, int cur,
-                  int64_t m, void *stream);
+                  int64_t m, const cgk_peers *peers, void *stream);
 
 /* beta = rr[cur^1]: bookkeeping + stop rule on thread 0; p = r + (beta/rho) p. */
 int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
-                 int ignore_stop, int64_t max_iter, int64_t m, void *stream);
+                 int ignore_stop, int64_t max_iter, int64_t m, const cgk_peers *peers,
+                 void *stream);
 
 /* Resets the scalars for a new solve (first kernel of the init phase). */
-int cgk_reset(cgk_scalars *sc, void *stream);
-/* rr[0] bookkeeping after the initial all-reduce. */
-int cgk_after_init(cgk_scalars *sc, void *stream);
+int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream);
+/* rr[0] bookkeeping after the initial all-reduce (peers != NULL: it IS the all-reduce --
+ * gathers the ranks' r.r partials from the local mailbox). */
+int cgk_after_init(cgk_scalars *sc, const cgk_peers *peers, void *stream);
 
 /* Rows [row0,row0+m) of the seeded SPD matrix into A (m x n); b rows likewise. */
 int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,

@@ -21,6 +21,8 @@
  *   --seed S          generator seed (default 20170209)   --round4  "%.4f" rounding
  *   --bench-iters K   fixed-iteration timing mode (stop test recorded, not acted on)
  *   --gemv V          1 = streaming loads, 2 = bulk-async ring
+ *   --comm nccl|peer  per-iteration exchange with --gpus > 1 (default: peer when the GPUs
+ *                     can map each other's memory: fused NVLink pushes, else NCCL)
  *   --stats           extra lines: iterations, residual, GEMV GB/s
  */
 #define _GNU_SOURCE
@@ -31,13 +33,14 @@
 #include <string.h>
 #include <time.h>
 #include <libgen.h>
+#include <unistd.h>
 
 #include "../../include/cgb200.h"
 #include "cg_io.h"
 
 typedef struct {
     const char *fileA, *fileB, *fileX, *dims, *write_x;
-    int gpus, print_x, stats, round4, gemv;
+    int gpus, print_x, stats, round4, gemv, comm;
     int64_t gen_n, max_iter, bench_iters;
     uint64_t seed;
     double eps;
@@ -66,6 +69,13 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         else if (!strcmp(a, "--seed")) { c->seed = strtoull(v, NULL, 10); ++i; }
         else if (!strcmp(a, "--bench-iters")) { c->bench_iters = atoll(v); ++i; }
         else if (!strcmp(a, "--gemv")) { c->gemv = atoi(v); ++i; }
+        else if (!strcmp(a, "--comm")) {
+            if (!strcmp(v, "nccl")) c->comm = CGB_COMM_NCCL;
+            else if (!strcmp(v, "peer")) c->comm = CGB_COMM_PEER;
+            else if (!strcmp(v, "auto")) c->comm = CGB_COMM_AUTO;
+            else { fprintf(stderr, "--comm takes nccl, peer or auto\n"); return -1; }
+            ++i;
+        }
         else { fprintf(stderr, "unknown option %s\n", a); return -1; }
     }
     c->fileA = pos[0]; c->fileB = pos[1]; c->fileX = pos[2];
@@ -109,6 +119,7 @@ int main(int argc, char **argv)
     opt.eps = cli.eps;
     opt.max_iter = cli.max_iter;
     opt.gemv_variant = cli.gemv;
+    opt.comm = cli.comm;
     if (cli.bench_iters > 0) { opt.ignore_stop = 1; opt.max_iter = cli.bench_iters; }
 
     cgb_stats st;
@@ -116,6 +127,11 @@ int main(int argc, char **argv)
     double *A = NULL, *b = NULL, *x = NULL;
     int64_t n = 0;
     int rc;
+    int saved_stdout = -1;
+    /* While the solver runs, fd 1 points at stderr: whatever a library underneath prints
+     * (NCCL's version banner with NCCL_DEBUG=VERSION) cannot land between the reference's lines. */
+#define SOLVER_STDOUT_OFF() do { fflush(stdout); saved_stdout = dup(1); if (saved_stdout >= 0) dup2(2, 1); } while (0)
+#define SOLVER_STDOUT_ON()  do { fflush(stdout); if (saved_stdout >= 0) { dup2(saved_stdout, 1); close(saved_stdout); saved_stdout = -1; } } while (0)
 
     if (cli.gen_n > 0) {
         n = cli.gen_n;
@@ -126,7 +142,9 @@ int main(int argc, char **argv)
         printf("Computing cg of matrix size : %lld\n", (long long)n * (long long)n);
         x = malloc((size_t)n * sizeof(double));
         if (!x) { printf("can't allocate memory for vector\n"); return 1; }
+        SOLVER_STDOUT_OFF();
         rc = cgb_solve_generated(n, cli.seed, cli.round4 ? CGB_GEN_ROUND4 : 0u, cli.gpus, &opt, x, &st);
+        SOLVER_STDOUT_ON();
     } else {
         int64_t dims[4];
         int inferred = 0;
@@ -165,7 +183,9 @@ int main(int argc, char **argv)
                 return 1;
             }
         }
+        SOLVER_STDOUT_OFF();
         rc = cgb_conjugrad_host_opt(A, b, x, n, cli.gpus, &opt, &st);
+        SOLVER_STDOUT_ON();
     }
     if (rc != CGB_OK) {
         fprintf(stderr, "cg_b200: %s\n", cgb_last_error());
@@ -183,6 +203,7 @@ int main(int argc, char **argv)
         printf("iterations: %lld\n", (long long)st.iterations);
         printf("loop index at break: %lld\n", (long long)st.break_k);
         printf("final residual sqrt(r.r): %.6e\n", st.final_residual);
+        if (cli.gpus > 1) printf("exchange: %s\n", st.comm == CGB_COMM_PEER ? "peer (fused NVLink pushes)" : "nccl");
         if (st.iterations > 0 && st.loop_ms > 0.0) {
             double it_s = 1.0e3 * (double)st.iterations / st.loop_ms;
             printf("iterations per second: %.3f\n", it_s);

@@ -17,6 +17,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <unistd.h>
 
 #include "../../include/cgb200.h"
 #include "cg_kernels.h"
@@ -161,13 +162,137 @@ static void drop_graph(cgb_ctx *c)
     memset(&c->graph_key, 0, sizeof c->graph_key);
 }
 
+/* Unmaps the peers' windows.  No collective here: a solve ends with the all-gather of x, so
+ * once cgb_solve() has returned on a rank no peer touches its window until the next
+ * (collective) solve or re-allocation. */
+static void close_peers(cgb_ctx *c)
+{
+    for (int g = 0; g < CGK_MAX_RANKS; ++g) {
+        if (c->peer_ipc[g] && c->peer_win[g]) cudaIpcCloseMemHandle(c->peer_win[g]);
+        c->peer_win[g] = NULL; c->peer_ipc[g] = 0;
+    }
+    memset(&c->peers, 0, sizeof c->peers);
+    c->peer_ok = 0;
+    (void)cudaGetLastError();
+}
+
 static void free_problem(cgb_ctx *c)
 {
     drop_graph(c);
+    close_peers(c);
     cudaFree(c->A); cudaFree(c->b); cudaFree(c->r); cudaFree(c->Ap);
-    cudaFree(c->p_full); cudaFree(c->x_full); cudaFree(c->partials_gemv);
+    if (c->win) cudaFree(c->win); else cudaFree(c->p_full);
+    cudaFree(c->x_full); cudaFree(c->partials_gemv);
     c->A = c->b = c->r = c->Ap = c->p_full = c->x_full = c->partials_gemv = NULL;
+    c->win = NULL; c->win_bytes = 0;
     c->n = c->m = 0; c->cap_n = c->cap_m = 0; c->loaded = 0;
+}
+
+/* Collective over the ranks: every rank publishes its window (CUDA IPC handle, or the raw
+ * pointer for ranks that are threads of one process) through one small ncclAllGather, maps
+ * the others', and the ranks agree (all-reduce MIN) on whether the peer path is usable.  This
+ * is the only set-up the fused exchange needs; it replaces nothing in the reference, where
+ * MPI owns the transport. */
+typedef struct {
+    cudaIpcMemHandle_t handle;        /* 64 B */
+    uint64_t ptr;
+    int64_t pid;
+    int32_t device;
+    int32_t exported;
+    char pad[128 - 64 - 8 - 8 - 4 - 4];
+} window_card;
+
+static int exchange_windows(cgb_ctx *c)
+{
+    const int G = c->ranks;
+    cudaStream_t st = c->stream;
+    close_peers(c);
+    snprintf(c->peer_why, sizeof c->peer_why, "%s", "");
+    int usable = G <= CGK_MAX_RANKS;
+    const char *off = getenv("CGB_DISABLE_PEER");
+    if (off && *off && *off != '0') { usable = 0; snprintf(c->peer_why, sizeof c->peer_why, "CGB_DISABLE_PEER is set"); }
+    if (G > CGK_MAX_RANKS) snprintf(c->peer_why, sizeof c->peer_why, "more than %d ranks", CGK_MAX_RANKS);
+
+    window_card mine;
+    memset(&mine, 0, sizeof mine);
+    mine.ptr = (uint64_t)(uintptr_t)c->win;
+    mine.pid = (int64_t)getpid();
+    mine.device = c->device;
+    if (usable) {
+        if (cudaIpcGetMemHandle(&mine.handle, c->win) == cudaSuccess) mine.exported = 1;
+        else (void)cudaGetLastError();       /* still usable by ranks of this process */
+    }
+    window_card *d_cards = NULL, *h_cards = NULL;
+    int *d_ok = NULL;
+    CU(cudaMalloc((void **)&d_cards, (size_t)G * sizeof(window_card) + 64));
+    h_cards = malloc((size_t)G * sizeof(window_card));
+    if (!h_cards) { cudaFree(d_cards); FAIL(CGB_ERR_NOMEM, "out of host memory"); }
+    d_ok = (int *)((char *)d_cards + (size_t)G * sizeof(window_card));
+    int rc = CGB_OK;
+#define XW(call) do { if ((call) != cudaSuccess) { cgb_set_error("CUDA error: %s in `%s` (cg_solver.c:%d)", cudaGetErrorString(cudaGetLastError()), #call, __LINE__); rc = CGB_ERR_CUDA; goto out; } } while (0)
+#define XN(call) do { ncclResult_t e_ = (call); if (e_ != ncclSuccess) { cgb_set_error("NCCL error: %s in `%s` (cg_solver.c:%d)", ncclGetErrorString(e_), #call, __LINE__); rc = CGB_ERR_NCCL; goto out; } } while (0)
+    XW(cudaMemcpyAsync(d_cards + c->rank, &mine, sizeof mine, cudaMemcpyHostToDevice, st));
+    XN(ncclAllGather(d_cards + c->rank, d_cards, sizeof(window_card), ncclChar, c->comm, st));
+    XW(cudaMemcpyAsync(h_cards, d_cards, (size_t)G * sizeof(window_card), cudaMemcpyDeviceToHost, st));
+    XW(cudaStreamSynchronize(st));
+
+    int ok = usable;
+    for (int g = 0; g < G && ok; ++g) {
+        if (g == c->rank) { c->peer_win[g] = c->win; continue; }
+        const window_card *k = &h_cards[g];
+        if (k->pid == mine.pid) {                       /* a thread of this process */
+            if (k->device == c->device) { ok = 0; snprintf(c->peer_why, sizeof c->peer_why, "two ranks share GPU %d", c->device); break; }
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, c->device, k->device) != cudaSuccess || !can) {
+                (void)cudaGetLastError();
+                ok = 0; snprintf(c->peer_why, sizeof c->peer_why, "GPU %d cannot access GPU %d", c->device, k->device);
+                break;
+            }
+            cudaError_t e = cudaDeviceEnablePeerAccess(k->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                ok = 0; snprintf(c->peer_why, sizeof c->peer_why, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            }
+            (void)cudaGetLastError();
+            c->peer_win[g] = (void *)(uintptr_t)k->ptr;
+        } else {
+            void *q = NULL;
+            cudaError_t e = k->exported ? cudaIpcOpenMemHandle(&q, k->handle, cudaIpcMemLazyEnablePeerAccess)
+                                        : cudaErrorNotSupported;
+            if (e != cudaSuccess) {
+                (void)cudaGetLastError();
+                ok = 0; snprintf(c->peer_why, sizeof c->peer_why, "cudaIpcOpenMemHandle(rank %d): %s", g, cudaGetErrorString(e));
+                break;
+            }
+            c->peer_win[g] = q; c->peer_ipc[g] = 1;
+        }
+    }
+    /* agree: MIN over the ranks */
+    XW(cudaMemcpyAsync(d_ok, &ok, sizeof ok, cudaMemcpyHostToDevice, st));
+    XN(ncclAllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, c->comm, st));
+    int all_ok = 0;
+    XW(cudaMemcpyAsync(&all_ok, d_ok, sizeof ok, cudaMemcpyDeviceToHost, st));
+    XW(cudaStreamSynchronize(st));
+    if (all_ok) {
+        c->peers.rank = c->rank; c->peers.ranks = G;
+        for (int g = 0; g < G; ++g) {
+            c->peers.mbox[g] = (cgk_mailbox *)c->peer_win[g];
+            c->peers.p_full[g] = (double *)((char *)c->peer_win[g] + CGK_WINDOW_HEADER_BYTES);
+        }
+        c->peer_ok = 1;
+    } else {
+        if (ok) snprintf(c->peer_why, sizeof c->peer_why, "another rank could not map its peers");
+        int keep_why = 1;
+        char why[sizeof c->peer_why];
+        snprintf(why, sizeof why, "%s", c->peer_why);
+        close_peers(c);
+        if (keep_why) snprintf(c->peer_why, sizeof c->peer_why, "%s", why);
+    }
+out:
+#undef XW
+#undef XN
+    free(h_cards);
+    cudaFree(d_cards);
+    return rc;
 }
 
 int cgb_destroy(cgb_ctx *c)
@@ -227,7 +352,19 @@ static int ensure_problem(cgb_ctx *c, int64_t n)
         CU(cudaMalloc((void **)&c->b, (size_t)m * sizeof(double)));
         CU(cudaMalloc((void **)&c->r, (size_t)m * sizeof(double)));
         CU(cudaMalloc((void **)&c->Ap, (size_t)m * sizeof(double)));
-        CU(cudaMalloc((void **)&c->p_full, (size_t)n * sizeof(double)));
+        if (c->ranks > 1) {
+            /* [mailbox | p_full] in one allocation of whole 2 MiB pages: one IPC handle */
+            const size_t gran = (size_t)2 << 20;
+            c->win_bytes = (CGK_WINDOW_HEADER_BYTES + (size_t)n * sizeof(double) + gran - 1) / gran * gran;
+            CU(cudaMalloc(&c->win, c->win_bytes));
+            CU(cudaMemsetAsync(c->win, 0, c->win_bytes, c->stream));
+            CU(cudaStreamSynchronize(c->stream));
+            c->p_full = (double *)((char *)c->win + CGK_WINDOW_HEADER_BYTES);
+            int rc = exchange_windows(c);
+            if (rc != CGB_OK) return rc;
+        } else {
+            CU(cudaMalloc((void **)&c->p_full, (size_t)n * sizeof(double)));
+        }
         CU(cudaMalloc((void **)&c->x_full, (size_t)n * sizeof(double)));
         CU(cudaMalloc((void **)&c->partials_gemv, (size_t)cgk_gemv_max_ctas(m) * sizeof(double)));
         c->cap_n = n; c->cap_m = m;
@@ -334,6 +471,19 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     double *x_loc = c->x_full + (size_t)c->rank * (size_t)c->m;
     cudaStream_t st = c->stream;
+    if (c->comm_mode == CGB_COMM_PEER) {
+        /* the three collectives live inside the kernels: p slices and dot partials are pushed
+         * into the peers' windows over NVLink, consumers spin on their own mailbox */
+        if (ev_a) CU(cudaEventRecord(ev_a, st));
+        KL(cgk_gemv_comm(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local,
+                         c->sc, c->m, c->n, &c->peers, st));                     /* :290-294 */
+        if (ev_b) CU(cudaEventRecord(ev_b, st));
+        KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec, &c->sc->rr_local, c->sc, cur,
+                         c->m, &c->peers, st));                                  /* :298-313 */
+        KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, &c->peers, st)); /* :314-323 */
+        c->launches += 3;
+        return CGB_OK;
+    }
     if (multi)                                                   /* MPI_Allgather(p), :290-291 */
         NC(ncclAllGather(p_loc, c->p_full, (size_t)c->m, ncclDouble, c->comm, st));
     if (ev_a) CU(cudaEventRecord(ev_a, st));
@@ -343,10 +493,10 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     if (multi)                                                   /* MPI_Allreduce(alpha), :294 */
         NC(ncclAllReduce(&c->sc->pAp_local, &c->sc->pAp, 1, ncclDouble, ncclSum, c->comm, st));
     KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec,
-                     multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, c->m, st)); /* :298-309 */
+                     multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, c->m, NULL, st)); /* :298-309 */
     if (multi)                                                   /* MPI_Allreduce(beta), :313 */
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[cur ^ 1], 1, ncclDouble, ncclSum, c->comm, st));
-    KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, st)); /* :314-323 */
+    KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, NULL, st)); /* :314-323 */
     c->launches += 3;
     return CGB_OK;
 }
@@ -357,7 +507,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     memset(&key, 0, sizeof key);
     key.n = c->n; key.m = c->m; key.max_iter = max_iter; key.eps = o->eps;
     key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan;
-    key.A = c->A;
+    key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -414,11 +564,24 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     cudaStream_t st = c->stream;
     CU(cudaSetDevice(c->device));
 
+    /* transport of the per-iteration exchange (every rank passes the same option) */
+    c->comm_mode = 0;
+    if (multi) {
+        if (o.comm == CGB_COMM_PEER && !c->peer_ok) {
+            snprintf(tl_err, sizeof tl_err, "CGB_COMM_PEER requested but the peer windows are not mapped: %s", c->peer_why);
+            return CGB_ERR_STATE;
+        }
+        c->comm_mode = (o.comm == CGB_COMM_NCCL || !c->peer_ok) ? CGB_COMM_NCCL : CGB_COMM_PEER;
+    }
+    const cgk_peers *peers = c->comm_mode == CGB_COMM_PEER ? &c->peers : NULL;
+
     cgk_gemv_plan req;
     plan_request_from_options(&req, &o);
     c->plan = req;
-    KL(cgk_gemv_make_plan(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
+    if (peers) KL(cgk_gemv_make_plan_comm(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
+    else KL(cgk_gemv_make_plan(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
     if ((int64_t)c->plan.grid > cgk_gemv_max_ctas(c->m)) FAIL(CGB_ERR_STATE, "gemv grid exceeds workspace");
+    if ((++c->gen & 0x3ffu) == 0u) ++c->gen;              /* tags never collide with zeroed memory */
 
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     const int use_graph = o.use_graph && !o.time_gemv;
@@ -440,17 +603,20 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     const double t0 = now_s();
     CU(cudaEventRecord(c->ev[0], st));
     /* ---- init: Ax0, r = p = b - Ax0, rho = r.r   (parallel_cg.c:283-287) */
-    KL(cgk_reset(c->sc, st));
+    if (peers)      /* the MPI_Barrier of parallel_cg.c:278: no rank pushes into a window whose
+                     * owner has not entered this solve (late ranks never meet a spin time-out) */
+        NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr_local, 1, ncclDouble, ncclSum, c->comm, st));
+    KL(cgk_reset(c->sc, c->gen, st));
     {
         cgk_gemv_plan ip = req;                     /* same request, v = x0 */
         KL(cgk_gemv_make_plan(&ip, c->m, c->n, c->A, c->x_full, c->sm_count));
         KL(cgk_gemv(&ip, c->A, c->x_full, NULL, c->Ap, c->partials_gemv, NULL, c->sc, c->m, c->n, st));
     }
     KL(cgk_init_residual(c->b, c->Ap, c->r, p_loc, c->partials_vec,
-                         multi ? &c->sc->rr_local : &c->sc->rr[0], c->sc, c->m, st));
-    if (multi)
+                         multi ? &c->sc->rr_local : &c->sc->rr[0], c->sc, c->m, peers, st));
+    if (multi && !peers)
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[0], 1, ncclDouble, ncclSum, c->comm, st));
-    KL(cgk_after_init(c->sc, st));
+    KL(cgk_after_init(c->sc, peers, st));
     c->launches += 4;
     CU(cudaEventRecord(c->ev[1], st));
 
@@ -478,7 +644,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         if (o.ignore_stop && issued < max_iter) continue;      /* fixed-iteration mode: no polling */
         CU(cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        if (c->h_sc->stop_req != 0) break;
+        if (c->h_sc->stop_req != 0 || c->h_sc->comm_error != 0) break;
         if (issued > max_iter + 4) FAIL(CGB_ERR_STATE, "solver loop did not terminate");
     }
     CU(cudaEventRecord(c->ev[2], st));
@@ -487,6 +653,11 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         NC(ncclAllGather(c->x_full + (size_t)c->rank * (size_t)c->m, c->x_full, (size_t)c->m, ncclDouble, c->comm, st));
     CU(cudaStreamSynchronize(st));
     const double t1 = now_s();
+    if (c->h_sc->comm_error != 0) {
+        snprintf(tl_err, sizeof tl_err, "rank %d: a peer rank did not answer within %.0f s during the solve "
+                 "(iteration %lld); results are invalid", c->rank, CGK_SPIN_TIMEOUT_NS * 1e-9, (long long)c->h_sc->iters);
+        return CGB_ERR_COMM;
+    }
 
     if (stats) {
         float ms_init = 0.f, ms_loop = 0.f;
@@ -510,6 +681,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->gemv_vec = c->plan.vec; stats->gemv_stages = c->plan.stages;
         stats->gemv_tile_cols = c->plan.tile_cols; stats->gemv_grid = c->plan.grid;
         stats->graph_chunk = chunk;
+        stats->comm = c->comm_mode;
         if (gemv_pairs_used > 0) {
             double sum = 0.0, mn = 1e300;
             for (int i = 0; i < gemv_pairs_used; ++i) {
@@ -559,7 +731,7 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
         CU(cudaMalloc(&c->flush_buf, flush_bytes));
         CU(cudaMemsetAsync(c->flush_buf, 0, flush_bytes, st));
     }
-    KL(cgk_reset(c->sc, st));
+    KL(cgk_reset(c->sc, c->gen, st));
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     for (int i = 0; i < warmup; ++i)
         KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
@@ -606,7 +778,7 @@ int cgb_op_matvec(cgb_ctx *c, const double *A, const double *v, const double *w,
     plan_request_from_options(&plan, &o);
     rc = CGB_ERR_CUDA;
     if (cgk_gemv_make_plan(&plan, m, n, dA, dv, c->sm_count) != 0) { cgb_set_error("%s%s (cg_solver.c:%d)", "no gemv plan for this shape", "", __LINE__); goto out; }
-    if (cgk_reset(c->sc, st) != 0) goto out;
+    if (cgk_reset(c->sc, c->gen, st) != 0) goto out;
     if (cgk_gemv(&plan, dA, dv, dw, dy, dpart, &c->sc->pAp, c->sc, m, n, st) != 0) {
         cgb_set_error("%s%s (cg_solver.c:%d)", "gemv launch failed: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
         goto out;
@@ -637,8 +809,8 @@ int cgb_op_init_residual(cgb_ctx *c, const double *b, const double *Ax, double *
         (rc = dev_dup(&dr, NULL, m, st)) || (rc = dev_dup(&dp, NULL, m, st)))
         goto out;
     rc = CGB_ERR_CUDA;
-    if (cgk_reset(c->sc, st) != 0) goto out;
-    if (cgk_init_residual(db, dAx, dr, dp, c->partials_vec, &c->sc->rr[0], c->sc, m, st) != 0) goto out;
+    if (cgk_reset(c->sc, c->gen, st) != 0) goto out;
+    if (cgk_init_residual(db, dAx, dr, dp, c->partials_vec, &c->sc->rr[0], c->sc, m, NULL, st) != 0) goto out;
     if (cudaMemcpyAsync(r, dr, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(p, dp, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
@@ -663,11 +835,11 @@ int cgb_op_xr_update(cgb_ctx *c, double rho, double pAp, double *x, double *r, c
         (rc = dev_dup(&dp, p, m, st)) || (rc = dev_dup(&dAp, Ap, m, st)))
         goto out;
     rc = CGB_ERR_CUDA;
-    if (cgk_reset(c->sc, st) != 0) goto out;
+    if (cgk_reset(c->sc, c->gen, st) != 0) goto out;
     memset(c->h_sc, 0, sizeof *c->h_sc);
     c->h_sc->rr[0] = rho; c->h_sc->pAp = pAp; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
     if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
-    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, m, st) != 0) goto out;
+    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, m, NULL, st) != 0) goto out;
     if (cudaMemcpyAsync(x, dx, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(r, dr, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
@@ -693,7 +865,7 @@ int cgb_op_p_update(cgb_ctx *c, double rho, double beta, double eps, double *p, 
     memset(c->h_sc, 0, sizeof *c->h_sc);
     c->h_sc->rr[0] = rho; c->h_sc->rr[1] = beta; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
     if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
-    if (cgk_p_update(dp, dr, c->sc, 0, eps, 0, (int64_t)1 << 40, m, st) != 0) goto out;
+    if (cgk_p_update(dp, dr, c->sc, 0, eps, 0, (int64_t)1 << 40, m, NULL, st) != 0) goto out;
     if (cudaMemcpyAsync(p, dp, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaStreamSynchronize(st) != cudaSuccess) goto out;

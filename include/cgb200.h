@@ -35,6 +35,7 @@ extern "C" {
 #define CGB_ERR_NOMEM         -5   /* host or device allocation failed (:140-144)     */
 #define CGB_ERR_STATE         -6   /* no problem loaded / wrong call order            */
 #define CGB_ERR_IO            -7   /* text input missing, short or malformed          */
+#define CGB_ERR_COMM          -8   /* a peer rank stopped answering during a solve    */
 
 #define CGB_EPSILON 1.0e-6         /* serialConjugate.c:28, parallel_cg.c:29          */
 
@@ -45,6 +46,12 @@ extern "C" {
 #define CGB_GEMV_AUTO 0
 #define CGB_GEMV_LDG  1            /* 128/256-bit streaming loads, registers          */
 #define CGB_GEMV_BULK 2            /* cp.async.bulk (TMA engine) shared-memory ring   */
+
+/* How the ranks exchange p and the two dot scalars each iteration (what MPI_Allgather /
+ * MPI_Allreduce do in parallel_cg.c:290-294,313); every rank must pass the same value */
+#define CGB_COMM_AUTO 0            /* PEER when every rank could map every window, else NCCL */
+#define CGB_COMM_NCCL 1            /* ncclAllGather + 2 x ncclAllReduce between the kernels   */
+#define CGB_COMM_PEER 2            /* fused: the kernels push over NVLink into peer memory    */
 
 typedef struct cgb_ctx cgb_ctx;    /* one per rank (= per GPU); owns all device state */
 
@@ -64,7 +71,8 @@ typedef struct cgb_options {
     int     gemv_vec;      /* LDG: doubles per load 1/2/4 (0 auto)                                 */
     int     gemv_stages;   /* BULK: ring depth (0 auto)                                            */
     int     gemv_tile_cols;/* BULK: columns per stage (0 auto)                                     */
-    int     reserved[4];
+    int     comm;          /* CGB_COMM_* (ranks > 1)                                               */
+    int     reserved[3];
 } cgb_options;
 
 typedef struct cgb_stats {
@@ -92,7 +100,8 @@ typedef struct cgb_stats {
     int     gemv_variant, gemv_rows, gemv_unroll, gemv_threads, gemv_vec, gemv_stages,
             gemv_tile_cols, gemv_grid;
     int     graph_chunk;       /* iterations per captured graph (0: stream mode)                   */
-    int     reserved[3];
+    int     comm;              /* CGB_COMM_NCCL / CGB_COMM_PEER as used (0 with one rank)          */
+    int     reserved[2];
 } cgb_stats;
 
 /* ---- library / device ------------------------------------------------------ */

@@ -123,6 +123,16 @@ def team_solve_generated(n, seed, ranks, flags=0, eps=1.0e-6, max_iter=None, ign
     return x, d
 
 
+def spd_with_condition(n, kappa, seed):
+    """Dense SPD test matrix with a log-spaced spectrum in [1, kappa] (Q diag(w) Q') and a
+    random right-hand side: CG needs ~sqrt(kappa) * ln(1/eps) iterations on it, unlike the
+    kappa ~ 1.5 systems of generateSPDmatrix.m that converge in ~5."""
+    rng = np.random.default_rng(seed)
+    Q, _ = np.linalg.qr(rng.standard_normal((n, n)))
+    A = (Q * np.logspace(0.0, np.log10(kappa), n)) @ Q.T
+    return np.ascontiguousarray(0.5 * (A + A.T)), rng.standard_normal(n)
+
+
 # ---------------------------------------------------------------- real reference
 def ref_available(kind, prec, n):
     return os.path.exists(os.path.join(REF_DIR, f"lib{kind}_{prec}_n{n}.so"))

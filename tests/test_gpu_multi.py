@@ -1,5 +1,5 @@
-"""Multi-GPU parity (row-sharded A, NCCL all-gather of p + all-reduce of the dot scalars,
-replacing parallel_cg.c:287-313).  Skipped on boxes with fewer GPUs than the case needs."""
+"""Multi-GPU parity (row-sharded A; the all-gather of p and the all-reduce of the dot scalars of
+parallel_cg.c:287-313 either as NCCL calls or fused into the kernels as peer-memory pushes).  Skipped on boxes with fewer GPUs than the case needs."""
 import os
 import subprocess
 import sys
@@ -29,9 +29,13 @@ def relerr(x, ref):
     return np.linalg.norm(x - ref) / np.linalg.norm(ref)
 
 
+COMMS = [1, 2]          # CGB_COMM_NCCL, CGB_COMM_PEER
+
+
+@pytest.mark.parametrize("comm", COMMS)
 @pytest.mark.parametrize("gpus", [2, 4, 8])
 @pytest.mark.parametrize("tag", ["g2", "g3", "g4"])
-def test_sharded_solve_matches_reference_mpi_golden(cg, golden, gpus, tag):
+def test_sharded_solve_matches_reference_mpi_golden(cg, golden, gpus, tag, comm):
     need(cg, gpus)
     c = golden["cases"][tag]
     n = c["n"]
@@ -41,26 +45,55 @@ def test_sharded_solve_matches_reference_mpi_golden(cg, golden, gpus, tag):
         A, b, x0 = unhex(c["A"]).reshape(n, n), unhex(c["b"]), unhex(c["x0"])
     else:
         A, b, x0 = O.gen_A(n, c["seed"]), O.gen_b(n, c["seed"]), np.zeros(n)
-    x, st = cg.conjugrad_host(A, b, x0, gpus=gpus)
+    x, st = cg.conjugrad_host(A, b, x0, gpus=gpus, comm=comm)
     want = unhex(c["x"][f"spmd{gpus}_f64"])       # the REAL parallel_cg.c (double build) over the MPI shim
     xo, so = O.conjugrad(A, b, x0, ranks=gpus)
     assert relerr(x, want) <= RTOL_X
     assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
-    assert st["ranks"] == gpus and st["m"] == n // gpus
+    assert st["ranks"] == gpus and st["m"] == n // gpus and st["comm"] == comm
+
+
+@pytest.mark.parametrize("comm", COMMS)
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_long_running_sharded_solve(cg, gpus, comm):
+    # ~85 iterations: epochs, slot parity and the replayed graph of the fused exchange
+    need(cg, gpus)
+    n = 512
+    A, b = O.spd_with_condition(n, 100.0, seed=5)
+    for use_graph in (1, 0):
+        x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus, comm=comm, use_graph=use_graph)
+        xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
+        assert so["iterations"] > 40 and st["comm"] == comm
+        assert relerr(x, xo) <= RTOL_X
+        assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
 
 
 @pytest.mark.parametrize("gpus", [2, 4, 8])
-def test_generated_sharded_solve(cg, gpus):
+def test_peer_exchange_is_bitwise_reproducible_and_rank_ordered(cg, gpus):
+    # the mailbox sums add the partials in rank order on every rank: two runs agree bit for bit,
+    # and so do the iteration counts of all ranks (else the solve would dead-lock or diverge)
+    need(cg, gpus)
+    n, seed = 2048, 77
+    x1, st1 = cg.solve_generated(n, seed, gpus=gpus, comm=2, ignore_stop=1, max_iter=9)
+    x2, st2 = cg.solve_generated(n, seed, gpus=gpus, comm=2, ignore_stop=1, max_iter=9)
+    assert st1["iterations"] == st2["iterations"] == 9
+    np.testing.assert_array_equal(x1, x2)
+    assert st1["final_beta"] == st2["final_beta"]
+
+
+@pytest.mark.parametrize("comm", COMMS)
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_generated_sharded_solve(cg, gpus, comm):
     need(cg, gpus)
     n, seed = 4096, 31
-    x, st = cg.solve_generated(n, seed, gpus=gpus)
+    x, st = cg.solve_generated(n, seed, gpus=gpus, comm=comm)
     xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n), ranks=gpus)
     assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
     x1, st1 = cg.solve_generated(n, seed, gpus=1)
     assert relerr(x, x1) <= RTOL_X
     # fixed-iteration mode across ranks: every rank stops at the same count
-    x, st = cg.solve_generated(n, seed, gpus=gpus, ignore_stop=1, max_iter=7)
-    assert st["iterations"] == 7
+    x, st = cg.solve_generated(n, seed, gpus=gpus, ignore_stop=1, max_iter=7, comm=comm)
+    assert st["iterations"] == 7 and st["comm"] == comm
 
 
 def test_not_divisible(cg):
@@ -98,3 +131,5 @@ def test_torchrun_bench_two_ranks(cg):
     import json
     line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert line["n_gpus"] == 2 and line["value"] > 0 and line["e2e"]["value"] > 0
+    # one process per GPU: the windows are mapped through CUDA IPC
+    assert "peer" in line["config"]["exchange"]

@@ -154,6 +154,20 @@ def test_generated_solve_vs_oracle(ctx, n, graph, chunk):
     assert abs(st["rsold0"] - so["rsold0"]) <= 1e-12 * so["rsold0"]
 
 
+@pytest.mark.parametrize("n,kappa,variant", [(512, 100.0, 1), (512, 100.0, 2), (1000, 30.0, 1)])
+def test_long_running_solve_on_ill_conditioned_matrix(ctx, n, kappa, variant):
+    # ~50-90 iterations (generateSPDmatrix-style systems stop after ~5): the device-side stop
+    # flag, the rr[] ping-pong and the graph chunking over many replays.  Summation-order
+    # sensitivity of CG at kappa = 100 is ~5e-12 (serial vs SPMD oracle), inside 1e-10.
+    A, b = O.spd_with_condition(n, kappa, seed=n)
+    ctx.load_host(A, b, np.zeros(n))
+    st = ctx.solve(gemv_variant=variant)
+    xo, so = O.conjugrad(A, b, np.zeros(n))
+    assert so["iterations"] > 40
+    assert relerr(ctx.read_x(), xo) <= RTOL_X
+    assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
+
+
 def test_nonzero_initial_guess_and_restart(ctx):
     n, seed = 768, 9
     A, b = O.gen_A(n, seed), O.gen_b(n, seed)
