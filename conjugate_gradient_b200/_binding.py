@@ -14,6 +14,13 @@ HEADER = os.path.join(ROOT, "include", "cgb200.h")
 
 CGB_EPSILON = 1.0e-6          # serialConjugate.c:28
 GEN_ROUND4 = 1
+
+
+def GEN_KAPPA_LOG2(k):
+    """cgb200.h CGB_GEN_KAPPA_LOG2: generator family with condition number ~2^k."""
+    return (int(k) & 0x3F) << 8
+
+
 GEMV_AUTO, GEMV_LDG, GEMV_BULK = 0, 1, 2
 COMM_AUTO, COMM_NCCL, COMM_PEER = 0, 1, 2
 
@@ -29,7 +36,7 @@ class Options(C.Structure):
                 ("use_graph", C.c_int), ("check_every", C.c_int), ("time_gemv", C.c_int),
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
-                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("reserved", C.c_int * 3)]
+                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("reserved", C.c_int * 2)]
 
 
 class Stats(C.Structure):
@@ -43,7 +50,7 @@ class Stats(C.Structure):
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
                 ("gemv_tile_cols", C.c_int), ("gemv_grid", C.c_int), ("graph_chunk", C.c_int),
-                ("comm", C.c_int), ("reserved", C.c_int * 2)]
+                ("comm", C.c_int), ("exit_reason", C.c_int), ("reserved", C.c_int * 1)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

@@ -1,0 +1,214 @@
+/* cg_ingest.cu -- text -> FP64 conversion ON the GPU for the reference's input files.
+ *
+ * Replaces initialize() (serialConjugate.c:85-105, parallel_cg.c:147-168: fscanf("%f%*c") per
+ * value on one host core, >95 % of the reference's published wall time)
+ * for the rank's row block of matrixA.txt: the host only moves BYTES (page cache -> pinned
+ * buffer -> HBM); tokenising and decimal->binary conversion run here, HBM-bound byte work:
+ *
+ *   ingest_count   16 bytes per thread (one 128-bit load): bitmask of token starts (a
+ *                  non-separator byte whose predecessor is a separator), popcount, CTA sum
+ *   ingest_scan    exclusive scan of the CTA sums, continued from the previous chunk's total
+ *   ingest_parse   the same masks -> every token start knows its value index; the token is
+ *                  converted with Clinger's exact fast path (integer mantissa < 10^15 times or
+ *                  divided by 10^k, k <= 22: ONE correctly rounded IEEE operation = strtod's
+ *                  result bit for bit) and stored at dst[index]
+ *
+ * Tokens outside the fast path (more than 15 significant digits, large exponents, inf/nan,
+ * hex floats, stray characters, a UTF-8 BOM) are not guessed at: their positions go to an
+ * exception list that the host resolves with strtod (cg_ingest.c), so the accepted grammar
+ * and every produced bit are those of the host parser in cg_io.c.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "cg_kernels.h"
+
+#define ING_NT 256
+#define ING_BYTES_PER_THREAD 16
+
+__constant__ double c_pow10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
+                                   1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+
+__device__ __forceinline__ bool ing_is_sep(unsigned int ch)
+{
+    return ch == ' ' || ch == '\t' || ch == '\n' || ch == '\r' || ch == ',' || ch == ';' || ch == '\f' || ch == '\v';
+}
+
+/* bit j set: byte 16*t + j starts a token.  `txt` is padded with separators to a multiple
+ * of 16 (plus slack for the parser's look-ahead). */
+__device__ __forceinline__ unsigned int ing_start_mask(const unsigned char *txt, long long t)
+{
+    const uint4 w = *reinterpret_cast<const uint4 *>(txt + t * ING_BYTES_PER_THREAD);
+    const unsigned int words[4] = {w.x, w.y, w.z, w.w};
+    bool prev_sep = (t == 0) ? true : ing_is_sep(txt[t * ING_BYTES_PER_THREAD - 1]);
+    unsigned int mask = 0u;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const unsigned int ch = (words[j >> 2] >> ((j & 3) * 8)) & 0xffu;
+        const bool sep = ing_is_sep(ch);
+        if (!sep && prev_sep) mask |= 1u << j;
+        prev_sep = sep;
+    }
+    return mask;
+}
+
+__global__ void __launch_bounds__(ING_NT)
+ingest_count_kernel(const unsigned char *__restrict__ txt, long long n16, unsigned int *__restrict__ block_counts)
+{
+    const long long t = (long long)blockIdx.x * ING_NT + threadIdx.x;
+    unsigned int c = (t < n16) ? __popc(ing_start_mask(txt, t)) : 0u;
+    __shared__ unsigned int s_w[ING_NT / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int s = 0;
+#pragma unroll
+        for (int q = 0; q < ING_NT / 32; ++q) s += s_w[q];
+        block_counts[blockIdx.x] = s;
+    }
+}
+
+/* One CTA: block_offsets[b] = state->base + sum_{q<b} block_counts[q]; state->base += total. */
+__global__ void __launch_bounds__(1024)
+ingest_scan_kernel(const unsigned int *__restrict__ block_counts, long long *__restrict__ block_offsets,
+                   int nblocks, cgk_ingest_state *state)
+{
+    __shared__ long long s_part[1024];
+    const int tid = threadIdx.x;
+    const int per = (nblocks + 1023) / 1024;
+    const int lo = tid * per, hi = min(lo + per, nblocks);
+    long long s = 0;
+    for (int i = lo; i < hi; ++i) s += block_counts[i];
+    s_part[tid] = s;
+    __syncthreads();
+    /* Hillis-Steele inclusive scan over the 1024 partial sums */
+    for (int o = 1; o < 1024; o <<= 1) {
+        const long long add = (tid >= o) ? s_part[tid - o] : 0;
+        __syncthreads();
+        s_part[tid] += add;
+        __syncthreads();
+    }
+    const long long base = state->base;
+    long long run = base + (tid == 0 ? 0 : s_part[tid - 1]);
+    for (int i = lo; i < hi; ++i) { block_offsets[i] = run; run += block_counts[i]; }
+    __syncthreads();
+    if (tid == 1023) state->base = base + s_part[1023];
+}
+
+/* Token at p (first byte is not a separator; the text ends with >= 64 separator bytes).
+ * Returns true and *out when the token is a plain decimal number inside the exact fast path. */
+__device__ __forceinline__ bool ing_parse(const unsigned char *p, double *out)
+{
+    const unsigned char *s = p;
+    bool neg = false;
+    if (*s == '+' || *s == '-') { neg = (*s == '-'); ++s; }
+    unsigned long long w = 0ull;
+    int digits = 0, sig = 0, exp10 = 0;
+    bool seen_point = false;
+    for (;; ++s) {
+        const unsigned int d = (unsigned int)*s - (unsigned int)'0';
+        if (d <= 9u) {
+            ++digits;
+            if (w != 0ull || d != 0u) {
+                if (++sig > 15) return false;
+                w = w * 10ull + d;
+            }
+            if (seen_point) --exp10;
+        } else if (*s == '.' && !seen_point) seen_point = true;
+        else break;
+    }
+    if (digits == 0) return false;
+    if (*s == 'e' || *s == 'E') {
+        const unsigned char *t = s + 1;
+        bool eneg = false;
+        int ev = 0, ed = 0;
+        if (*t == '+' || *t == '-') { eneg = (*t == '-'); ++t; }
+        for (; (unsigned int)*t - (unsigned int)'0' <= 9u; ++t) { if (ev < 10000) ev = ev * 10 + (int)(*t - '0'); ++ed; }
+        if (ed == 0) return false;
+        exp10 += eneg ? -ev : ev;
+        s = t;
+    }
+    if (!ing_is_sep(*s)) return false;                       /* trailing characters */
+    if (w == 0ull) { *out = neg ? -0.0 : 0.0; return true; }
+    if (exp10 < -22 || exp10 > 22) return false;
+    double v = __ull2double_rn(w);                           /* exact: w < 10^15 < 2^53 */
+    v = exp10 < 0 ? __ddiv_rn(v, c_pow10[-exp10]) : __dmul_rn(v, c_pow10[exp10]);
+    *out = neg ? -v : v;
+    return true;
+}
+
+__global__ void __launch_bounds__(ING_NT)
+ingest_parse_kernel(const unsigned char *__restrict__ txt, long long n16, long long abs_pos,
+                    const long long *__restrict__ block_offsets, double *__restrict__ dst,
+                    long long cap, cgk_ingest_state *state, unsigned long long *__restrict__ exc_pos,
+                    long long *__restrict__ exc_idx, unsigned int exc_cap)
+{
+    const long long t = (long long)blockIdx.x * ING_NT + threadIdx.x;
+    unsigned int mask = (t < n16) ? ing_start_mask(txt, t) : 0u;
+    /* exclusive prefix of the per-thread token counts inside the CTA */
+    const unsigned int cnt = __popc(mask);
+    unsigned int incl = cnt;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    __shared__ unsigned int s_w[ING_NT / 32];
+    if (lane == 31) s_w[wid] = incl;
+    __syncthreads();
+    unsigned int warp_base = 0;
+    for (int q = 0; q < wid; ++q) warp_base += s_w[q];
+    long long idx = block_offsets[blockIdx.x] + warp_base + (incl - cnt);
+    while (mask) {
+        const int j = __ffs(mask) - 1;
+        mask &= mask - 1u;
+        if (idx < cap) {
+            const unsigned char *p = txt + t * ING_BYTES_PER_THREAD + j;
+            double v;
+            if (ing_parse(p, &v)) dst[idx] = v;
+            else {
+                const unsigned int e = atomicAdd(&state->exc_count, 1u);
+                if (e < exc_cap) { exc_pos[e] = (unsigned long long)(abs_pos + t * ING_BYTES_PER_THREAD + j); exc_idx[e] = idx; }
+            }
+        }
+        ++idx;
+    }
+}
+
+__global__ void scatter_kernel(double *__restrict__ dst, const long long *__restrict__ idx,
+                               const double *__restrict__ val, long long count)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) dst[idx[i]] = val[i];
+}
+
+extern "C" int64_t cgk_ingest_blocks(int64_t padded_len)
+{
+    const int64_t n16 = padded_len / ING_BYTES_PER_THREAD;
+    return (n16 + ING_NT - 1) / ING_NT;
+}
+
+extern "C" int cgk_ingest_chunk(const unsigned char *txt, int64_t padded_len, int64_t abs_pos, double *dst,
+                                int64_t cap, unsigned int *block_counts, long long *block_offsets,
+                                cgk_ingest_state *state, unsigned long long *exc_pos, long long *exc_idx,
+                                unsigned int exc_cap, void *stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long n16 = padded_len / ING_BYTES_PER_THREAD;
+    const int nb = (int)cgk_ingest_blocks(padded_len);
+    if (nb < 1) return 0;
+    ingest_count_kernel<<<nb, ING_NT, 0, st>>>(txt, n16, block_counts);
+    ingest_scan_kernel<<<1, 1024, 0, st>>>(block_counts, block_offsets, nb, state);
+    ingest_parse_kernel<<<nb, ING_NT, 0, st>>>(txt, n16, (long long)abs_pos, block_offsets, dst, (long long)cap,
+                                              state, exc_pos, exc_idx, exc_cap);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_scatter(double *dst, const long long *idx, const double *val, int64_t count, void *stream)
+{
+    if (count < 1) return 0;
+    scatter_kernel<<<(unsigned int)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dst, idx, val, (long long)count);
+    return (int)cudaGetLastError();
+}

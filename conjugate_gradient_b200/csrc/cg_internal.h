@@ -13,7 +13,7 @@ struct cgb_graph_key {
     cgk_gemv_plan plan;
     const void *A;
     const void *win;        /* peer window the captured kernels point into */
-    int comm, pad_;
+    int comm, guard;
 };
 
 struct cgb_ctx {

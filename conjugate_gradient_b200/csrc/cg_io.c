@@ -338,7 +338,12 @@ static void *fmt_main(void *arg)
 
 int cgb_write_values(const char *path, const double *v, int64_t count, int fmt_decimals)
 {
-    FILE *f = fopen(path, "w");
+    return cgb_write_values_mode(path, v, count, fmt_decimals, 0);
+}
+
+int cgb_write_values_mode(const char *path, const double *v, int64_t count, int fmt_decimals, int append)
+{
+    FILE *f = fopen(path, append ? "a" : "w");
     if (!f) return CGB_ERR_IO;
     int rc = CGB_OK;
     const int64_t slab = (int64_t)1 << 22;                 /* values per round: bounds the buffers */

@@ -13,6 +13,8 @@ extern "C" {
 #endif
 /* printer() (serialConjugate.c:260-276): "%f  " per element, newline after the last column. */
 void cgb_print_vector(FILE *out, const double *v, int64_t rows, int64_t cols);
+/* cgb_write_values() with the choice to append (row blocks of a matrix written in turn). */
+int cgb_write_values_mode(const char *path, const double *v, int64_t count, int fmt_decimals, int append);
 #ifdef __cplusplus
 }
 #endif

@@ -730,7 +730,7 @@ __global__ void __launch_bounds__(VEC_NT)
 xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
                  const double *p_loc, const double *__restrict__ Ap,
                  double *__restrict__ partials, double *__restrict__ rr_out,
-                 cgk_scalars *sc, int cur, long long m, const cgk_peers peers)
+                 cgk_scalars *sc, int cur, int guard, long long m, const cgk_peers peers)
 {
     if (*(volatile int *)&sc->stop_req) return;
     unsigned int ep = 0u, gen = 0u;
@@ -743,6 +743,12 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
         pAp = sc->pAp;
     }
     const double alpha = sc->rr[cur] / pAp;
+    if (guard && !isfinite(alpha)) {
+        /* every thread of every rank sees the same alpha: all leave x, r alone.  Later kernels
+         * read the flags (p_update of this iteration: breakdown; the next GEMV: stop_req). */
+        if (blockIdx.x == 0 && threadIdx.x == 0) { sc->breakdown = 3; sc->stop_req = 3; sc->pAp = pAp; }
+        return;
+    }
     double s = 0.0;
     for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
          i += (long long)gridDim.x * VEC_NT) {
@@ -780,7 +786,7 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
                 cgk_scalars *sc, int cur, double eps, int ignore_stop,
                 long long max_iter, long long m, const cgk_peers peers)
 {
-    if (*(volatile int *)&sc->stopped) return;
+    if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
     unsigned int ep = 0u, gen = 0u;
     const double rho = sc->rr[cur];
     double beta;
@@ -841,10 +847,11 @@ __global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
     sc->ticket_gemv = 0u; sc->ticket_vec = 0u;
     sc->gen = gen; sc->ep_gemv = sc->ep_xr = sc->ep_p = 0u;
     sc->comm_error = 0;
+    sc->breakdown = 0;
 }
 
 template <bool COMM>
-__global__ void after_init_kernel(cgk_scalars *sc, const cgk_peers peers)
+__global__ void after_init_kernel(cgk_scalars *sc, int guard, const cgk_peers peers)
 {
     if constexpr (COMM) {
         const unsigned int gen = *(volatile unsigned int *)&sc->gen;
@@ -855,6 +862,9 @@ __global__ void after_init_kernel(cgk_scalars *sc, const cgk_peers peers)
     if (threadIdx.x == 0) {
         sc->rsold0 = sc->rr[0];
         sc->final_beta = sc->rr[0];
+        /* guard: x0 already solves the system exactly -> nothing to iterate (the reference
+         * would divide 0/0 in its first iteration, parallel_cg.c:298) */
+        if (guard && sc->rr[0] == 0.0) { sc->breakdown = 4; sc->stop_req = 4; }
     }
 }
 
@@ -863,7 +873,18 @@ __device__ __forceinline__ double gen_elem(uint64_t key, uint64_t n, uint64_t i,
                                            unsigned flags)
 {
     double val = 0.5 * (cgb_gen_u(key, i * n + j) + cgb_gen_u(key, j * n + i));
-    if (i == j) val = __dadd_rn(val, (double)n);
+    if (i == j) {
+        /* n*I (generateSPDmatrix.m:17), or with CGB_GEN_KAPPA_LOG2(k) the spread diagonal
+         * n*(1 + (2^k - 1) t^2), t = i/(n-1): every operation individually rounded, so the
+         * CPU twin reproduces the bits; k = 0 gives exactly n */
+        const unsigned k = (flags >> 8) & 0x3fu;
+        double d = 1.0;
+        if (k != 0u && n > 1) {
+            const double t = __ddiv_rn((double)i, (double)(n - 1));
+            d = __dadd_rn(1.0, __dmul_rn(__dsub_rn(ldexp(1.0, (int)k), 1.0), __dmul_rn(t, t)));
+        }
+        val = __dadd_rn(val, __dmul_rn((double)n, d));
+    }
     if (flags & CGB_GEN_ROUND4) val = __ddiv_rn(rint(__dmul_rn(val, 1.0e4)), 1.0e4);
     return val;
 }
@@ -1143,15 +1164,15 @@ extern "C" int cgk_init_residual(const double *b, const double *Ax, double *r, d
 }
 
 extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
-                             double *partials, double *rr_out, cgk_scalars *sc, int cur,
+                             double *partials, double *rr_out, cgk_scalars *sc, int cur, int guard,
                              int64_t m, const cgk_peers *peers, void *stream)
 {
     if (peers)
         xr_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                                sc, cur, (long long)m, *peers);
+                                                                                sc, cur, guard, (long long)m, *peers);
     else
         xr_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                                 sc, cur, (long long)m, k_no_peers);
+                                                                                 sc, cur, guard, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
 
@@ -1174,10 +1195,10 @@ extern "C" int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream)
     return (int)cudaGetLastError();
 }
 
-extern "C" int cgk_after_init(cgk_scalars *sc, const cgk_peers *peers, void *stream)
+extern "C" int cgk_after_init(cgk_scalars *sc, int guard, const cgk_peers *peers, void *stream)
 {
-    if (peers) after_init_kernel<true><<<1, 32, 0, (cudaStream_t)stream>>>(sc, *peers);
-    else after_init_kernel<false><<<1, 32, 0, (cudaStream_t)stream>>>(sc, k_no_peers);
+    if (peers) after_init_kernel<true><<<1, 32, 0, (cudaStream_t)stream>>>(sc, guard, *peers);
+    else after_init_kernel<false><<<1, 32, 0, (cudaStream_t)stream>>>(sc, guard, k_no_peers);
     return (int)cudaGetLastError();
 }
 

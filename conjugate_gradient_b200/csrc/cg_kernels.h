@@ -39,7 +39,8 @@ typedef struct cgk_scalars {
     unsigned int gen;      /* solve generation: high bits of every tag, set by cgk_reset      */
     unsigned int ep_gemv, ep_xr, ep_p;
     int comm_error;        /* a spin on a peer's flag ran into CGK_SPIN_TIMEOUT_NS            */
-    int pad_;
+    int breakdown;         /* guard mode only: 3 = alpha not finite (p.Ap = 0), 4 = r0.r0 = 0;   */
+                           /* written by cgk_xr_update / cgk_after_init, read by LATER kernels  */
 } cgk_scalars;
 
 /* ---- peer-memory exchange over NVLink (replaces MPI_Allgather(p) parallel_cg.c:290-291 and the
@@ -117,9 +118,11 @@ int cgk_init_residual(const double *b, const double *Ax, double *r, double *p_lo
                       double *partials, double *rr_out, cgk_scalars *sc, int64_t m,
                       const cgk_peers *peers, void *stream);
 
-/* alpha = rr[cur]/pAp; x += alpha p; r -= alpha Ap; r.r partials -> *rr_out. */
+/* alpha = rr[cur]/pAp; x += alpha p; r -= alpha Ap; r.r partials -> *rr_out.
+ * guard != 0 (not in the reference, which iterates NaNs to the loop bound):
+ * a non-finite alpha leaves x and r untouched and ends the solve (stop_req = breakdown = 3). */
 int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
-                  double *partials, double *rr_out, cgk_scalars *sc, int cur,
+                  double *partials, double *rr_out, cgk_scalars *sc, int cur, int guard,
                   int64_t m, const cgk_peers *peers, void *stream);
 
 /* beta = rr[cur^1]: bookkeeping + stop rule on thread 0; p = r + (beta/rho) p. */
@@ -131,7 +134,7 @@ int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, doubl
 int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream);
 /* rr[0] bookkeeping after the initial all-reduce (peers != NULL: it IS the all-reduce --
  * gathers the ranks' r.r partials from the local mailbox). */
-int cgk_after_init(cgk_scalars *sc, const cgk_peers *peers, void *stream);
+int cgk_after_init(cgk_scalars *sc, int guard, const cgk_peers *peers, void *stream);
 
 /* Rows [row0,row0+m) of the seeded SPD matrix into A (m x n); b rows likewise. */
 int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
@@ -141,6 +144,26 @@ int cgk_generate_b(double *b, int64_t n, int64_t row0, int64_t m, uint64_t seed,
 
 /* Writes `bytes` of zeros-then-ones traffic over buf: evicts L2 between timed launches. */
 int cgk_l2_flush(void *buf, int64_t bytes, void *stream);
+
+/* ---- text ingest (cg_ingest.cu): the rank's part of matrixA.txt parsed on the GPU */
+typedef struct cgk_ingest_state {
+    long long base;            /* values produced by the chunks so far (next chunk's first index) */
+    unsigned int exc_count;    /* tokens left to the host (outside the exact fast path)           */
+    unsigned int pad_;
+} cgk_ingest_state;
+/* CTAs (= entries of block_counts / block_offsets) a chunk of `padded_len` bytes needs. */
+int64_t cgk_ingest_blocks(int64_t padded_len);
+/* One chunk of text already in device memory: `txt` holds whole tokens, starts at a token or
+ * separator, is padded with separator bytes to `padded_len` (a multiple of 16) and followed by
+ * at least 64 more separator bytes.  Values land at dst[state->base ...] (indices >= cap are
+ * counted but not stored); `abs_pos` is the chunk's byte offset in the file, reported back in
+ * exc_pos[] for tokens the host has to convert. */
+int cgk_ingest_chunk(const unsigned char *txt, int64_t padded_len, int64_t abs_pos, double *dst,
+                     int64_t cap, unsigned int *block_counts, long long *block_offsets,
+                     cgk_ingest_state *state, unsigned long long *exc_pos, long long *exc_idx,
+                     unsigned int exc_cap, void *stream);
+/* dst[idx[i]] = val[i] (the host-converted exceptions). */
+int cgk_scatter(double *dst, const long long *idx, const double *val, int64_t count, void *stream);
 
 const char *cgk_error_string(int err);
 

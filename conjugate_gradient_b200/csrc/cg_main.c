@@ -19,11 +19,21 @@
  *   --write-x FILE    write x one value per line ("%.17g"): usable as initialguess
  *   --gen N           no input files: seeded on-device SPD system of order N
  *   --seed S          generator seed (default 20170209)   --round4  "%.4f" rounding
+ *   --kappa-log2 K    generator: spread the diagonal so that cond(A) ~ 2^K (K = 0: the
+ *                     reference's kappa ~ 1.5 family, ~5 iterations)
  *   --bench-iters K   fixed-iteration timing mode (stop test recorded, not acted on)
  *   --gemv V          1 = streaming loads, 2 = bulk-async ring
  *   --comm nccl|peer  per-iteration exchange with --gpus > 1 (default: peer when the GPUs
  *                     can map each other's memory: fused NVLink pushes, else NCCL)
  *   --stats           extra lines: iterations, residual, GEMV GB/s
+ *   --emit-files P    with --gen: also write the system in generateSPDmatrix.m's file format
+ *                     (generateSPDmatrix.m:23-43: one value per line, A and b "%.4f", x0 "%.1f")
+ *                     as P_matrix.txt, P_vector.txt, P_x0.txt and P_dimensions.txt; implies
+ *                     --round4 so that the files hold exactly the system that is solved
+ *   --guard           end the solve on p.Ap = 0 / exact x0 instead of iterating NaNs to the
+ *                     loop bound as the reference does (parallel_cg.c:298,318)
+ *   --run-record FILE machine-readable record of the run (JSON: iterations, sqrt(r.r), exit
+ *                     reason, timings, GB/s) -- the reference reports only a time
  */
 #define _GNU_SOURCE
 #include <math.h>
@@ -39,8 +49,8 @@
 #include "cg_io.h"
 
 typedef struct {
-    const char *fileA, *fileB, *fileX, *dims, *write_x;
-    int gpus, print_x, stats, round4, gemv, comm;
+    const char *fileA, *fileB, *fileX, *dims, *write_x, *record, *emit;
+    int gpus, print_x, stats, round4, gemv, comm, kappa_log2, guard;
     int64_t gen_n, max_iter, bench_iters;
     uint64_t seed;
     double eps;
@@ -59,9 +69,12 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         if (!strcmp(a, "--print-x")) c->print_x = 1;
         else if (!strcmp(a, "--stats")) c->stats = 1;
         else if (!strcmp(a, "--round4")) c->round4 = 1;
+        else if (!strcmp(a, "--guard")) c->guard = 1;
         else if (!v) { fprintf(stderr, "option %s needs a value\n", a); return -1; }
         else if (!strcmp(a, "--dims")) { c->dims = v; ++i; }
         else if (!strcmp(a, "--write-x")) { c->write_x = v; ++i; }
+        else if (!strcmp(a, "--run-record")) { c->record = v; ++i; }
+        else if (!strcmp(a, "--emit-files")) { c->emit = v; c->round4 = 1; ++i; }
         else if (!strcmp(a, "--gpus")) { c->gpus = atoi(v); ++i; }
         else if (!strcmp(a, "--eps")) { c->eps = atof(v); ++i; }
         else if (!strcmp(a, "--max-iter")) { c->max_iter = atoll(v); ++i; }
@@ -69,6 +82,7 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         else if (!strcmp(a, "--seed")) { c->seed = strtoull(v, NULL, 10); ++i; }
         else if (!strcmp(a, "--bench-iters")) { c->bench_iters = atoll(v); ++i; }
         else if (!strcmp(a, "--gemv")) { c->gemv = atoi(v); ++i; }
+        else if (!strcmp(a, "--kappa-log2")) { c->kappa_log2 = atoi(v); ++i; }
         else if (!strcmp(a, "--comm")) {
             if (!strcmp(v, "nccl")) c->comm = CGB_COMM_NCCL;
             else if (!strcmp(v, "peer")) c->comm = CGB_COMM_PEER;
@@ -81,6 +95,84 @@ static int parse_cli(int argc, char **argv, cli_t *c)
     c->fileA = pos[0]; c->fileB = pos[1]; c->fileX = pos[2];
     if (c->gen_n > 0) return npos == 0 ? 0 : -1;
     return npos == 3 ? 0 : -2;
+}
+
+static const char *exit_reason_name(int r)
+{
+    switch (r) {
+    case CGB_EXIT_STOP_RULE: return "stop_rule";
+    case CGB_EXIT_MAX_ITER: return "max_iter";
+    case CGB_EXIT_BREAKDOWN: return "breakdown";
+    case CGB_EXIT_EXACT_X0: return "exact_initial_guess";
+    default: return "none";
+    }
+}
+
+static int write_run_record(const char *path, const cli_t *cli, const cgb_stats *st, double total_s)
+{
+    FILE *f = fopen(path, "w");
+    if (!f) return -1;
+    const double it_s = (st->iterations > 0 && st->loop_ms > 0.0) ? 1.0e3 * (double)st->iterations / st->loop_ms : 0.0;
+    fprintf(f, "{\"n\": %lld, \"gpus\": %d, \"rows_per_gpu\": %lld, \"source\": \"%s\", \"seed\": %llu,\n",
+            (long long)st->n, st->ranks, (long long)st->m, cli->gen_n > 0 ? "generated" : "files",
+            (unsigned long long)cli->seed);
+    fprintf(f, " \"eps\": %.17g, \"iterations\": %lld, \"break_k\": %lld, \"exit\": \"%s\",\n",
+            cli->eps, (long long)st->iterations, (long long)st->break_k, exit_reason_name(st->exit_reason));
+    /* NaN / inf are not JSON: a broken-down unguarded run reports null */
+    if (isfinite(st->final_residual)) fprintf(f, " \"final_residual\": %.17g,", st->final_residual);
+    else fprintf(f, " \"final_residual\": null,");
+    if (isfinite(st->rsold0)) fprintf(f, " \"initial_rr\": %.17g,\n", st->rsold0);
+    else fprintf(f, " \"initial_rr\": null,\n");
+    fprintf(f, " \"solve_seconds\": %.9f, \"loop_ms\": %.6f, \"init_ms\": %.6f, \"h2d_seconds\": %.9f, \"total_cpu_seconds\": %.6f,\n",
+            st->solve_seconds, st->loop_ms, st->init_ms, st->h2d_seconds, total_s);
+    fprintf(f, " \"iterations_per_second\": %.6f, \"gemv_bytes_per_gpu\": %.0f, \"iteration_gbs_per_gpu\": %.3f,\n",
+            it_s, st->gemv_bytes, st->gemv_bytes * it_s * 1.0e-9);
+    fprintf(f, " \"exchange\": \"%s\", \"graph_chunk\": %d, \"kernel_launches\": %lld,\n",
+            st->comm == CGB_COMM_PEER ? "peer" : st->comm == CGB_COMM_NCCL ? "nccl" : "none", st->graph_chunk,
+            (long long)st->kernel_launches);
+    fprintf(f, " \"gemv\": {\"variant\": %d, \"rows\": %d, \"unroll\": %d, \"threads\": %d, \"vec\": %d, \"grid\": %d}}\n",
+            st->gemv_variant, st->gemv_rows, st->gemv_unroll, st->gemv_threads, st->gemv_vec, st->gemv_grid);
+    return fclose(f) == 0 ? 0 : -1;
+}
+
+/* The generated system as the text files generateSPDmatrix.m:23-43 writes (the row blocks come
+ * from the on-device generator, a slab of rows at a time). */
+static int emit_files(const cli_t *cli, int64_t n, unsigned flags)
+{
+    char path[4200];
+    cgb_ctx *ctx = NULL;
+    if (cgb_create(&ctx, 0) != CGB_OK) return -1;
+    int64_t slab = ((int64_t)1 << 25) / n;                 /* <= 256 MiB of doubles per slab */
+    if (slab < 1) slab = 1;
+    if (slab > n) slab = n;
+    double *rows = malloc((size_t)slab * (size_t)n * sizeof(double));
+    double *vec = malloc((size_t)n * sizeof(double));
+    int rc = (rows && vec) ? 0 : -1;
+    snprintf(path, sizeof path, "%s_matrix.txt", cli->emit);
+    for (int64_t r0 = 0; r0 < n && rc == 0; r0 += slab) {
+        const int64_t cnt = n - r0 < slab ? n - r0 : slab;
+        if (cgb_op_generate(ctx, n, r0, cnt, cli->seed, flags, rows, NULL) != CGB_OK ||
+            cgb_write_values_mode(path, rows, cnt * n, 4, r0 != 0) != CGB_OK) rc = -1;
+    }
+    if (rc == 0) {
+        snprintf(path, sizeof path, "%s_vector.txt", cli->emit);
+        if (cgb_op_generate(ctx, n, 0, n, cli->seed, flags, NULL, vec) != CGB_OK ||
+            cgb_write_values(path, vec, n, 4) != CGB_OK) rc = -1;
+    }
+    if (rc == 0) {
+        snprintf(path, sizeof path, "%s_x0.txt", cli->emit);
+        for (int64_t i = 0; i < n; ++i) vec[i] = 0.0;      /* generateSPDmatrix.m:8 */
+        if (cgb_write_values(path, vec, n, 1) != CGB_OK) rc = -1;
+    }
+    if (rc == 0) {
+        snprintf(path, sizeof path, "%s_dimensions.txt", cli->emit);
+        FILE *f = fopen(path, "w");
+        if (!f) rc = -1;
+        else { fprintf(f, "%lld\n%lld\n%lld\n1\n", (long long)n, (long long)n, (long long)n); fclose(f); }
+    }
+    free(rows); free(vec);
+    cgb_destroy(ctx);
+    return rc;
 }
 
 /* dimensions.txt lookup: --dims, ./dimensions.txt, <dir of A>/dimensions.txt */
@@ -120,6 +212,7 @@ int main(int argc, char **argv)
     opt.max_iter = cli.max_iter;
     opt.gemv_variant = cli.gemv;
     opt.comm = cli.comm;
+    opt.guard = cli.guard;
     if (cli.bench_iters > 0) { opt.ignore_stop = 1; opt.max_iter = cli.bench_iters; }
 
     cgb_stats st;
@@ -142,8 +235,13 @@ int main(int argc, char **argv)
         printf("Computing cg of matrix size : %lld\n", (long long)n * (long long)n);
         x = malloc((size_t)n * sizeof(double));
         if (!x) { printf("can't allocate memory for vector\n"); return 1; }
+        const unsigned gflags = (cli.round4 ? CGB_GEN_ROUND4 : 0u) | CGB_GEN_KAPPA_LOG2(cli.kappa_log2);
+        if (cli.emit && emit_files(&cli, n, gflags) != 0) {
+            fprintf(stderr, "cg_b200: cannot write the %s_* files: %s\n", cli.emit, cgb_last_error());
+            return 1;
+        }
         SOLVER_STDOUT_OFF();
-        rc = cgb_solve_generated(n, cli.seed, cli.round4 ? CGB_GEN_ROUND4 : 0u, cli.gpus, &opt, x, &st);
+        rc = cgb_solve_generated(n, cli.seed, gflags, cli.gpus, &opt, x, &st);
         SOLVER_STDOUT_ON();
     } else {
         int64_t dims[4];
@@ -203,6 +301,7 @@ int main(int argc, char **argv)
         printf("iterations: %lld\n", (long long)st.iterations);
         printf("loop index at break: %lld\n", (long long)st.break_k);
         printf("final residual sqrt(r.r): %.6e\n", st.final_residual);
+        printf("exit: %s\n", exit_reason_name(st.exit_reason));
         if (cli.gpus > 1) printf("exchange: %s\n", st.comm == CGB_COMM_PEER ? "peer (fused NVLink pushes)" : "nccl");
         if (st.iterations > 0 && st.loop_ms > 0.0) {
             double it_s = 1.0e3 * (double)st.iterations / st.loop_ms;
@@ -210,6 +309,10 @@ int main(int argc, char **argv)
             printf("iteration-level GEMV GB/s per GPU (8*(m*n+n+m) bytes / iteration time): %.1f\n",
                    st.gemv_bytes * it_s * 1.0e-9);
         }
+    }
+    if (cli.record && write_run_record(cli.record, &cli, &st, (double)(clock() - c0) / CLOCKS_PER_SEC) != 0) {
+        fprintf(stderr, "cg_b200: cannot write %s\n", cli.record);
+        return 1;
     }
     if (cli.write_x && cgb_write_values(cli.write_x, x, n, -1) != CGB_OK) {
         fprintf(stderr, "cg_b200: cannot write %s\n", cli.write_x);

@@ -479,7 +479,7 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
                          c->sc, c->m, c->n, &c->peers, st));                     /* :290-294 */
         if (ev_b) CU(cudaEventRecord(ev_b, st));
         KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec, &c->sc->rr_local, c->sc, cur,
-                         c->m, &c->peers, st));                                  /* :298-313 */
+                         o->guard, c->m, &c->peers, st));                                  /* :298-313 */
         KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, &c->peers, st)); /* :314-323 */
         c->launches += 3;
         return CGB_OK;
@@ -493,7 +493,7 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     if (multi)                                                   /* MPI_Allreduce(alpha), :294 */
         NC(ncclAllReduce(&c->sc->pAp_local, &c->sc->pAp, 1, ncclDouble, ncclSum, c->comm, st));
     KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec,
-                     multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, c->m, NULL, st)); /* :298-309 */
+                     multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, o->guard, c->m, NULL, st)); /* :298-309 */
     if (multi)                                                   /* MPI_Allreduce(beta), :313 */
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[cur ^ 1], 1, ncclDouble, ncclSum, c->comm, st));
     KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, NULL, st)); /* :314-323 */
@@ -506,7 +506,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     struct cgb_graph_key key;
     memset(&key, 0, sizeof key);
     key.n = c->n; key.m = c->m; key.max_iter = max_iter; key.eps = o->eps;
-    key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan;
+    key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan; key.guard = o->guard;
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
@@ -616,7 +616,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
                          multi ? &c->sc->rr_local : &c->sc->rr[0], c->sc, c->m, peers, st));
     if (multi && !peers)
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[0], 1, ncclDouble, ncclSum, c->comm, st));
-    KL(cgk_after_init(c->sc, peers, st));
+    KL(cgk_after_init(c->sc, o.guard, peers, st));
     c->launches += 4;
     CU(cudaEventRecord(c->ev[1], st));
 
@@ -682,6 +682,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->gemv_tile_cols = c->plan.tile_cols; stats->gemv_grid = c->plan.grid;
         stats->graph_chunk = chunk;
         stats->comm = c->comm_mode;
+        stats->exit_reason = c->h_sc->stop_req;
         if (gemv_pairs_used > 0) {
             double sum = 0.0, mn = 1e300;
             for (int i = 0; i < gemv_pairs_used; ++i) {
@@ -839,7 +840,7 @@ int cgb_op_xr_update(cgb_ctx *c, double rho, double pAp, double *x, double *r, c
     memset(c->h_sc, 0, sizeof *c->h_sc);
     c->h_sc->rr[0] = rho; c->h_sc->pAp = pAp; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
     if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
-    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, m, NULL, st) != 0) goto out;
+    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, 0, m, NULL, st) != 0) goto out;
     if (cudaMemcpyAsync(x, dx, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(r, dr, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;

@@ -41,6 +41,10 @@ extern "C" {
 
 /* generator flags */
 #define CGB_GEN_ROUND4 1u          /* mimic generateSPDmatrix.m's "%.4f" round trip   */
+/* Harder SPD family for iteration-bound runs: the n*I shift of generateSPDmatrix.m:17
+ * becomes n*diag(1 + (2^k - 1) t_i^2), t_i = i/(n-1), k in 1..63 (condition number ~2^k:
+ * k = 4 -> ~35 CG iterations, 7 -> ~100, 10 -> ~270 at eps = 1e-6).  k = 0: the reference's. */
+#define CGB_GEN_KAPPA_LOG2(k) (((unsigned)(k) & 0x3fu) << 8)
 
 /* GEMV kernel selection (0 = library default) */
 #define CGB_GEMV_AUTO 0
@@ -72,8 +76,16 @@ typedef struct cgb_options {
     int     gemv_stages;   /* BULK: ring depth (0 auto)                                            */
     int     gemv_tile_cols;/* BULK: columns per stage (0 auto)                                     */
     int     comm;          /* CGB_COMM_* (ranks > 1)                                               */
-    int     reserved[3];
+    int     guard;         /* 1: end the solve instead of iterating NaNs when p.Ap = 0 (alpha not  */
+                           /*    finite) or the initial residual is exactly 0.  Default 0 mirrors  */
+                           /*    the reference, which has no such test (parallel_cg.c:298,318)     */
+    int     reserved[2];
 } cgb_options;
+
+#define CGB_EXIT_STOP_RULE 1       /* sqrt(r.r) < eps                 (parallel_cg.c:314-317)  */
+#define CGB_EXIT_MAX_ITER  2       /* loop bound reached              (parallel_cg.c:288)      */
+#define CGB_EXIT_BREAKDOWN 3       /* guard: alpha = rho/p.Ap not finite                       */
+#define CGB_EXIT_EXACT_X0  4       /* guard: initial residual exactly zero                     */
 
 typedef struct cgb_stats {
     int64_t n, m;              /* order; rows owned by this rank (n / ranks, parallel_cg.c:83)     */
@@ -101,7 +113,8 @@ typedef struct cgb_stats {
             gemv_tile_cols, gemv_grid;
     int     graph_chunk;       /* iterations per captured graph (0: stream mode)                   */
     int     comm;              /* CGB_COMM_NCCL / CGB_COMM_PEER as used (0 with one rank)          */
-    int     reserved[2];
+    int     exit_reason;       /* CGB_EXIT_*                                                       */
+    int     reserved[1];
 } cgb_stats;
 
 /* ---- library / device ------------------------------------------------------ */

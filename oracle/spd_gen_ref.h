@@ -24,6 +24,11 @@
 #include <math.h>
 
 #define ORC_GEN_ROUND4 1u
+/* Harder family: bits 8..13 of the flags hold k; the n*I shift of
+ * generateSPDmatrix.m:17 becomes n*diag(1 + (2^k - 1) * t_i^2), t_i = i/(n-1), which spreads
+ * the spectrum over [~n, ~n*2^k] (still strictly diagonally dominant, hence SPD) so CG needs
+ * tens to hundreds of iterations instead of ~5.  k = 0 is the reference's construction. */
+#define ORC_GEN_KAPPA_LOG2(k) (((unsigned)(k) & 0x3fu) << 8)
 
 static inline uint64_t orc_mix64(uint64_t z)
 {
@@ -53,7 +58,19 @@ static inline double orc_gen_a(uint64_t key, uint64_t n, uint64_t i, uint64_t j,
                                unsigned flags)
 {
     double v = 0.5 * (orc_gen_u(key, i * n + j) + orc_gen_u(key, j * n + i));
-    if (i == j) v += (double)n;
+    if (i == j) {
+        unsigned k = (flags >> 8) & 0x3fu;
+        double scale = 1.0;
+        if (k && n > 1) {
+            double t = (double)i / (double)(n - 1);
+            double tt = t * t;
+            double span = (double)(1ULL << k) - 1.0;
+            double st = span * tt;
+            scale = 1.0 + st;
+        }
+        double shift = (double)n * scale;
+        v = v + shift;
+    }
     if (flags & ORC_GEN_ROUND4) v = orc_gen_round4(v);
     return v;
 }

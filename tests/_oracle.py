@@ -68,6 +68,11 @@ def _ptr(a):
     return a.ctypes.data_as(C.POINTER(ct))
 
 
+def GEN_KAPPA_LOG2(k):
+    """oracle/spd_gen_ref.h ORC_GEN_KAPPA_LOG2: the spread-diagonal family, cond(A) ~ 2^k."""
+    return (int(k) & 0x3F) << 8
+
+
 def gen_A(n, seed, flags=0, row0=0, m=None):
     m = n if m is None else m
     A = np.empty((m, n), dtype=np.float64)

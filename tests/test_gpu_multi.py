@@ -56,10 +56,12 @@ def test_sharded_solve_matches_reference_mpi_golden(cg, golden, gpus, tag, comm)
 @pytest.mark.parametrize("comm", COMMS)
 @pytest.mark.parametrize("gpus", [2, 4, 8])
 def test_long_running_sharded_solve(cg, gpus, comm):
-    # ~85 iterations: epochs, slot parity and the replayed graph of the fused exchange
+    # ~47 iterations: epochs, slot parity and the replayed graph of the fused exchange.
+    # kappa = 30: see test_gpu_parity.py (at kappa = 100 the reference's own serial and SPMD
+    # orders already differ by more than the 1e-10 bar)
     need(cg, gpus)
     n = 512
-    A, b = O.spd_with_condition(n, 100.0, seed=5)
+    A, b = O.spd_with_condition(n, 30.0, seed=5)
     for use_graph in (1, 0):
         x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus, comm=comm, use_graph=use_graph)
         xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
@@ -94,6 +96,19 @@ def test_generated_sharded_solve(cg, gpus, comm):
     # fixed-iteration mode across ranks: every rank stops at the same count
     x, st = cg.solve_generated(n, seed, gpus=gpus, ignore_stop=1, max_iter=7, comm=comm)
     assert st["iterations"] == 7 and st["comm"] == comm
+
+
+@pytest.mark.parametrize("comm", COMMS)
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_generated_spread_family_sharded(cg, gpus, comm):
+    # ~100 iterations on the on-device generator's cond ~ 2^7 family, every GPU its own rows
+    need(cg, gpus)
+    n, seed, flags = 2048, 23, cg.GEN_KAPPA_LOG2(7)
+    x, st = cg.solve_generated(n, seed, gpus=gpus, flags=flags, comm=comm)
+    xo, so = O.conjugrad(O.gen_A(n, seed, flags), O.gen_b(n, seed, flags), np.zeros(n), ranks=gpus)
+    assert so["iterations"] > 80
+    assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    assert st["final_residual"] < EPS and st["comm"] == comm
 
 
 def test_not_divisible(cg):

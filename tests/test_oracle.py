@@ -126,3 +126,22 @@ def test_generator_construction_matches_generateSPDmatrix():
     Ar = O.gen_A(n, seed, O.GEN_ROUND4)
     assert np.abs(Ar - A).max() <= 0.5e-4 + 1e-12 and (Ar == Ar.T).all()
     assert np.allclose(Ar * 1e4, np.rint(Ar * 1e4), atol=1e-6)
+
+
+def test_generator_spread_family_is_spd_with_prescribed_condition():
+    # n*I -> n*diag(1 + (2^k - 1) t^2); k = 0 is the reference's matrix
+    n, seed = 256, 99
+    assert O.gen_A(n, seed, O.GEN_KAPPA_LOG2(0)).tobytes() == O.gen_A(n, seed).tobytes()
+    iters = []
+    for k in (4, 7):
+        A = O.gen_A(n, seed, O.GEN_KAPPA_LOG2(k))
+        assert (A == A.T).all()
+        d = np.diag(A)
+        assert abs(d[0] - n) < 1.0 and abs(d[-1] - n * 2.0 ** k) < 1.0 and (np.diff(d) > -1.0).all()
+        w = np.linalg.eigvalsh(A)
+        assert w[0] > 0 and 0.5 * 2 ** k < w[-1] / w[0] < 2.0 * 2 ** k
+        assert (O.gen_A(n, seed, O.GEN_KAPPA_LOG2(k), row0=64, m=32) == A[64:96]).all()
+        x, st = O.conjugrad(A, O.gen_b(n, seed), np.zeros(n))
+        assert st["break_k"] >= 0 and np.linalg.norm(A @ x - O.gen_b(n, seed)) < 1e-5
+        iters.append(st["iterations"])
+    assert iters[0] > 20 and iters[1] > 2 * iters[0]      # ~sqrt(kappa) growth: iteration-bound workloads
