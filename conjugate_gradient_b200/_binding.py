@@ -36,7 +36,7 @@ class Options(C.Structure):
                 ("use_graph", C.c_int), ("check_every", C.c_int), ("time_gemv", C.c_int),
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
-                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("reserved", C.c_int * 2)]
+                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("gemv_l2_keep_pct", C.c_int), ("reserved", C.c_int * 1)]
 
 
 class Stats(C.Structure):
@@ -50,7 +50,8 @@ class Stats(C.Structure):
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
                 ("gemv_tile_cols", C.c_int), ("gemv_grid", C.c_int), ("graph_chunk", C.c_int),
-                ("comm", C.c_int), ("exit_reason", C.c_int), ("reserved", C.c_int * 1)]
+                ("comm", C.c_int), ("exit_reason", C.c_int), ("reserved", C.c_int * 1),
+                ("gemv_keep_rows", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
@@ -94,6 +95,8 @@ def lib():
         "cgb_create_rank": ([C.POINTER(vp), C.c_int, C.c_int, C.c_int, vp], C.c_int),
         "cgb_destroy": ([vp], C.c_int),
         "cgb_load_host": ([vp, i64, vp, vp, vp], C.c_int),
+        "cgb_load_text": ([vp, i64, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
+        "cgb_conjugrad_files": ([C.c_char_p, C.c_char_p, C.c_char_p, i64, C.c_int, op, vp, sp], C.c_int),
         "cgb_generate": ([vp, i64, u64, C.c_uint], C.c_int), "cgb_set_x0": ([vp, vp], C.c_int),
         "cgb_solve": ([vp, op, sp], C.c_int), "cgb_read_x": ([vp, vp], C.c_int),
         "cgb_conjugrad_host": ([vp, vp, vp, i64, C.c_double, i64, C.c_int, sp], C.c_int),
@@ -197,6 +200,11 @@ class Context:
         _check(lib().cgb_load_host(self._h, n, A_ptr, b_ptr, x0_ptr))
         self.n = n
 
+    def load_text(self, n, file_a, file_b, file_x):
+        """The reference's three text files; this rank's rows of A are parsed on the GPU."""
+        _check(lib().cgb_load_text(self._h, n, os.fsencode(file_a), os.fsencode(file_b), os.fsencode(file_x)))
+        self.n = n
+
     def generate(self, n, seed, flags=0):
         _check(lib().cgb_generate(self._h, n, seed, flags))
         self.n = n
@@ -298,6 +306,16 @@ def conjugrad_host(A, b, x0, gpus=1, **opts):
     st = Stats()
     _check(lib().cgb_conjugrad_host_opt(A.ctypes.data, b.ctypes.data, x.ctypes.data, x.shape[0], gpus,
                                         C.byref(o), C.byref(st)))
+    return x, st.as_dict()
+
+
+def conjugrad_files(file_a, file_b, file_x, n, gpus=1, **opts):
+    """`prog matrixA.txt vectorb.txt initialguess.txt` (serialConjugate.c:62-68) on `gpus` GPUs."""
+    x = np.empty(n, dtype=np.float64)
+    o = make_options(**opts)
+    st = Stats()
+    _check(lib().cgb_conjugrad_files(os.fsencode(file_a), os.fsencode(file_b), os.fsencode(file_x), n, gpus,
+                                     C.byref(o), x.ctypes.data, C.byref(st)))
     return x, st.as_dict()
 
 

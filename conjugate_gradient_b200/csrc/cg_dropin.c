@@ -223,6 +223,79 @@ int cgb_solve_generated(int64_t n, uint64_t seed, unsigned flags, int gpus,
     return rc;
 }
 
+/* ---- the three text files: every GPU ingests its own rows (cg_ingest.c) */
+typedef struct {
+    int g, gpus;
+    cgb_ctx **slot;
+    int64_t n;
+    const char *fileA, *fileB, *fileX;
+    const cgb_options *opt;
+    double *x;
+    cgb_stats stats;
+    int rc;
+    char err[512];
+} filemember_t;
+
+static void *team_files_main(void *arg)
+{
+    filemember_t *me = arg;
+    me->rc = cgb_load_text(*me->slot, me->n, me->fileA, me->fileB, me->fileX);
+    if (me->rc != CGB_OK) snprintf(me->err, sizeof me->err, "%s", cgb_last_error());
+    return NULL;
+}
+
+static void *team_files_solve_main(void *arg)
+{
+    filemember_t *me = arg;
+    me->rc = cgb_solve(*me->slot, me->opt, &me->stats);
+    if (me->rc == CGB_OK && me->g == 0 && me->x) me->rc = cgb_read_x(*me->slot, me->x);
+    if (me->rc != CGB_OK) snprintf(me->err, sizeof me->err, "%s", cgb_last_error());
+    return NULL;
+}
+
+int cgb_conjugrad_files(const char *fileA, const char *fileB, const char *fileX, int64_t n, int gpus,
+                        const cgb_options *opt, double *x, cgb_stats *stats)
+{
+    if (!fileA || !fileB || !fileX || n < 1) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_files: bad argument", "", __LINE__); return CGB_ERR_ARG; }
+    if (gpus < 1) gpus = 1;
+    if (gpus > MAX_GPUS) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_files: too many GPUs", "", __LINE__); return CGB_ERR_ARG; }
+    if (n % gpus != 0) {
+        char msg[96];
+        snprintf(msg, sizeof msg, "%lld is not divisible by %d", (long long)n, gpus);   /* parallel_cg.c:88 */
+        cgb_set_error("%s%s (cg_dropin.c:%d)", msg, "", __LINE__);
+        return CGB_ERR_NOT_DIVISIBLE;
+    }
+    if (cgb_device_count() < gpus) { cgb_set_error("%s%s (cg_dropin.c:%d)", "not enough CUDA devices for the requested --gpus", "", __LINE__); return CGB_ERR_CUDA; }
+    pthread_mutex_lock(&g_team_mu);
+    int rc = team_ensure(gpus);
+    if (rc != CGB_OK) { pthread_mutex_unlock(&g_team_mu); return rc; }
+    pthread_t th[MAX_GPUS];
+    filemember_t mb[MAX_GPUS];
+    memset(mb, 0, sizeof mb);
+    /* two collective phases: a rank whose input is bad must not leave the others inside a
+     * solve that waits for it */
+    for (int phase = 0; phase < 2 && rc == CGB_OK; ++phase) {
+        for (int g = 0; g < gpus; ++g) {
+            mb[g].g = g; mb[g].gpus = gpus; mb[g].slot = &g_team.ctx[g]; mb[g].n = n;
+            mb[g].fileA = fileA; mb[g].fileB = fileB; mb[g].fileX = fileX; mb[g].opt = opt; mb[g].x = x;
+            pthread_create(&th[g], NULL, phase == 0 ? team_files_main : team_files_solve_main, &mb[g]);
+        }
+        for (int g = 0; g < gpus; ++g) pthread_join(th[g], NULL);
+        for (int g = 0; g < gpus; ++g)
+            if (mb[g].rc != CGB_OK) { rc = mb[g].rc; cgb_set_error("%s%s (cg_dropin.c:%d)", "", mb[g].err, __LINE__); break; }
+    }
+    if (rc == CGB_OK && stats) {
+        *stats = mb[0].stats;
+        for (int g = 1; g < gpus; ++g) {
+            if (mb[g].stats.solve_seconds > stats->solve_seconds) stats->solve_seconds = mb[g].stats.solve_seconds;
+            if (mb[g].stats.h2d_seconds > stats->h2d_seconds) stats->h2d_seconds = mb[g].stats.h2d_seconds;
+            if (mb[g].stats.loop_ms > stats->loop_ms) stats->loop_ms = mb[g].stats.loop_ms;
+        }
+    }
+    pthread_mutex_unlock(&g_team_mu);
+    return rc;
+}
+
 int cgb_conjugrad_host(const double *A, const double *b, double *x, int64_t n, double eps,
                        int64_t max_iter, int gpus, cgb_stats *stats)
 {

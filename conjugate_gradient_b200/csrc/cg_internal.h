@@ -18,6 +18,7 @@ struct cgb_graph_key {
 
 struct cgb_ctx {
     int device, rank, ranks, sm_count, has_comm, loaded;
+    int64_t l2_bytes;
     char name[64];
     cudaStream_t stream;
     cudaEvent_t ev[3];
@@ -56,5 +57,7 @@ struct cgb_ctx {
 };
 
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);
+/* (Re)allocates the device arrays (and, with ranks > 1, the peer window: collective) for order n. */
+int cgb_ensure_problem(cgb_ctx *c, int64_t n);
 
 #endif

@@ -80,13 +80,13 @@ static int64_t parse_all(const char *buf, size_t len, double *dst, int64_t cap, 
 static const double k_pow10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
-static inline int is_sep_byte(unsigned char ch)
+int cgb_is_sep_byte(unsigned char ch)
 {
     return ch == ' ' || ch == '\t' || ch == '\n' || ch == '\r' || ch == ',' || ch == ';' || ch == '\f' || ch == '\v';
 }
 
 /* One token [p, e): returns 1 and *out if it is a plain decimal number, else 0. */
-static int token_to_double(const char *p, const char *e, double *out)
+int cgb_token_to_double(const char *p, const char *e, double *out)
 {
     const char *s = p;
     int neg = 0;
@@ -151,7 +151,7 @@ static void *span_count(void *arg)
     int in_tok = 0;
     for (const char *p = j->beg; p < j->end; ++p) {
         const unsigned char ch = (unsigned char)*p;
-        const int sep = is_sep_byte(ch);
+        const int sep = cgb_is_sep_byte(ch);
         if (ch >= 0x80) j->irregular = 1;                  /* BOM or junk: sequential path decides */
         if (!sep && !in_tok) ++k;
         in_tok = !sep;
@@ -166,12 +166,12 @@ static void *span_parse(void *arg)
     const char *p = j->beg;
     int64_t k = j->offset;
     while (p < j->end) {
-        while (p < j->end && is_sep_byte((unsigned char)*p)) ++p;
+        while (p < j->end && cgb_is_sep_byte((unsigned char)*p)) ++p;
         if (p >= j->end) break;
         const char *e = p;
-        while (e < j->end && !is_sep_byte((unsigned char)*e)) ++e;
+        while (e < j->end && !cgb_is_sep_byte((unsigned char)*e)) ++e;
         if (k >= j->cap) break;                            /* caller wanted only the first `cap` values */
-        if (!token_to_double(p, e, &j->dst[k])) { j->irregular = 1; return NULL; }
+        if (!cgb_token_to_double(p, e, &j->dst[k])) { j->irregular = 1; return NULL; }
         ++k;
         p = e;
     }
@@ -200,7 +200,7 @@ static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t 
     for (int t = 0; t < T; ++t) {
         const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
         if (nxt < cut) nxt = cut;
-        while (nxt < end && !is_sep_byte((unsigned char)*nxt)) ++nxt;     /* cut only at a separator */
+        while (nxt < end && !cgb_is_sep_byte((unsigned char)*nxt)) ++nxt;     /* cut only at a separator */
         memset(&job[t], 0, sizeof job[t]);
         job[t].beg = cut; job[t].end = nxt;
         cut = nxt;
@@ -225,9 +225,9 @@ static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t 
 }
 
 /* Whole file, read-only: mmap when possible (no copy of a multi-GB text), else slurp. */
-typedef struct { char *p; size_t len; int mapped; } text_t;
+typedef cgb_text text_t;
 
-static int text_open(const char *path, text_t *t)
+int cgb_text_open(const char *path, cgb_text *t)
 {
     memset(t, 0, sizeof *t);
     int fd = open(path, O_RDONLY);
@@ -247,28 +247,80 @@ static int text_open(const char *path, text_t *t)
     return t->p ? 0 : -1;
 }
 
-static void text_close(text_t *t)
+void cgb_text_close(cgb_text *t)
 {
     if (t->mapped) munmap(t->p, t->len); else free(t->p);
     t->p = NULL;
+}
+
+/* k-th (0-based) token start inside [beg, end), or end. */
+static const char *span_seek(const char *beg, const char *end, int64_t k)
+{
+    const char *p = beg;
+    for (;;) {
+        while (p < end && cgb_is_sep_byte((unsigned char)*p)) ++p;
+        if (p >= end || k == 0) return p;
+        while (p < end && !cgb_is_sep_byte((unsigned char)*p)) ++p;
+        --k;
+    }
+}
+
+int64_t cgb_text_locate(const cgb_text *tx, int64_t first, int64_t count, size_t *beg_out, size_t *end_out)
+{
+    const char *buf = tx->p;
+    const size_t len = tx->len;
+    const int T = io_threads(len);
+    span_job job[IO_MAX_THREADS];
+    pthread_t th[IO_MAX_THREADS];
+    const char *end = buf + len, *cut = buf;
+    for (int t = 0; t < T; ++t) {
+        const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
+        if (nxt < cut) nxt = cut;
+        while (nxt < end && !cgb_is_sep_byte((unsigned char)*nxt)) ++nxt;
+        memset(&job[t], 0, sizeof job[t]);
+        job[t].beg = cut; job[t].end = nxt;
+        cut = nxt;
+    }
+    for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, span_count, &job[t]);
+    span_count(&job[0]);
+    for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+    int64_t total = 0;
+    for (int t = 0; t < T; ++t) {
+        if (job[t].irregular) return -1;
+        job[t].offset = total;
+        total += job[t].count;
+    }
+    if (first < 0 || count < 0 || first + count > total) { *beg_out = *end_out = len; return total; }
+    const char *pb = end, *pe = end;
+    for (int t = 0; t < T; ++t) {
+        if (first >= job[t].offset && first < job[t].offset + job[t].count)
+            pb = span_seek(job[t].beg, job[t].end, first - job[t].offset);
+        const int64_t last = first + count;                /* first token AFTER the range */
+        if (last >= job[t].offset && last < job[t].offset + job[t].count)
+            pe = span_seek(job[t].beg, job[t].end, last - job[t].offset);
+    }
+    if (count == 0) pe = pb;
+    *beg_out = (size_t)(pb - buf);
+    *end_out = (size_t)(pe - buf);
+    return total;
 }
 
 int cgb_read_values(const char *path, double *dst, int64_t count, int64_t *got)
 {
     text_t tx;
     if (got) *got = 0;
-    if (text_open(path, &tx) != 0) return CGB_ERR_IO;
+    if (cgb_text_open(path, &tx) != 0) return CGB_ERR_IO;
     int64_t k = parse_parallel(tx.p, tx.len, dst, count);
     int bad = 0;
     if (k < 0) {                                           /* irregular tokens: exact sequential semantics */
-        text_close(&tx);
+        cgb_text_close(&tx);
         size_t len = 0;
         char *buf = slurp(path, &len);
         if (!buf) return CGB_ERR_IO;
         k = parse_all(buf, len, dst, count, &bad);
         free(buf);
     } else {
-        text_close(&tx);
+        cgb_text_close(&tx);
         if (k > count) k = count;                          /* parse_all stops after `count` values too */
     }
     if (got) *got = k;
@@ -278,9 +330,9 @@ int cgb_read_values(const char *path, double *dst, int64_t count, int64_t *got)
 int64_t cgb_count_values(const char *path)
 {
     text_t tx;
-    if (text_open(path, &tx) != 0) return -1;
+    if (cgb_text_open(path, &tx) != 0) return -1;
     int64_t k = parse_parallel(tx.p, tx.len, NULL, 0);
-    text_close(&tx);
+    cgb_text_close(&tx);
     if (k >= 0) return k;
     size_t len = 0;
     char *buf = slurp(path, &len);

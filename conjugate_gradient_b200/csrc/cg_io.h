@@ -13,6 +13,18 @@ extern "C" {
 #endif
 /* printer() (serialConjugate.c:260-276): "%f  " per element, newline after the last column. */
 void cgb_print_vector(FILE *out, const double *v, int64_t rows, int64_t cols);
+/* ---- pieces of the host parser the GPU ingest path (cg_ingest.c) shares */
+typedef struct cgb_text { char *p; size_t len; int mapped; } cgb_text;
+int  cgb_text_open(const char *path, cgb_text *t);          /* mmap (read-only) or slurp; 0 = ok */
+void cgb_text_close(cgb_text *t);
+int  cgb_is_sep_byte(unsigned char ch);                     /* whitespace , ;                    */
+/* One token [p, e) -> double exactly as strtod would; 0 when it is not a plain number. */
+int  cgb_token_to_double(const char *p, const char *e, double *out);
+/* Byte range [*beg, *end) that holds values first .. first+count-1 (it starts at the first
+ * byte of value `first`).  Returns the number of values in the file, or -1 when the text has
+ * bytes the fast tokeniser does not handle (a BOM): use cgb_read_values() then. */
+int64_t cgb_text_locate(const cgb_text *t, int64_t first, int64_t count, size_t *beg, size_t *end);
+
 /* cgb_write_values() with the choice to append (row blocks of a matrix written in turn). */
 int cgb_write_values_mode(const char *path, const double *v, int64_t count, int fmt_decimals, int append);
 #ifdef __cplusplus

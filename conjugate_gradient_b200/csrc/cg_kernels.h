@@ -78,6 +78,10 @@ typedef struct cgk_gemv_plan {
     int tile_cols;         /* C: columns per ring stage (variant BULK)    */
     int grid;              /* CTAs (resolved)                             */
     int smem_bytes;        /* dynamic shared memory (resolved)            */
+    int keep_pct;          /* request: % of L2 to keep rows of A in across iterations;
+                              0 = default (60), < 0 = never                  */
+    long long l2_bytes;    /* request: the device's L2 size (0: no L2 policy) */
+    long long keep_rows;   /* resolved: rows [0, keep_rows) are loaded evict_last */
 } cgk_gemv_plan;
 
 enum { CGK_GEMV_AUTO = 0, CGK_GEMV_LDG = 1, CGK_GEMV_BULK = 2 };

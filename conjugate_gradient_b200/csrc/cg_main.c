@@ -217,7 +217,7 @@ int main(int argc, char **argv)
 
     cgb_stats st;
     memset(&st, 0, sizeof st);
-    double *A = NULL, *b = NULL, *x = NULL;
+    double *x = NULL;
     int64_t n = 0;
     int rc;
     int saved_stdout = -1;
@@ -266,24 +266,18 @@ int main(int argc, char **argv)
             return 1;
         }
         printf("Computing cg of matrix size : %lld\n", (long long)n * (long long)n);   /* :58, 64-bit */
-        A = malloc((size_t)n * (size_t)n * sizeof(double));
-        b = malloc((size_t)n * sizeof(double));
         x = malloc((size_t)n * sizeof(double));
-        if (!A || !b || !x) { printf("can't allocate memory for vector\n"); return 1; }  /* :80 */
-        const char *files[3] = {cli.fileA, cli.fileB, cli.fileX};
-        double *dst[3] = {A, b, x};
-        int64_t cnt[3] = {n * n, n, n};
-        for (int i = 0; i < 3; ++i) {
-            int64_t got = 0;
-            if (cgb_read_values(files[i], dst[i], cnt[i], &got) != CGB_OK) {
-                if (got == 0) printf("Could not open file\n");
-                fprintf(stderr, "cg_b200: %s: expected %lld values, found %lld\n", files[i], (long long)cnt[i], (long long)got);
-                return 1;
-            }
-        }
+        if (!x) { printf("can't allocate memory for vector\n"); return 1; }             /* :80 */
+        /* initialize() x3 + MPI_Scatter (parallel_cg.c:105-115): every GPU ingests the bytes of
+         * its own rows and parses them on the device; the matrix never exists on the host */
         SOLVER_STDOUT_OFF();
-        rc = cgb_conjugrad_host_opt(A, b, x, n, cli.gpus, &opt, &st);
+        rc = cgb_conjugrad_files(cli.fileA, cli.fileB, cli.fileX, n, cli.gpus, &opt, x, &st);
         SOLVER_STDOUT_ON();
+        if (rc == CGB_ERR_IO) {
+            if (strstr(cgb_last_error(), "Could not open file")) printf("Could not open file\n");   /* :103 */
+            fprintf(stderr, "cg_b200: %s\n", cgb_last_error());
+            return 1;
+        }
     }
     if (rc != CGB_OK) {
         fprintf(stderr, "cg_b200: %s\n", cgb_last_error());
@@ -318,7 +312,7 @@ int main(int argc, char **argv)
         fprintf(stderr, "cg_b200: cannot write %s\n", cli.write_x);
         return 1;
     }
-    free(A); free(b); free(x);
+    free(x);
     cgb_shutdown();
     return 0;
 }

@@ -98,6 +98,14 @@ static int ctx_init_common(cgb_ctx *c, int device)
     }
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
+    c->l2_bytes = (int64_t)prop.l2CacheSize;
+    {
+        /* experiments: CGB_L2_SETASIDE=1 reserves the maximum persisting L2 carve-out */
+        const char *e = getenv("CGB_L2_SETASIDE");
+        if (e && *e == '1' && prop.persistingL2CacheMaxSize > 0)
+            (void)cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize);
+        (void)cudaGetLastError();
+    }
     snprintf(c->name, sizeof c->name, "%.63s", prop.name);
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev[0]));
@@ -329,7 +337,7 @@ int cgb_device_info(cgb_ctx *c, int *device, int *sm_count, int64_t *free_bytes,
 }
 
 /* ------------------------------------------------------------------ problem */
-static int ensure_problem(cgb_ctx *c, int64_t n)
+int cgb_ensure_problem(cgb_ctx *c, int64_t n)
 {
     if (n < 1) FAIL(CGB_ERR_ARG, "matrix order must be >= 1");
     if (n % c->ranks != 0) {
@@ -377,7 +385,7 @@ int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_r
                   const double *x0_full)
 {
     if (!c || !A_rows || !b_rows || !x0_full) FAIL(CGB_ERR_ARG, "cgb_load_host: null argument");
-    int rc = ensure_problem(c, n);
+    int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
     const int64_t m = c->m;
     double t0 = now_s();
@@ -398,7 +406,7 @@ int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_r
 int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
 {
     if (!c) FAIL(CGB_ERR_ARG, "cgb_generate: null context");
-    int rc = ensure_problem(c, n);
+    int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
     const int64_t row0 = (int64_t)c->rank * c->m;
     KL(cgk_generate_A(c->A, n, row0, c->m, seed, flags, c->stream));
@@ -457,6 +465,7 @@ int cgb_debug_read(cgb_ctx *c, int what, int64_t offset, int64_t count, double *
 static void plan_request_from_options(cgk_gemv_plan *p, const cgb_options *o)
 {
     memset(p, 0, sizeof *p);
+    p->keep_pct = o->gemv_l2_keep_pct;
     p->variant = o->gemv_variant; p->rows_per_cta = o->gemv_rows; p->unroll = o->gemv_unroll;
     p->threads = o->gemv_threads; p->vec = o->gemv_vec; p->stages = o->gemv_stages;
     p->tile_cols = o->gemv_tile_cols;
@@ -577,6 +586,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
 
     cgk_gemv_plan req;
     plan_request_from_options(&req, &o);
+    req.l2_bytes = c->l2_bytes;
     c->plan = req;
     if (peers) KL(cgk_gemv_make_plan_comm(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
     else KL(cgk_gemv_make_plan(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
@@ -682,6 +692,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->gemv_tile_cols = c->plan.tile_cols; stats->gemv_grid = c->plan.grid;
         stats->graph_chunk = chunk;
         stats->comm = c->comm_mode;
+        stats->gemv_keep_rows = c->plan.keep_rows;
         stats->exit_reason = c->h_sc->stop_req;
         if (gemv_pairs_used > 0) {
             double sum = 0.0, mn = 1e300;

@@ -79,7 +79,10 @@ typedef struct cgb_options {
     int     guard;         /* 1: end the solve instead of iterating NaNs when p.Ap = 0 (alpha not  */
                            /*    finite) or the initial residual is exactly 0.  Default 0 mirrors  */
                            /*    the reference, which has no such test (parallel_cg.c:298,318)     */
-    int     reserved[2];
+    int     gemv_l2_keep_pct; /* small n (A within ~0.8..3 L2 sizes): % of L2 in which the first rows  */
+                           /* of A are kept (evict_last) from one iteration to the next; 0 = the   */
+                           /* library default, < 0 = plain streaming                               */
+    int     reserved[1];
 } cgb_options;
 
 #define CGB_EXIT_STOP_RULE 1       /* sqrt(r.r) < eps                 (parallel_cg.c:314-317)  */
@@ -115,6 +118,7 @@ typedef struct cgb_stats {
     int     comm;              /* CGB_COMM_NCCL / CGB_COMM_PEER as used (0 with one rank)          */
     int     exit_reason;       /* CGB_EXIT_*                                                       */
     int     reserved[1];
+    int64_t gemv_keep_rows;    /* rows of A held in L2 across iterations (0: plain streaming)      */
 } cgb_stats;
 
 /* ---- library / device ------------------------------------------------------ */
@@ -141,6 +145,13 @@ int cgb_destroy(cgb_ctx *ctx);
  * caller-owned, copied to the GPU (pinned buffers copy at PCIe rate). */
 int cgb_load_host(cgb_ctx *ctx, int64_t n, const double *A_rows, const double *b_rows,
                   const double *x0_full);
+/* The same three inputs as the reference's TEXT files (initialize(), parallel_cg.c:147-168,
+ * "%f%*c" token rules): the rank locates the bytes of its own m rows in matrixA.txt, streams
+ * them through pinned memory and the GPU tokenises and converts them (bit-identical to
+ * strtod; tokens outside the exact fast path are resolved by strtod on the host).  The full
+ * matrix is never held on the host.  vectorb.txt / initialguess.txt: n values each.
+ * Short or missing files are CGB_ERR_IO. */
+int cgb_load_text(cgb_ctx *ctx, int64_t n, const char *fileA, const char *fileB, const char *fileX);
 /* North-star item 4: the rank's rows of the seeded SPD system generated in place
  * on the GPU (generateSPDmatrix.m:4-17): A = 0.5(R+R') + nI, b = rand, x0 = 0. */
 int cgb_generate(cgb_ctx *ctx, int64_t n, uint64_t seed, unsigned flags);
@@ -172,6 +183,12 @@ int cgb_conjugrad_host_opt(const double *A, const double *b, double *x, int64_t 
  * `gpus` GPUs (each its own row block, generateSPDmatrix.m:4-17), solve, and
  * return x (n doubles, may be NULL).  No text files, no host copy of A. */
 int cgb_solve_generated(int64_t n, uint64_t seed, unsigned flags, int gpus,
+                        const cgb_options *opt, double *x, cgb_stats *stats);
+/* The reference's whole program minus its printing: `prog matrixA.txt vectorb.txt
+ * initialguess.txt` (serialConjugate.c:62-68; rank-0 read + MPI_Scatter of parallel_cg.c:
+ * 100-118) on `gpus` GPUs through cgb_load_text(); x (n doubles, may be NULL) receives the
+ * solution.  stats->h2d_seconds is the text ingest ("data distribution") time. */
+int cgb_conjugrad_files(const char *fileA, const char *fileB, const char *fileX, int64_t n, int gpus,
                         const cgb_options *opt, double *x, cgb_stats *stats);
 /* Releases the contexts cached by the one-call entry points (GPU memory, NCCL
  * communicators, graphs).  The reference frees its temporaries at the end of

@@ -1,16 +1,23 @@
 set -x
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -8
-run() { tag=$1; shift; timeout 900 python bench.py "$@" > gpurun_out/b1_$tag.json 2> gpurun_out/b1_$tag.err; echo "rc=$?"; python - <<PY
-import json
-try:
-    l=json.loads(open("gpurun_out/b1_$tag.json").read().strip().splitlines()[-1])
-    print("G=1 $tag", "it/s", round(l["value"],2), "graph", round(l["graph_replay"]["value"],2), "gemv_ms", round(l["roofline"]["gemv_ms_avg"],4), "GB/s", round(l["roofline"]["achieved"]), "e2e", l.get("e2e",{}).get("value"), "cpu", l.get("cpu_baseline",{}).get("value"), l["clocks"])
-except Exception as e:
-    print("G=1 $tag FAILED", e); print(open("gpurun_out/b1_$tag.err").read()[-1500:])
+timeout 900 python -m pytest tests/test_gpu_ingest.py tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -12
+# ingest throughput: n = 8192 in generateSPDmatrix.m's format (the reference's largest published size)
+python - <<'PY'
+import time, os, sys, numpy as np
+sys.path.insert(0, "tests")
+import conjugate_gradient_b200 as cg
+n = 8192
+pre = "/tmp/sys8192"
+t = time.time()
+os.system(f"conjugate_gradient_b200/lib/cg_b200 --gen {n} --seed 1 --emit-files {pre} > /tmp/emit.log 2>&1")
+print("emit+solve seconds", round(time.time() - t, 2), "file MB", os.path.getsize(pre + "_matrix.txt") / 1e6)
+with cg.Context(0) as ctx:
+    for rep in range(3):
+        t = time.time(); ctx.load_text(n, pre + "_matrix.txt", pre + "_vector.txt", pre + "_x0.txt"); dt = time.time() - t
+        print(f"GPU ingest n={n}: {dt:.3f} s  {n*n/dt/1e6:.1f} Mvalues/s  {os.path.getsize(pre + '_matrix.txt')/dt/1e9:.2f} GB/s of text")
+    t = time.time(); v = cg.read_values(pre + "_matrix.txt", n * n); dt = time.time() - t
+    print(f"host parallel parser: {dt:.3f} s  {n*n/dt/1e6:.1f} Mvalues/s ({os.cpu_count()} cores)")
+    assert ctx.debug_read(0, 0, n * n).tobytes() == v.tobytes()
+t = time.time()
+os.system(f"conjugate_gradient_b200/lib/cg_b200 {pre}_matrix.txt {pre}_vector.txt {pre}_x0.txt --dims {pre}_dimensions.txt --stats")
+print("CLI wall seconds (files, 1 GPU)", round(time.time() - t, 2))
 PY
-}
-run default
-run n131072 --matrix-n 131072 --steps 20 --no-e2e --no-cpu
-run n16384 --matrix-n 16384 --steps 200 --no-e2e --no-cpu
-run n4096 --matrix-n 4096 --steps 2000 --no-e2e --no-cpu
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/b1_reference.json 2>gpurun_out/b1_reference.err; tail -c 600 gpurun_out/b1_reference.json
