@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=0, help="GEMV rows per CTA (0 = library default)")
     ap.add_argument("--unroll", type=int, default=0)
     ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--l2-keep", type=int, default=0, help="small n: %% of L2 holding rows of A across iterations (0 default, -1 off)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
@@ -70,6 +71,18 @@ def peak_hbm_gbs():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(n, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per GEMV launch from the committed `ncu --set full`
+    capture of this command (profiles/ncu_traffic.json, written from the .ncu-rep), else None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+        e = t.get(f"n{n}_g{world}")
+        return (float(e["bytes"]), e["source"]) if e else (None, None)
+    except Exception:
+        return None, None
 
 
 def gemv_bytes(m, n):
@@ -238,7 +251,8 @@ def b200_arm(args):
     info = ctx.device_info()
     ctx.generate(n, SEED)                                   # each GPU writes its own row block in HBM
     gopts = dict(gemv_variant=args.gemv, comm={"auto": 0, "nccl": 1, "peer": 2}[args.comm],
-                 gemv_rows=args.rows, gemv_unroll=args.unroll, gemv_threads=args.threads)
+                 gemv_rows=args.rows, gemv_unroll=args.unroll, gemv_threads=args.threads,
+                 gemv_l2_keep_pct=args.l2_keep)
 
     # ---- warm-up: W untimed iterations (also builds plans, first-touches everything)
     if W > 0:
@@ -269,6 +283,7 @@ def b200_arm(args):
 
     peak, peak_src = peak_hbm_gbs()
     gbytes = gemv_bytes(m, n)
+    traffic, traffic_src = ncu_traffic(n, world)
     achieved = gbytes / (gemv_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -282,7 +297,7 @@ def b200_arm(args):
                    "gemv_kernel": {k: st[k] for k in ("gemv_variant", "gemv_rows", "gemv_unroll", "gemv_threads",
                                                       "gemv_vec", "gemv_stages", "gemv_tile_cols", "gemv_grid")}},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
                      "kernel": "gemv (A*p with fused p.Ap)", "bytes_per_launch": gbytes,
                      "gemv_ms_avg": gemv_ms, "gemv_ms_min": st["gemv_ms_min"], "launches_timed": st["gemv_timed"],
                      "gemv_share_of_step": gemv_ms * K / loop_ms},
