@@ -36,7 +36,7 @@ class Options(C.Structure):
                 ("use_graph", C.c_int), ("check_every", C.c_int), ("time_gemv", C.c_int),
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
-                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("gemv_l2_keep_pct", C.c_int), ("reserved", C.c_int * 1)]
+                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("gemv_l2_keep_pct", C.c_int), ("symmetric", C.c_int)]
 
 
 class Stats(C.Structure):

@@ -192,6 +192,7 @@ done:
     if (rc == CGB_OK) {
         c->h2d_seconds = now_s() - t0;
         c->loaded = 1;
+        c->sym_state = 0;
     }
 out:
     if (have_text) cgb_text_close(&tx);

@@ -14,6 +14,7 @@ struct cgb_graph_key {
     const void *A;
     const void *win;        /* peer window the captured kernels point into */
     int comm, guard;
+    int symv, symv_ru;
 };
 
 struct cgb_ctx {
@@ -54,6 +55,12 @@ struct cgb_ctx {
     unsigned int gen;                 /* solve generation, in lockstep on all ranks      */
     int comm_mode;                    /* CGB_COMM_* in use by the current / last solve   */
     char peer_why[160];               /* why peer_ok == 0                                */
+    /* symmetric product (cg_symv.cu) */
+    int sym_state;                    /* 0 not checked, 1 exactly symmetric, -1 not      */
+    int use_symv, symv_ru;
+    double *sy_rowpart, *sy_colpart;  /* (n / T) * n each                                */
+    void *sy_tiles;
+    int64_t sy_ntiles;
 };
 
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);

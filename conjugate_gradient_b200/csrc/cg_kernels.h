@@ -84,7 +84,7 @@ typedef struct cgk_gemv_plan {
     long long keep_rows;   /* resolved: rows [0, keep_rows) are loaded evict_last */
 } cgk_gemv_plan;
 
-enum { CGK_GEMV_AUTO = 0, CGK_GEMV_LDG = 1, CGK_GEMV_BULK = 2 };
+enum { CGK_GEMV_AUTO = 0, CGK_GEMV_LDG = 1, CGK_GEMV_BULK = 2, CGK_GEMV_SYMV = 3 };
 
 /* Upper bound on gemv CTAs for any plan (sizes the partials workspace). */
 int64_t cgk_gemv_max_ctas(int64_t m);
@@ -148,6 +148,17 @@ int cgk_generate_b(double *b, int64_t n, int64_t row0, int64_t m, uint64_t seed,
 
 /* Writes `bytes` of zeros-then-ones traffic over buf: evicts L2 between timed launches. */
 int cgk_l2_flush(void *buf, int64_t bytes, void *stream);
+
+/* ---- symmetric product (cg_symv.cu): y = A v reading only the upper T x T tiles of an exactly
+ * symmetric A (n a multiple of cgk_symv_tile(), one GPU).  tiles: device array of (I, J) pairs
+ * made from cgk_symv_tile_list(); rowpart / colpart: (n / T) * n doubles each. */
+int     cgk_symv_tile(void);
+int64_t cgk_symv_tile_list(int64_t n, int *tiles_xy);
+int cgk_symv(const double *A, const double *v, const double *w, double *y, const void *tiles,
+             int64_t ntiles, double *rowpart, double *colpart, double *partials, double *dot_out,
+             cgk_scalars *sc, int64_t n, int rows_in_flight, void *stream);
+/* *d_flag = 1 unless a_ij and a_ji are bit-identical for all i, j (and no NaN). */
+int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void *stream);
 
 /* ---- text ingest (cg_ingest.cu): the rank's part of matrixA.txt parsed on the GPU */
 typedef struct cgk_ingest_state {

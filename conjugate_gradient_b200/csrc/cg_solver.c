@@ -191,6 +191,8 @@ static void free_problem(cgb_ctx *c)
     cudaFree(c->A); cudaFree(c->b); cudaFree(c->r); cudaFree(c->Ap);
     if (c->win) cudaFree(c->win); else cudaFree(c->p_full);
     cudaFree(c->x_full); cudaFree(c->partials_gemv);
+    cudaFree(c->sy_rowpart); cudaFree(c->sy_colpart); cudaFree(c->sy_tiles);
+    c->sy_rowpart = c->sy_colpart = NULL; c->sy_tiles = NULL; c->sy_ntiles = 0; c->sym_state = 0;
     c->A = c->b = c->r = c->Ap = c->p_full = c->x_full = c->partials_gemv = NULL;
     c->win = NULL; c->win_bytes = 0;
     c->n = c->m = 0; c->cap_n = c->cap_m = 0; c->loaded = 0;
@@ -400,6 +402,7 @@ int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_r
     CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = now_s() - t0;
     c->loaded = 1;
+    c->sym_state = 0;
     return CGB_OK;
 }
 
@@ -415,6 +418,7 @@ int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
     CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = 0.0;
     c->loaded = 1;
+    c->sym_state = 1;          /* 0.5 (u_ij + u_ji): IEEE addition commutes, exactly symmetric */
     return CGB_OK;
 }
 
@@ -471,6 +475,52 @@ static void plan_request_from_options(cgk_gemv_plan *p, const cgb_options *o)
     p->tile_cols = o->gemv_tile_cols;
 }
 
+/* cgb_options.symmetric: verify a_ij == a_ji once per loaded matrix, allocate the tile list and
+ * the two partial-sum workspaces, and switch the loop's matVec to cg_symv.cu. */
+static int prepare_symv(cgb_ctx *c, const cgb_options *o)
+{
+    const int T = cgk_symv_tile();
+    if (c->ranks != 1) FAIL(CGB_ERR_STATE, "cgb_options.symmetric: the upper-tile product runs on one rank in this build");
+    if (c->n % T != 0) {
+        snprintf(tl_err, sizeof tl_err, "cgb_options.symmetric needs n to be a multiple of %d (n = %lld)", T, (long long)c->n);
+        return CGB_ERR_ARG;
+    }
+    cudaStream_t st = c->stream;
+    if (c->sym_state == 0) {
+        int *d_flag = NULL, h_flag = 1;
+        CU(cudaMalloc((void **)&d_flag, sizeof(int)));
+        int e = cgk_symmetry_check(c->A, c->n, d_flag, st);
+        cudaError_t ce = cudaMemcpyAsync(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+        cudaFree(d_flag);
+        if (e != 0 || ce != cudaSuccess) { (void)cudaGetLastError(); FAIL(CGB_ERR_CUDA, "symmetry check failed to run"); }
+        c->sym_state = h_flag ? -1 : 1;
+    }
+    if (c->sym_state < 0)
+        FAIL(CGB_ERR_ARG, "cgb_options.symmetric: the matrix is not exactly symmetric (a_ij != a_ji somewhere)");
+    if (!c->sy_tiles) {
+        const int64_t ntl = c->n / T, cnt = cgk_symv_tile_list(c->n, NULL);
+        int *h = malloc((size_t)cnt * 2 * sizeof(int));
+        if (!h) FAIL(CGB_ERR_NOMEM, "out of host memory for the tile list");
+        cgk_symv_tile_list(c->n, h);
+        cudaError_t ce = cudaMalloc(&c->sy_tiles, (size_t)cnt * 2 * sizeof(int));
+        if (ce == cudaSuccess) ce = cudaMemcpy(c->sy_tiles, h, (size_t)cnt * 2 * sizeof(int), cudaMemcpyHostToDevice);
+        free(h);
+        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_rowpart, (size_t)ntl * (size_t)c->n * sizeof(double));
+        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_colpart, (size_t)ntl * (size_t)c->n * sizeof(double));
+        if (ce != cudaSuccess) {
+            (void)cudaGetLastError();
+            cudaFree(c->sy_tiles); cudaFree(c->sy_rowpart); cudaFree(c->sy_colpart);
+            c->sy_tiles = NULL; c->sy_rowpart = c->sy_colpart = NULL;
+            FAIL(CGB_ERR_NOMEM, "can't allocate memory for the symmetric-product workspaces");
+        }
+        c->sy_ntiles = cnt;
+    }
+    c->symv_ru = (o->gemv_unroll == 1 || o->gemv_unroll == 4) ? o->gemv_unroll : 2;
+    c->use_symv = 1;
+    return CGB_OK;
+}
+
 /* One CG iteration on the solver stream; `cur` is the parity of the loop index
  * (selects which rr[] slot is rho).  Mirrors parallel_cg.c:290-323. */
 static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int cur,
@@ -496,6 +546,11 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     if (multi)                                                   /* MPI_Allgather(p), :290-291 */
         NC(ncclAllGather(p_loc, c->p_full, (size_t)c->m, ncclDouble, c->comm, st));
     if (ev_a) CU(cudaEventRecord(ev_a, st));
+    if (c->use_symv) {                                           /* upper tiles only, two kernels */
+        KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
+                    c->partials_gemv, &c->sc->pAp, c->sc, c->n, c->symv_ru, st));
+        c->launches += 1;
+    } else
     KL(cgk_gemv(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv,
                 multi ? &c->sc->pAp_local : &c->sc->pAp, c->sc, c->m, c->n, st));   /* :292-293 */
     if (ev_b) CU(cudaEventRecord(ev_b, st));
@@ -517,6 +572,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     key.n = c->n; key.m = c->m; key.max_iter = max_iter; key.eps = o->eps;
     key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan; key.guard = o->guard;
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
+    key.symv = c->use_symv; key.symv_ru = c->symv_ru;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -592,6 +648,11 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     else KL(cgk_gemv_make_plan(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
     if ((int64_t)c->plan.grid > cgk_gemv_max_ctas(c->m)) FAIL(CGB_ERR_STATE, "gemv grid exceeds workspace");
     if ((++c->gen & 0x3ffu) == 0u) ++c->gen;              /* tags never collide with zeroed memory */
+    c->use_symv = 0;
+    if (o.symmetric) {
+        int rc = prepare_symv(c, &o);
+        if (rc != CGB_OK) return rc;
+    }
 
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     const int use_graph = o.use_graph && !o.time_gemv;
@@ -685,6 +746,8 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->loop_ms = ms_loop; stats->init_ms = ms_init;
         stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds;
         stats->gemv_bytes = 8.0 * ((double)c->m * (double)c->n + (double)c->n + (double)c->m);
+        if (c->use_symv)      /* declared change of algorithmic bytes: the upper triangle, p once, Ap once */
+            stats->gemv_bytes = 8.0 * (0.5 * (double)c->n * ((double)c->n + 1.0) + 2.0 * (double)c->n);
         stats->kernel_launches = c->launches;
         stats->gemv_variant = c->plan.variant; stats->gemv_rows = c->plan.rows_per_cta;
         stats->gemv_unroll = c->plan.unroll; stats->gemv_threads = c->plan.threads;
@@ -692,6 +755,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->gemv_tile_cols = c->plan.tile_cols; stats->gemv_grid = c->plan.grid;
         stats->graph_chunk = chunk;
         stats->comm = c->comm_mode;
+        if (c->use_symv) { stats->gemv_variant = CGB_GEMV_SYMV; stats->gemv_unroll = c->symv_ru; stats->gemv_grid = (int)c->sy_ntiles; }
         stats->gemv_keep_rows = c->plan.keep_rows;
         stats->exit_reason = c->h_sc->stop_req;
         if (gemv_pairs_used > 0) {
@@ -737,6 +801,11 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
     cgk_gemv_plan plan;
     plan_request_from_options(&plan, &o);
     KL(cgk_gemv_make_plan(&plan, c->m, c->n, c->A, c->p_full, c->sm_count));
+    c->use_symv = 0;
+    if (o.symmetric) {
+        int rc = prepare_symv(c, &o);
+        if (rc != CGB_OK) return rc;
+    }
     cudaStream_t st = c->stream;
     const size_t flush_bytes = (size_t)512 << 20;
     if (flush_l2 && !c->flush_buf) {
@@ -746,11 +815,19 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
     KL(cgk_reset(c->sc, c->gen, st));
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     for (int i = 0; i < warmup; ++i)
+        if (c->use_symv)
+            KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
+                        c->partials_gemv, &c->sc->pAp_local, c->sc, c->n, c->symv_ru, st));
+        else
         KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
     double sum = 0.0, mn = 1e300;
     for (int i = 0; i < reps; ++i) {
         if (flush_l2) KL(cgk_l2_flush(c->flush_buf, (int64_t)flush_bytes, st));
         CU(cudaEventRecord(c->ev[0], st));
+        if (c->use_symv)
+            KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
+                        c->partials_gemv, &c->sc->pAp_local, c->sc, c->n, c->symv_ru, st));
+        else
         KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
         CU(cudaEventRecord(c->ev[1], st));
         CU(cudaEventSynchronize(c->ev[1]));

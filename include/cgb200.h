@@ -50,6 +50,7 @@ extern "C" {
 #define CGB_GEMV_AUTO 0
 #define CGB_GEMV_LDG  1            /* 128/256-bit streaming loads, registers          */
 #define CGB_GEMV_BULK 2            /* cp.async.bulk (TMA engine) shared-memory ring   */
+#define CGB_GEMV_SYMV 3            /* reported in cgb_stats when cgb_options.symmetric ran */
 
 /* How the ranks exchange p and the two dot scalars each iteration (what MPI_Allgather /
  * MPI_Allreduce do in parallel_cg.c:290-294,313); every rank must pass the same value */
@@ -82,7 +83,10 @@ typedef struct cgb_options {
     int     gemv_l2_keep_pct; /* small n (A within ~0.8..3 L2 sizes): % of L2 in which the first rows  */
                            /* of A are kept (evict_last) from one iteration to the next; 0 = the   */
                            /* library default, < 0 = plain streaming                               */
-    int     reserved[1];
+    int     symmetric;     /* 1: matVec reads only the upper tiles of A (half the bytes, SURVEY.md  */
+                           /*    8f-4).  Needs a_ij == a_ji bit for bit -- verified on the device   */
+                           /*    once per loaded matrix, CGB_ERR_ARG otherwise -- one rank, and n a */
+                           /*    multiple of 512.  0 (default): the reference's full row products   */
 } cgb_options;
 
 #define CGB_EXIT_STOP_RULE 1       /* sqrt(r.r) < eps                 (parallel_cg.c:314-317)  */

@@ -184,6 +184,57 @@ def test_generated_spread_family_solve(cg, ctx, n, k):
     assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
 
 
+# ----------------------------------------------------------------- symmetric product
+@pytest.mark.parametrize("n,k,ru", [(512, 0, 0), (1024, 0, 1), (2048, 7, 2), (1536, 4, 4)])
+def test_symmetric_upper_tile_product_solves_like_the_reference(cg, ctx, n, k, ru):
+    # matVec from the upper 512 x 512 tiles only (half the bytes): same solution, same stop
+    seed, flags = 41 + n, cg.GEN_KAPPA_LOG2(k)
+    ctx.generate(n, seed, flags)
+    st = ctx.solve(symmetric=1, gemv_unroll=ru)
+    x = ctx.read_x()
+    xo, so = O.conjugrad(O.gen_A(n, seed, flags), O.gen_b(n, seed, flags), np.zeros(n))
+    assert st["gemv_variant"] == 3 and relerr(x, xo) <= RTOL_X
+    assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
+    assert st["gemv_bytes"] == 8.0 * (0.5 * n * (n + 1) + 2 * n)
+    # bitwise reproducible (fixed-order partial sums, no atomics)
+    ctx.set_x0(np.zeros(n))
+    ctx.solve(symmetric=1, gemv_unroll=ru)
+    np.testing.assert_array_equal(ctx.read_x(), x)
+
+
+def test_symmetric_product_matches_the_full_product_elementwise(ctx):
+    n, seed = 2048, 3
+    ctx.generate(n, seed)
+    ctx.solve(ignore_stop=1, max_iter=1)
+    ap_full = ctx.debug_read(5, 0, n)
+    ctx.set_x0(np.zeros(n))
+    ctx.solve(ignore_stop=1, max_iter=1, symmetric=1)
+    ap_sym = ctx.debug_read(5, 0, n)
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    want = A @ b                                             # first direction p0 = b - A 0 = b
+    assert np.abs(ap_sym - want).max() <= 1e-13 * np.abs(want).max()
+    assert np.abs(ap_sym - ap_full).max() <= 1e-13 * np.abs(want).max()
+
+
+def test_symmetric_option_checks_its_preconditions(cg, ctx):
+    n = 512
+    A, b = O.spd_with_condition(n, 30.0, seed=2)
+    ctx.load_host(A, b, np.zeros(n))                         # host matrix: verified on the device first
+    st = ctx.solve(symmetric=1)
+    xo, so = O.conjugrad(A, b, np.zeros(n))
+    assert st["gemv_variant"] == 3 and relerr(ctx.read_x(), xo) <= RTOL_X
+    A2 = A.copy(); A2[3, 400] = np.nextafter(A2[3, 400], 1e9)       # one ulp off in one element
+    ctx.load_host(A2, b, np.zeros(n))
+    with pytest.raises(cg.CgbError) as e:
+        ctx.solve(symmetric=1)
+    assert e.value.code == -1 and "not exactly symmetric" in str(e.value)
+    assert ctx.solve()["gemv_variant"] != 3                  # the full product still serves it
+    ctx.generate(1000, 1)
+    with pytest.raises(cg.CgbError) as e:
+        ctx.solve(symmetric=1)
+    assert e.value.code == -1 and "multiple of 512" in str(e.value)
+
+
 def test_nonzero_initial_guess_and_restart(ctx):
     n, seed = 768, 9
     A, b = O.gen_A(n, seed), O.gen_b(n, seed)
