@@ -61,6 +61,7 @@ struct cgb_ctx {
     double *sy_rowpart, *sy_colpart;  /* (n / T) * n each                                */
     void *sy_tiles;
     int64_t sy_ntiles;
+    cgk_symplan sy_plan;              /* ranks > 1: which half of the row block this rank reads */
 };
 
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);

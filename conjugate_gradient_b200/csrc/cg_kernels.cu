@@ -19,151 +19,6 @@
 
 #include "cg_device.cuh"
 
-/* ------------------------------------------------------------------ peer exchange */
-__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_sys(unsigned long long *p, unsigned long long v)
-{
-    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long global_ns(void)
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-/* tag of exchange event e of solve generation gen (never 0 for gen & 0x3ff != 0) */
-__device__ __forceinline__ unsigned int cgk_tag(unsigned int gen, unsigned int e)
-{
-    return ((gen & 0x3ffu) << 22) | (e & 0x3fffffu);
-}
-/* Called every 1024 failed polls: gives up once any waiter has given up or the peer has been
- * silent for CGK_SPIN_TIMEOUT_NS, so a dead rank becomes an error code instead of a hung GPU. */
-__device__ __noinline__ bool spin_give_up(unsigned long long *t0, cgk_scalars *sc)
-{
-    if (*(volatile int *)&sc->comm_error) return true;
-    const unsigned long long now = global_ns();
-    if (*t0 == 0ull) { *t0 = now; return false; }
-    if (now - *t0 > CGK_SPIN_TIMEOUT_NS) {
-        *(volatile int *)&sc->comm_error = 1;
-        __threadfence();
-        return true;
-    }
-    return false;
-}
-/* LL-style scalar: two 8-byte words, each {32 bits of the double | tag << 32}; 8-byte stores
- * are single NVLink writes, so a reader that sees the tag in both words has the value. */
-__device__ __forceinline__ void ll_send(unsigned long long *slot, double v, unsigned int tag)
-{
-    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
-    const unsigned long long t = (unsigned long long)tag << 32;
-    st_relaxed_sys(slot, (b & 0xffffffffull) | t);
-    st_relaxed_sys(slot + 1, (b >> 32) | t);
-}
-/* All threads call it.  Threads g < G poll the LOCAL slots[g][2] until both words carry `tag`;
- * thread 0 adds the G values in rank order -- every rank computes the same bits. */
-__device__ __forceinline__ double ll_gather_sum(const unsigned long long *slots, int G,
-                                                unsigned int tag, cgk_scalars *sc)
-{
-    __shared__ double s_val[CGK_MAX_RANKS];
-    __shared__ double s_sum;
-    if ((int)threadIdx.x < G) {
-        const unsigned long long *s = slots + 2 * threadIdx.x;
-        unsigned long long w0, w1, t0 = 0ull;
-        unsigned int polls = 0;
-        for (;;) {
-            w0 = ld_relaxed_sys(s);
-            w1 = ld_relaxed_sys(s + 1);
-            if ((unsigned int)(w0 >> 32) == tag && (unsigned int)(w1 >> 32) == tag) break;
-            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
-        }
-        s_val[threadIdx.x] = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int g = 0; g < G; ++g) t += s_val[g];
-        s_sum = t;
-    }
-    __syncthreads();
-    return s_sum;
-}
-/* Threads g < G (g != rank) wait until peer g's p slice of event `tag` has landed here. */
-__device__ __forceinline__ void wait_p_flags(const cgk_peers &peers, unsigned int tag, cgk_scalars *sc)
-{
-    const int g = threadIdx.x;
-    if (g < peers.ranks && g != peers.rank) {
-        const unsigned long long *f = &peers.mbox[peers.rank]->p_flag[g];
-        unsigned long long t0 = 0ull;
-        unsigned int polls = 0;
-        while (ld_relaxed_sys(f) != (unsigned long long)tag)
-            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
-        (void)ld_acquire_sys(f);
-    }
-    __syncthreads();
-}
-/* Warp-level form for use inside a streaming loop: no CTA barrier, the warps stay decoupled. */
-__device__ __forceinline__ void warp_wait_p_flags(const cgk_peers &peers, unsigned int tag, cgk_scalars *sc)
-{
-    const int g = threadIdx.x & 31;
-    if (g < peers.ranks && g != peers.rank) {
-        const unsigned long long *f = &peers.mbox[peers.rank]->p_flag[g];
-        unsigned long long t0 = 0ull;
-        unsigned int polls = 0;
-        /* poll relaxed (no L1 invalidation per poll), then acquire once */
-        while (ld_relaxed_sys(f) != (unsigned long long)tag)
-            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
-        (void)ld_acquire_sys(f);
-    }
-    __syncwarp();
-}
-/* cta_partials_finish for kernels that stored into peer memory: thread 0's fence is
- * system-scope and cumulative over the CTA's stores (all before the preceding barrier), so
- * whatever the last CTA posts afterwards is ordered behind every CTA's peer stores.  Returns
- * true in all threads of the last CTA; *total is valid in its thread 0. */
-template <int NT>
-__device__ __forceinline__ bool cta_partials_finish_sys(double mine, double *partials, double *out,
-                                                        unsigned int *ticket, double *total)
-{
-    __shared__ int s_last;
-    __shared__ double s_red[NT / 32];
-    const int tid = threadIdx.x;
-    if (tid == 0) {
-        partials[blockIdx.x] = mine;
-        __threadfence_system();
-        unsigned int t = atomicAdd(ticket, 1u);
-        s_last = (t == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!s_last) return false;
-    __threadfence();
-    double s = 0.0;
-    for (unsigned int i = tid; i < gridDim.x; i += NT) s += __ldcg(partials + i);
-    s = warp_sum(s);
-    if ((tid & 31) == 0) s_red[tid >> 5] = s;
-    __syncthreads();
-    if (tid == 0) {
-        double t = 0.0;
-#pragma unroll
-        for (int q = 0; q < NT / 32; ++q) t += s_red[q];
-        *out = t;
-        *total = t;
-        *ticket = 0u;
-        __threadfence_system();
-    }
-    return true;
-}
-
 /* ------------------------------------------------------------------ GEMV (LDG) */
 /* One CTA owns R adjacent rows (one contiguous R*n*8-byte panel of A) and walks
  * all n columns; thread t of NT owns VW adjacent columns of every step, so a

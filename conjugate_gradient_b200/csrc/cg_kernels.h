@@ -60,13 +60,30 @@ typedef struct cgk_scalars {
 typedef struct cgk_mailbox {
     unsigned long long p_flag[CGK_MAX_RANKS];             /* tag of the last p slice rank g pushed */
     unsigned long long dot[2][2][CGK_MAX_RANKS][2];       /* [0 p.Ap | 1 r.r][parity][src][LL word] */
+    unsigned long long c_flag[CGK_MAX_RANKS];             /* symmetric product: tag of the column sums rank g pushed */
 } cgk_mailbox;
 
 typedef struct cgk_peers {
     int rank, ranks;
     double *p_full[CGK_MAX_RANKS];      /* every rank's gathered-direction vector, peer-mapped */
     cgk_mailbox *mbox[CGK_MAX_RANKS];   /* every rank's mailbox; mbox[rank] is local           */
+    double *crecv[CGK_MAX_RANKS];       /* every rank's [ranks][m] receive area for column sums */
 } cgk_peers;
+
+/* Row-sharded symmetric product (cg_symv.cu): which tiles of its m x n row block a rank reads.
+ * Block pairs {g, h} are split so that every rank reads exactly half of its block: its own
+ * diagonal block's upper tiles, all of the blocks at cyclic distance 1 .. G/2 - 1 (G even;
+ * .. (G-1)/2 for odd G), and half of the block at distance G/2 (the lower-numbered rank of the
+ * pair takes tile rows < row_end, the other one the tile columns >= col_begin). */
+typedef struct cgk_symplan {
+    int nblk;                           /* foreign column blocks this rank reads                */
+    int blk_rank[CGK_MAX_RANKS];        /* their owners, in reading order (distance ascending)  */
+    int row_end[CGK_MAX_RANKS];         /* local tile rows [0, row_end) contribute              */
+    int col_begin[CGK_MAX_RANKS];       /* tile columns [col_begin, mt) of the block are read   */
+    int nsrc;                           /* ranks that send column sums to this rank             */
+    int src_rank[CGK_MAX_RANKS];
+    int src_col_begin[CGK_MAX_RANKS];   /* they cover my local tile columns >= this             */
+} cgk_symplan;
 
 typedef struct cgk_gemv_plan {
     int variant;           /* CGK_GEMV_*                                  */
@@ -157,6 +174,16 @@ int64_t cgk_symv_tile_list(int64_t n, int *tiles_xy);
 int cgk_symv(const double *A, const double *v, const double *w, double *y, const void *tiles,
              int64_t ntiles, double *rowpart, double *colpart, double *partials, double *dot_out,
              cgk_scalars *sc, int64_t n, int rows_in_flight, void *stream);
+/* Row-sharded form (ranks > 1, peer windows): local tile rows, p exchange flags checked per
+ * tile, column sums pushed to their owners (cgk_symv_comm = tile kernel + push kernel + finish
+ * kernel; the finish also pushes the p.Ap partial like cgk_gemv_comm).  tiles: (I_local, J)
+ * pairs from cgk_symv_tile_list_rank(); rowpart: (n / T) * m doubles; colpart: (m / T) * n. */
+void    cgk_symv_make_plan(cgk_symplan *sp, int rank, int ranks, int64_t m);
+int64_t cgk_symv_tile_list_rank(const cgk_symplan *sp, int rank, int64_t m, int *tiles_xy);
+int cgk_symv_comm(const double *A, const double *v, const double *w, double *y, const void *tiles,
+                  int64_t ntiles, double *rowpart, double *colpart, double *partials, double *dot_out,
+                  cgk_scalars *sc, int64_t m, int64_t n, int rows_in_flight, const cgk_symplan *sp,
+                  const cgk_peers *peers, void *stream);
 /* *d_flag = 1 unless a_ij and a_ji are bit-identical for all i, j (and no NaN). */
 int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void *stream);
 

@@ -287,6 +287,7 @@ static int exchange_windows(cgb_ctx *c)
         for (int g = 0; g < G; ++g) {
             c->peers.mbox[g] = (cgk_mailbox *)c->peer_win[g];
             c->peers.p_full[g] = (double *)((char *)c->peer_win[g] + CGK_WINDOW_HEADER_BYTES);
+            c->peers.crecv[g] = c->peers.p_full[g] + c->n;          /* [ranks][m] = n doubles */
         }
         c->peer_ok = 1;
     } else {
@@ -365,7 +366,8 @@ int cgb_ensure_problem(cgb_ctx *c, int64_t n)
         if (c->ranks > 1) {
             /* [mailbox | p_full] in one allocation of whole 2 MiB pages: one IPC handle */
             const size_t gran = (size_t)2 << 20;
-            c->win_bytes = (CGK_WINDOW_HEADER_BYTES + (size_t)n * sizeof(double) + gran - 1) / gran * gran;
+            /* [mailbox | p_full (n) | column-sum receive area (ranks x m = n)] */
+            c->win_bytes = (CGK_WINDOW_HEADER_BYTES + 2 * (size_t)n * sizeof(double) + gran - 1) / gran * gran;
             CU(cudaMalloc(&c->win, c->win_bytes));
             CU(cudaMemsetAsync(c->win, 0, c->win_bytes, c->stream));
             CU(cudaStreamSynchronize(c->stream));
@@ -480,12 +482,20 @@ static void plan_request_from_options(cgk_gemv_plan *p, const cgb_options *o)
 static int prepare_symv(cgb_ctx *c, const cgb_options *o)
 {
     const int T = cgk_symv_tile();
-    if (c->ranks != 1) FAIL(CGB_ERR_STATE, "cgb_options.symmetric: the upper-tile product runs on one rank in this build");
-    if (c->n % T != 0) {
-        snprintf(tl_err, sizeof tl_err, "cgb_options.symmetric needs n to be a multiple of %d (n = %lld)", T, (long long)c->n);
+    const int multi = c->ranks > 1;
+    if (multi && c->comm_mode != CGB_COMM_PEER)
+        FAIL(CGB_ERR_STATE, "cgb_options.symmetric on several ranks needs the peer-memory exchange (CGB_COMM_PEER)");
+    if (c->n % T != 0 || c->m % T != 0) {
+        snprintf(tl_err, sizeof tl_err, "cgb_options.symmetric needs n (and n / ranks) to be a multiple of %d (n = %lld, ranks = %d)",
+                 T, (long long)c->n, c->ranks);
         return CGB_ERR_ARG;
     }
     cudaStream_t st = c->stream;
+    if (multi && c->sym_state != 1 && o->symmetric != 2)
+        FAIL(CGB_ERR_ARG, "cgb_options.symmetric = 1 on several ranks: a row block cannot verify a_ij == a_ji by itself; "
+                          "generated systems are symmetric by construction, for loaded ones pass symmetric = 2 to assert it");
+    if (multi && o->symmetric == 2 && c->sym_state == 0) c->sym_state = 1;
+    if (c->sym_state == 0 && o->symmetric == 2) c->sym_state = 1;
     if (c->sym_state == 0) {
         int *d_flag = NULL, h_flag = 1;
         CU(cudaMalloc((void **)&d_flag, sizeof(int)));
@@ -499,14 +509,16 @@ static int prepare_symv(cgb_ctx *c, const cgb_options *o)
     if (c->sym_state < 0)
         FAIL(CGB_ERR_ARG, "cgb_options.symmetric: the matrix is not exactly symmetric (a_ij != a_ji somewhere)");
     if (!c->sy_tiles) {
-        const int64_t ntl = c->n / T, cnt = cgk_symv_tile_list(c->n, NULL);
+        if (multi) cgk_symv_make_plan(&c->sy_plan, c->rank, c->ranks, c->m);
+        const int64_t ntl = multi ? c->m / T : c->n / T;      /* tile rows of colpart; rowpart has n / T x m */
+        const int64_t cnt = multi ? cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, NULL) : cgk_symv_tile_list(c->n, NULL);
         int *h = malloc((size_t)cnt * 2 * sizeof(int));
         if (!h) FAIL(CGB_ERR_NOMEM, "out of host memory for the tile list");
-        cgk_symv_tile_list(c->n, h);
+        if (multi) cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, h); else cgk_symv_tile_list(c->n, h);
         cudaError_t ce = cudaMalloc(&c->sy_tiles, (size_t)cnt * 2 * sizeof(int));
         if (ce == cudaSuccess) ce = cudaMemcpy(c->sy_tiles, h, (size_t)cnt * 2 * sizeof(int), cudaMemcpyHostToDevice);
         free(h);
-        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_rowpart, (size_t)ntl * (size_t)c->n * sizeof(double));
+        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_rowpart, (size_t)(c->n / T) * (size_t)c->m * sizeof(double));
         if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_colpart, (size_t)ntl * (size_t)c->n * sizeof(double));
         if (ce != cudaSuccess) {
             (void)cudaGetLastError();
@@ -534,6 +546,12 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
         /* the three collectives live inside the kernels: p slices and dot partials are pushed
          * into the peers' windows over NVLink, consumers spin on their own mailbox */
         if (ev_a) CU(cudaEventRecord(ev_a, st));
+        if (c->use_symv) {
+            KL(cgk_symv_comm(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
+                             c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, c->symv_ru, &c->sy_plan,
+                             &c->peers, st));
+            c->launches += 2;
+        } else
         KL(cgk_gemv_comm(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local,
                          c->sc, c->m, c->n, &c->peers, st));                     /* :290-294 */
         if (ev_b) CU(cudaEventRecord(ev_b, st));
@@ -746,8 +764,9 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->loop_ms = ms_loop; stats->init_ms = ms_init;
         stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds;
         stats->gemv_bytes = 8.0 * ((double)c->m * (double)c->n + (double)c->n + (double)c->m);
-        if (c->use_symv)      /* declared change of algorithmic bytes: the upper triangle, p once, Ap once */
-            stats->gemv_bytes = 8.0 * (0.5 * (double)c->n * ((double)c->n + 1.0) + 2.0 * (double)c->n);
+        if (c->use_symv)      /* declared change of algorithmic bytes: the rank's half of its row block
+                               * (the upper triangle on one rank), p once, Ap once */
+            stats->gemv_bytes = 8.0 * (0.5 * (double)c->m * ((double)c->n + 1.0) + (double)c->n + (double)c->m);
         stats->kernel_launches = c->launches;
         stats->gemv_variant = c->plan.variant; stats->gemv_rows = c->plan.rows_per_cta;
         stats->gemv_unroll = c->plan.unroll; stats->gemv_threads = c->plan.threads;
@@ -802,7 +821,7 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
     plan_request_from_options(&plan, &o);
     KL(cgk_gemv_make_plan(&plan, c->m, c->n, c->A, c->p_full, c->sm_count));
     c->use_symv = 0;
-    if (o.symmetric) {
+    if (o.symmetric && c->ranks == 1) {
         int rc = prepare_symv(c, &o);
         if (rc != CGB_OK) return rc;
     }

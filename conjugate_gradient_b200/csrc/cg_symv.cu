@@ -197,3 +197,255 @@ extern "C" int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void 
     symmetry_check_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, nb, d_flag);
     return (int)cudaGetLastError();
 }
+
+/* ================================================================== row-sharded form (ranks > 1)
+ * Rank g stores rows [g m, (g+1) m) of A and reads HALF of that block (cgk_symplan).  A tile
+ * (I_local, J) gives row sums for the rank's own rows and column sums for columns of block
+ * h = J / mt; the latter belong to rank h and travel there over NVLink:
+ *   symv_tile_comm   as symv_tile, but p_J of a foreign block is read only after that rank's
+ *                    p_flag of this iteration has been seen (tiles of the own block come first
+ *                    in the list, so the exchange of p hides behind them)
+ *   symv_push        column sums of each foreign block, added over the local tile rows in a
+ *                    fixed order, stored into the owner's crecv[rank][...]; last CTA posts c_flag
+ *   symv_finish_comm waits for the c_flags of the ranks that read blocks of MY columns, adds
+ *                    row partials, own-block column partials and the received sums in a fixed
+ *                    order; p.Ap partial pushed to every mailbox as in gemv_ldg_comm_kernel */
+template <int RU>
+__global__ void __launch_bounds__(SY_NT)
+symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 *__restrict__ tiles,
+                      double *__restrict__ rowpart, double *__restrict__ colpart, cgk_scalars *sc,
+                      long long m, long long n, const cgk_peers peers)
+{
+    const int stop = *(volatile int *)&sc->stop_req;
+    if (stop) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
+        return;
+    }
+    const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
+    const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+    __shared__ double s_pI[SY_T];
+    __shared__ double s_row[SY_T];
+    __shared__ double s_col[SY_NW][SY_T];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int2 t = tiles[blockIdx.x];
+    const long long mt = m / SY_T;
+    const long long Il = t.x, J = t.y;
+    const bool diag = ((long long)peers.rank * mt + Il == J);
+    const int h = (int)(J / mt);
+
+    /* the rank's own slice of p needs no flag */
+    for (int i = tid; i < SY_T; i += SY_NT) s_pI[i] = p[(long long)peers.rank * m + Il * SY_T + i];
+    if (h != peers.rank) {
+        if (tid == 0) {
+            const unsigned long long *f = &peers.mbox[peers.rank]->p_flag[h];
+            const unsigned long long tag = (unsigned long long)cgk_tag(gen, ep);
+            unsigned long long t0 = 0ull;
+            unsigned int polls = 0;
+            while (ld_relaxed_sys(f) != tag)
+                if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
+            (void)ld_acquire_sys(f);
+        }
+    }
+    __syncthreads();
+    double pj[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) Ld<4>::coherent(p + J * SY_T + k * 128 + lane * 4, pj[k]);
+
+    double cacc[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) cacc[k][e] = 0.0;
+
+    const double *base = A + (Il * SY_T) * n + J * SY_T + lane * 4;
+    for (int r = wid; r < SY_T; r += SY_NW * RU) {
+        double av[RU][4][4];
+#pragma unroll
+        for (int u = 0; u < RU; ++u)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) Ld<4>::stream(base + (long long)(r + SY_NW * u) * n + k * 128, av[u][k]);
+#pragma unroll
+        for (int u = 0; u < RU; ++u) {
+            double ra[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) ra[k] = fma(av[u][k][e], pj[k][e], ra[k]);
+            if (!diag) {
+                const double pi = s_pI[r + SY_NW * u];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) cacc[k][e] = fma(av[u][k][e], pi, cacc[k][e]);
+            }
+            const double rs = warp_sum((ra[0] + ra[1]) + (ra[2] + ra[3]));
+            if (lane == 0) s_row[r + SY_NW * u] = rs;
+        }
+    }
+    if (!diag) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) s_col[wid][k * 128 + lane * 4 + e] = cacc[k][e];
+    }
+    __syncthreads();
+    for (int i = tid; i < SY_T; i += SY_NT) rowpart[J * m + Il * SY_T + i] = s_row[i];
+    if (!diag) {
+        for (int c = tid; c < SY_T; c += SY_NT) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < SY_NW; ++w) s += s_col[w][c];
+            colpart[Il * n + J * SY_T + c] = s;
+        }
+    }
+}
+
+/* grid: (m / SY_NT, nblk).  Column j of foreign block b: sum over the contributing local tile
+ * rows, pushed into the owner's receive area.  The last CTA posts c_flag to every owner. */
+__global__ void __launch_bounds__(SY_NT)
+symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long m, long long n,
+                 const cgk_symplan sp, const cgk_peers peers)
+{
+    if (*(volatile int *)&sc->stop_req) return;
+    const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
+    const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+    const int b = blockIdx.y;
+    const int h = sp.blk_rank[b];
+    const long long jl = (long long)blockIdx.x * SY_NT + threadIdx.x;        /* column inside block h */
+    if (jl >= (long long)sp.col_begin[b] * SY_T) {
+        double s = 0.0;
+        for (int Il = 0; Il < sp.row_end[b]; ++Il) s += __ldcs(colpart + (long long)Il * n + (long long)h * m + jl);
+        peers.crecv[h][(long long)peers.rank * m + jl] = s;
+    }
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int total = gridDim.x * gridDim.y;
+        s_last = (atomicAdd(&sc->ticket_vec, 1u) == total - 1u);
+        if (s_last) {
+            __threadfence_system();
+            const unsigned long long tag = (unsigned long long)cgk_tag(gen, ep);
+            for (int q = 0; q < sp.nblk; ++q)
+                st_relaxed_sys(&peers.mbox[sp.blk_rank[q]]->c_flag[peers.rank], tag);
+            sc->ticket_vec = 0u;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SY_NT)
+symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
+                        const double *w, double *__restrict__ y, double *__restrict__ partials,
+                        double *__restrict__ dot_out, cgk_scalars *sc, long long m, long long n,
+                        const cgk_symplan sp, const cgk_peers peers)
+{
+    if (*(volatile int *)&sc->stop_req) return;
+    const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
+    const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+    const int tid = threadIdx.x;
+    const long long mt = m / SY_T;
+    const long long i = (long long)blockIdx.x * SY_NT + tid;                 /* local row, < m */
+    const long long Il = i / SY_T;
+    double s = 0.0;
+    /* everything this rank computed itself first (hides the wait for the peers' sums) */
+    for (long long J = (long long)peers.rank * mt + Il; J < (long long)(peers.rank + 1) * mt; ++J)
+        s += __ldcs(rowpart + J * m + i);
+    for (int b = 0; b < sp.nblk; ++b)
+        if (Il < sp.row_end[b])
+            for (long long J = (long long)sp.blk_rank[b] * mt + sp.col_begin[b]; J < (long long)(sp.blk_rank[b] + 1) * mt; ++J)
+                s += __ldcs(rowpart + J * m + i);
+    for (long long I2 = 0; I2 < Il; ++I2) s += __ldcs(colpart + I2 * n + (long long)peers.rank * m + i);
+    /* column sums other ranks computed for my columns */
+    if (tid < sp.nsrc) {
+        const unsigned long long *f = &peers.mbox[peers.rank]->c_flag[sp.src_rank[tid]];
+        const unsigned long long tag = (unsigned long long)cgk_tag(gen, ep);
+        unsigned long long t0 = 0ull;
+        unsigned int polls = 0;
+        while (ld_relaxed_sys(f) != tag)
+            if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) break;
+        (void)ld_acquire_sys(f);
+    }
+    __syncthreads();
+    const double *rx = peers.crecv[peers.rank];
+    for (int q = 0; q < sp.nsrc; ++q)
+        if (Il >= sp.src_col_begin[q]) s += __ldcg(rx + (long long)sp.src_rank[q] * m + i);
+    y[i] = s;
+    double contrib = s * w[i];
+    __shared__ double s_w[SY_NW];
+    contrib = warp_sum(contrib);
+    if ((tid & 31) == 0) s_w[tid >> 5] = contrib;
+    __syncthreads();
+    double mine = 0.0;
+    if (tid == 0)
+        for (int q = 0; q < SY_NW; ++q) mine += s_w[q];
+    double total = 0.0;
+    if (cta_partials_finish_sys<SY_NT>(mine, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {
+        const unsigned int tag = cgk_tag(gen, ep);
+        for (int g = 0; g < peers.ranks; ++g)
+            ll_send(&peers.mbox[g]->dot[0][ep & 1u][peers.rank][0], total, tag);
+        sc->ep_gemv = ep + 1u;
+    }
+}
+
+extern "C" void cgk_symv_make_plan(cgk_symplan *sp, int rank, int ranks, int64_t m)
+{
+    const int G = ranks, mt = (int)(m / SY_T), half = mt / 2;
+    sp->nblk = 0; sp->nsrc = 0;
+    for (int d = 1; d <= G / 2; ++d) {
+        const bool halved = (G % 2 == 0 && d == G / 2);
+        /* blocks I read */
+        const int h = (rank + d) % G;
+        int row_end = mt, col_begin = 0;
+        if (halved) { if (rank < h) row_end = half; else col_begin = half; }
+        if (row_end > 0 && col_begin < mt) {
+            sp->blk_rank[sp->nblk] = h; sp->row_end[sp->nblk] = row_end; sp->col_begin[sp->nblk] = col_begin;
+            sp->nblk++;
+        }
+        /* ranks that read a block of my columns */
+        const int g = (rank - d + G) % G;
+        int g_row_end = mt, g_col_begin = 0;
+        if (halved) { if (g < rank) g_row_end = half; else g_col_begin = half; }
+        if (g_row_end > 0 && g_col_begin < mt) {
+            sp->src_rank[sp->nsrc] = g; sp->src_col_begin[sp->nsrc] = g_col_begin;
+            sp->nsrc++;
+        }
+    }
+}
+
+extern "C" int64_t cgk_symv_tile_list_rank(const cgk_symplan *sp, int rank, int64_t m, int *tiles_xy)
+{
+    const int64_t mt = m / SY_T;
+    int64_t k = 0;
+    for (int64_t Il = 0; Il < mt; ++Il)
+        for (int64_t J = rank * mt + Il; J < (rank + 1) * mt; ++J) {
+            if (tiles_xy) { tiles_xy[2 * k] = (int)Il; tiles_xy[2 * k + 1] = (int)J; }
+            ++k;
+        }
+    for (int b = 0; b < sp->nblk; ++b)
+        for (int64_t Il = 0; Il < sp->row_end[b]; ++Il)
+            for (int64_t Jl = sp->col_begin[b]; Jl < mt; ++Jl) {
+                if (tiles_xy) { tiles_xy[2 * k] = (int)Il; tiles_xy[2 * k + 1] = (int)(sp->blk_rank[b] * mt + Jl); }
+                ++k;
+            }
+    return k;
+}
+
+extern "C" int cgk_symv_comm(const double *A, const double *v, const double *w, double *y, const void *tiles,
+                             int64_t ntiles, double *rowpart, double *colpart, double *partials,
+                             double *dot_out, cgk_scalars *sc, int64_t m, int64_t n, int rows_in_flight,
+                             const cgk_symplan *sp, const cgk_peers *peers, void *stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    if (m % SY_T != 0 || n % SY_T != 0 || ntiles < 1 || !sp || !peers || !w) return (int)cudaErrorInvalidValue;
+    const int2 *tl = (const int2 *)tiles;
+    switch (rows_in_flight) {
+    case 1: symv_tile_comm_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, *peers); break;
+    case 4: symv_tile_comm_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, *peers); break;
+    default: symv_tile_comm_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, *peers); break;
+    }
+    if (sp->nblk > 0)
+        symv_push_kernel<<<dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), SY_NT, 0, st>>>(colpart, sc, (long long)m, (long long)n, *sp, *peers);
+    symv_finish_comm_kernel<<<(unsigned)(m / SY_NT), SY_NT, 0, st>>>(rowpart, colpart, w, y, partials, dot_out, sc,
+                                                                     (long long)m, (long long)n, *sp, *peers);
+    return (int)cudaGetLastError();
+}

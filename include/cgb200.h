@@ -83,10 +83,12 @@ typedef struct cgb_options {
     int     gemv_l2_keep_pct; /* small n (A within ~0.8..3 L2 sizes): % of L2 in which the first rows  */
                            /* of A are kept (evict_last) from one iteration to the next; 0 = the   */
                            /* library default, < 0 = plain streaming                               */
-    int     symmetric;     /* 1: matVec reads only the upper tiles of A (half the bytes, SURVEY.md  */
+    int     symmetric;     /* 1: matVec reads each pair a_ij, a_ji once (half the bytes, SURVEY.md  */
                            /*    8f-4).  Needs a_ij == a_ji bit for bit -- verified on the device   */
-                           /*    once per loaded matrix, CGB_ERR_ARG otherwise -- one rank, and n a */
-                           /*    multiple of 512.  0 (default): the reference's full row products   */
+                           /*    once per loaded matrix on one rank (CGB_ERR_ARG otherwise);        */
+                           /*    several ranks (peer exchange only) accept generated systems, or    */
+                           /*    2 = the caller asserts symmetry.  n / ranks a multiple of 512.     */
+                           /*    0 (default): the reference's full row products                     */
 } cgb_options;
 
 #define CGB_EXIT_STOP_RULE 1       /* sqrt(r.r) < eps                 (parallel_cg.c:314-317)  */

@@ -111,6 +111,34 @@ def test_generated_spread_family_sharded(cg, gpus, comm):
     assert st["final_residual"] < EPS and st["comm"] == comm
 
 
+@pytest.mark.parametrize("gpus,n,k", [(2, 2048, 7), (2, 1024, 0), (4, 4096, 4), (4, 2048, 7), (8, 4096, 4), (8, 8192, 0)])
+def test_symmetric_product_row_sharded(cg, gpus, n, k):
+    # every rank reads half of its row block; column sums travel to their owners over NVLink
+    need(cg, gpus)
+    seed, flags = 50 + gpus, cg.GEN_KAPPA_LOG2(k)
+    x, st = cg.solve_generated(n, seed, gpus=gpus, flags=flags, symmetric=1)
+    xo, so = O.conjugrad(O.gen_A(n, seed, flags), O.gen_b(n, seed, flags), np.zeros(n), ranks=gpus)
+    assert st["gemv_variant"] == 3 and st["comm"] == 2
+    assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    assert st["final_residual"] < EPS
+    x2, st2 = cg.solve_generated(n, seed, gpus=gpus, flags=flags, symmetric=1)
+    np.testing.assert_array_equal(x, x2)                       # fixed-order sums on every rank
+
+
+def test_symmetric_option_on_ranks_needs_assertion_for_loaded_matrices(cg):
+    need(cg, 2)
+    n = 1024
+    A, b = O.spd_with_condition(n, 30.0, seed=8)
+    with pytest.raises(cg.CgbError) as e:
+        cg.conjugrad_host(A, b, np.zeros(n), gpus=2, symmetric=1)
+    assert "symmetric = 2" in str(e.value)
+    x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=2, symmetric=2)
+    xo, so = O.conjugrad(A, b, np.zeros(n), ranks=2)
+    assert st["gemv_variant"] == 3 and relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    with pytest.raises(cg.CgbError):                            # NCCL transport: not available for this product
+        cg.solve_generated(n, 1, gpus=2, symmetric=1, comm=1)
+
+
 def test_not_divisible(cg):
     need(cg, 2)
     with pytest.raises(cg.CgbError) as e:
