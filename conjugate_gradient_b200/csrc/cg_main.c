@@ -30,6 +30,8 @@
  *                     (generateSPDmatrix.m:23-43: one value per line, A and b "%.4f", x0 "%.1f")
  *                     as P_matrix.txt, P_vector.txt, P_x0.txt and P_dimensions.txt; implies
  *                     --round4 so that the files hold exactly the system that is solved
+ *   --symmetric       matVec from the upper tiles only (half the bytes); the matrix must be exactly
+ *                     symmetric (checked on the GPU; with --gpus > 1 only for --gen systems)
  *   --guard           end the solve on p.Ap = 0 / exact x0 instead of iterating NaNs to the
  *                     loop bound as the reference does (parallel_cg.c:298,318)
  *   --run-record FILE machine-readable record of the run (JSON: iterations, sqrt(r.r), exit
@@ -50,7 +52,7 @@
 
 typedef struct {
     const char *fileA, *fileB, *fileX, *dims, *write_x, *record, *emit;
-    int gpus, print_x, stats, round4, gemv, comm, kappa_log2, guard;
+    int gpus, print_x, stats, round4, gemv, comm, kappa_log2, guard, symmetric;
     int64_t gen_n, max_iter, bench_iters;
     uint64_t seed;
     double eps;
@@ -70,6 +72,7 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         else if (!strcmp(a, "--stats")) c->stats = 1;
         else if (!strcmp(a, "--round4")) c->round4 = 1;
         else if (!strcmp(a, "--guard")) c->guard = 1;
+        else if (!strcmp(a, "--symmetric")) c->symmetric = 1;
         else if (!v) { fprintf(stderr, "option %s needs a value\n", a); return -1; }
         else if (!strcmp(a, "--dims")) { c->dims = v; ++i; }
         else if (!strcmp(a, "--write-x")) { c->write_x = v; ++i; }
@@ -213,6 +216,7 @@ int main(int argc, char **argv)
     opt.gemv_variant = cli.gemv;
     opt.comm = cli.comm;
     opt.guard = cli.guard;
+    opt.symmetric = cli.symmetric;
     if (cli.bench_iters > 0) { opt.ignore_stop = 1; opt.max_iter = cli.bench_iters; }
 
     cgb_stats st;

@@ -212,7 +212,7 @@ typedef struct {
     char pad[128 - 64 - 8 - 8 - 4 - 4];
 } window_card;
 
-static int exchange_windows(cgb_ctx *c)
+static int exchange_windows(cgb_ctx *c, int64_t n)
 {
     const int G = c->ranks;
     cudaStream_t st = c->stream;
@@ -287,7 +287,7 @@ static int exchange_windows(cgb_ctx *c)
         for (int g = 0; g < G; ++g) {
             c->peers.mbox[g] = (cgk_mailbox *)c->peer_win[g];
             c->peers.p_full[g] = (double *)((char *)c->peer_win[g] + CGK_WINDOW_HEADER_BYTES);
-            c->peers.crecv[g] = c->peers.p_full[g] + c->n;          /* [ranks][m] = n doubles */
+            c->peers.crecv[g] = c->peers.p_full[g] + n;             /* [ranks][m] = n doubles; c->n is not set yet */
         }
         c->peer_ok = 1;
     } else {
@@ -372,7 +372,7 @@ int cgb_ensure_problem(cgb_ctx *c, int64_t n)
             CU(cudaMemsetAsync(c->win, 0, c->win_bytes, c->stream));
             CU(cudaStreamSynchronize(c->stream));
             c->p_full = (double *)((char *)c->win + CGK_WINDOW_HEADER_BYTES);
-            int rc = exchange_windows(c);
+            int rc = exchange_windows(c, n);
             if (rc != CGB_OK) return rc;
         } else {
             CU(cudaMalloc((void **)&c->p_full, (size_t)n * sizeof(double)));
