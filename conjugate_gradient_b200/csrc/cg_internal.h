@@ -14,7 +14,7 @@ struct cgb_graph_key {
     const void *A;
     const void *win;        /* peer window the captured kernels point into */
     int comm, guard;
-    int symv, symv_ru;
+    int symv, symv_ru, symv_split, pad2_;
 };
 
 struct cgb_ctx {
@@ -57,7 +57,7 @@ struct cgb_ctx {
     char peer_why[160];               /* why peer_ok == 0                                */
     /* symmetric product (cg_symv.cu) */
     int sym_state;                    /* 0 not checked, 1 exactly symmetric, -1 not      */
-    int use_symv, symv_ru;
+    int use_symv, symv_ru, symv_split;
     double *sy_rowpart, *sy_colpart;  /* (n / T) * n each                                */
     void *sy_tiles;
     int64_t sy_ntiles;

@@ -168,22 +168,23 @@ int cgk_l2_flush(void *buf, int64_t bytes, void *stream);
 
 /* ---- symmetric product (cg_symv.cu): y = A v reading only the upper T x T tiles of an exactly
  * symmetric A (n a multiple of cgk_symv_tile(), one GPU).  tiles: device array of (I, J) pairs
- * made from cgk_symv_tile_list(); rowpart / colpart: (n / T) * n doubles each. */
+ * made from cgk_symv_tile_list(); rowpart: (n / T) * n doubles, colpart: split * (n / T) * n. */
 int     cgk_symv_tile(void);
-int64_t cgk_symv_tile_list(int64_t n, int *tiles_xy);
+int64_t cgk_symv_tile_list(int64_t n, int split, int *tiles_xy);   /* split: CTAs (row parts) per tile: 1, 2, 4 */
+int     cgk_symv_pick_split(int64_t tiles, int sm_count);
 int cgk_symv(const double *A, const double *v, const double *w, double *y, const void *tiles,
              int64_t ntiles, double *rowpart, double *colpart, double *partials, double *dot_out,
-             cgk_scalars *sc, int64_t n, int rows_in_flight, void *stream);
+             cgk_scalars *sc, int64_t n, int rows_in_flight, int split, void *stream);
 /* Row-sharded form (ranks > 1, peer windows): local tile rows, p exchange flags checked per
  * tile, column sums pushed to their owners (cgk_symv_comm = tile kernel + push kernel + finish
  * kernel; the finish also pushes the p.Ap partial like cgk_gemv_comm).  tiles: (I_local, J)
- * pairs from cgk_symv_tile_list_rank(); rowpart: (n / T) * m doubles; colpart: (m / T) * n. */
+ * pairs from cgk_symv_tile_list_rank(); rowpart: (n / T) * m doubles; colpart: split * (m / T) * n. */
 void    cgk_symv_make_plan(cgk_symplan *sp, int rank, int ranks, int64_t m);
-int64_t cgk_symv_tile_list_rank(const cgk_symplan *sp, int rank, int64_t m, int *tiles_xy);
+int64_t cgk_symv_tile_list_rank(const cgk_symplan *sp, int rank, int64_t m, int split, int *tiles_xy);
 int cgk_symv_comm(const double *A, const double *v, const double *w, double *y, const void *tiles,
                   int64_t ntiles, double *rowpart, double *colpart, double *partials, double *dot_out,
-                  cgk_scalars *sc, int64_t m, int64_t n, int rows_in_flight, const cgk_symplan *sp,
-                  const cgk_peers *peers, void *stream);
+                  cgk_scalars *sc, int64_t m, int64_t n, int rows_in_flight, int split,
+                  const cgk_symplan *sp, const cgk_peers *peers, void *stream);
 /* *d_flag = 1 unless a_ij and a_ji are bit-identical for all i, j (and no NaN). */
 int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void *stream);
 

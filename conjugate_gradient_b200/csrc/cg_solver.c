@@ -511,15 +511,20 @@ static int prepare_symv(cgb_ctx *c, const cgb_options *o)
     if (!c->sy_tiles) {
         if (multi) cgk_symv_make_plan(&c->sy_plan, c->rank, c->ranks, c->m);
         const int64_t ntl = multi ? c->m / T : c->n / T;      /* tile rows of colpart; rowpart has n / T x m */
-        const int64_t cnt = multi ? cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, NULL) : cgk_symv_tile_list(c->n, NULL);
+        const int64_t whole = multi ? cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, 1, NULL) : cgk_symv_tile_list(c->n, 1, NULL);
+        int split = cgk_symv_pick_split(whole, c->sm_count);
+        const char *es = getenv("CGB_SYMV_SPLIT");
+        if (es && (atoi(es) == 1 || atoi(es) == 2 || atoi(es) == 4)) split = atoi(es);
+        c->symv_split = split;
+        const int64_t cnt = whole * split;
         int *h = malloc((size_t)cnt * 2 * sizeof(int));
         if (!h) FAIL(CGB_ERR_NOMEM, "out of host memory for the tile list");
-        if (multi) cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, h); else cgk_symv_tile_list(c->n, h);
+        if (multi) cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, split, h); else cgk_symv_tile_list(c->n, split, h);
         cudaError_t ce = cudaMalloc(&c->sy_tiles, (size_t)cnt * 2 * sizeof(int));
         if (ce == cudaSuccess) ce = cudaMemcpy(c->sy_tiles, h, (size_t)cnt * 2 * sizeof(int), cudaMemcpyHostToDevice);
         free(h);
         if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_rowpart, (size_t)(c->n / T) * (size_t)c->m * sizeof(double));
-        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_colpart, (size_t)ntl * (size_t)c->n * sizeof(double));
+        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_colpart, (size_t)split * (size_t)ntl * (size_t)c->n * sizeof(double));
         if (ce != cudaSuccess) {
             (void)cudaGetLastError();
             cudaFree(c->sy_tiles); cudaFree(c->sy_rowpart); cudaFree(c->sy_colpart);
@@ -528,7 +533,7 @@ static int prepare_symv(cgb_ctx *c, const cgb_options *o)
         }
         c->sy_ntiles = cnt;
     }
-    c->symv_ru = (o->gemv_unroll == 1 || o->gemv_unroll == 4) ? o->gemv_unroll : 2;
+    c->symv_ru = (o->gemv_unroll == 1 || o->gemv_unroll == 2) ? o->gemv_unroll : 4;   /* 4 rows in flight measured best */
     c->use_symv = 1;
     return CGB_OK;
 }
@@ -548,8 +553,8 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
         if (ev_a) CU(cudaEventRecord(ev_a, st));
         if (c->use_symv) {
             KL(cgk_symv_comm(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                             c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, c->symv_ru, &c->sy_plan,
-                             &c->peers, st));
+                             c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, c->symv_ru, c->symv_split,
+                             &c->sy_plan, &c->peers, st));
             c->launches += 2;
         } else
         KL(cgk_gemv_comm(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local,
@@ -566,7 +571,7 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     if (ev_a) CU(cudaEventRecord(ev_a, st));
     if (c->use_symv) {                                           /* upper tiles only, two kernels */
         KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                    c->partials_gemv, &c->sc->pAp, c->sc, c->n, c->symv_ru, st));
+                    c->partials_gemv, &c->sc->pAp, c->sc, c->n, c->symv_ru, c->symv_split, st));
         c->launches += 1;
     } else
     KL(cgk_gemv(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv,
@@ -590,7 +595,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     key.n = c->n; key.m = c->m; key.max_iter = max_iter; key.eps = o->eps;
     key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan; key.guard = o->guard;
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
-    key.symv = c->use_symv; key.symv_ru = c->symv_ru;
+    key.symv = c->use_symv; key.symv_ru = c->symv_ru; key.symv_split = c->symv_split;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -836,7 +841,7 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
     for (int i = 0; i < warmup; ++i)
         if (c->use_symv)
             KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                        c->partials_gemv, &c->sc->pAp_local, c->sc, c->n, c->symv_ru, st));
+                        c->partials_gemv, &c->sc->pAp_local, c->sc, c->n, c->symv_ru, c->symv_split, st));
         else
         KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
     double sum = 0.0, mn = 1e300;
@@ -845,7 +850,7 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
         CU(cudaEventRecord(c->ev[0], st));
         if (c->use_symv)
             KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                        c->partials_gemv, &c->sc->pAp_local, c->sc, c->n, c->symv_ru, st));
+                        c->partials_gemv, &c->sc->pAp_local, c->sc, c->n, c->symv_ru, c->symv_split, st));
         else
         KL(cgk_gemv(&plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, st));
         CU(cudaEventRecord(c->ev[1], st));

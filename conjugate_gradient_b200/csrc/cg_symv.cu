@@ -28,7 +28,7 @@ template <int RU>
 __global__ void __launch_bounds__(SY_NT)
 symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
                  const int2 *__restrict__ tiles, double *__restrict__ rowpart,
-                 double *__restrict__ colpart, cgk_scalars *__restrict__ sc, long long n)
+                 double *__restrict__ colpart, cgk_scalars *__restrict__ sc, long long n, int split)
 {
     const int stop = *(volatile int *)&sc->stop_req;
     if (stop) {
@@ -39,8 +39,11 @@ symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
     __shared__ double s_row[SY_T];
     __shared__ double s_col[SY_NW][SY_T];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    /* a tile is read by `split` CTAs, each taking SY_T / split of its rows (more, smaller work
+     * items when a GPU has few tiles: the last wave of CTAs stays full) */
     const int2 t = tiles[blockIdx.x];
-    const long long I = t.x, J = t.y;
+    const long long I = t.x & 0xffffff, J = t.y;
+    const int part = t.x >> 24, rows_per = SY_T / split, r_lo = part * rows_per, r_hi = r_lo + rows_per;
     const bool diag = (I == J);
 
     double pj[4][4];
@@ -56,7 +59,7 @@ symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
         for (int e = 0; e < 4; ++e) cacc[k][e] = 0.0;
 
     const double *base = A + (I * SY_T) * n + J * SY_T + lane * 4;
-    for (int r = wid; r < SY_T; r += SY_NW * RU) {
+    for (int r = r_lo + wid; r < r_hi; r += SY_NW * RU) {
         double av[RU][4][4];
 #pragma unroll
         for (int u = 0; u < RU; ++u)
@@ -88,13 +91,13 @@ symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
     }
     __syncthreads();
     /* rowpart[J][i]: contiguous in i for a fixed J, so both this store and the finish are coalesced */
-    for (int i = tid; i < SY_T; i += SY_NT) rowpart[J * n + I * SY_T + i] = s_row[i];
+    for (int i = r_lo + tid; i < r_hi; i += SY_NT) rowpart[J * n + I * SY_T + i] = s_row[i];
     if (!diag) {
         for (int c = tid; c < SY_T; c += SY_NT) {
             double s = 0.0;
 #pragma unroll
             for (int w = 0; w < SY_NW; ++w) s += s_col[w][c];
-            colpart[I * n + J * SY_T + c] = s;
+            colpart[(I * split + part) * n + J * SY_T + c] = s;
         }
     }
 }
@@ -105,14 +108,14 @@ __global__ void __launch_bounds__(SY_NT)
 symv_finish_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
                    const double *__restrict__ w, double *__restrict__ y,
                    double *__restrict__ partials, double *__restrict__ dot_out,
-                   cgk_scalars *__restrict__ sc, long long n)
+                   cgk_scalars *__restrict__ sc, long long n, int split)
 {
     if (*(volatile int *)&sc->stop_req) return;
     const long long i = (long long)blockIdx.x * SY_NT + threadIdx.x;     /* n % SY_T == 0: always < n */
     const long long I = i / SY_T, ntl = n / SY_T;
     double s = 0.0;
     for (long long J = I; J < ntl; ++J) s += __ldcs(rowpart + J * n + i);
-    for (long long I2 = 0; I2 < I; ++I2) s += __ldcs(colpart + I2 * n + i);
+    for (long long I2 = 0; I2 < I * split; ++I2) s += __ldcs(colpart + I2 * n + i);
     y[i] = s;
     if (w == nullptr) return;
     double contrib = s * w[i];
@@ -159,32 +162,44 @@ symmetry_check_kernel(const double *__restrict__ A, long long n, long long nb, i
 extern "C" int cgk_symv_tile(void) { return SY_T; }
 
 /* Fills tiles[] (host) with the upper tile triangle, row-major; returns the count. */
-extern "C" int64_t cgk_symv_tile_list(int64_t n, int *tiles_xy)
+extern "C" int64_t cgk_symv_tile_list(int64_t n, int split, int *tiles_xy)
 {
     const int64_t ntl = n / SY_T;
     int64_t k = 0;
     for (int64_t I = 0; I < ntl; ++I)
-        for (int64_t J = I; J < ntl; ++J) {
-            if (tiles_xy) { tiles_xy[2 * k] = (int)I; tiles_xy[2 * k + 1] = (int)J; }
-            ++k;
-        }
+        for (int64_t J = I; J < ntl; ++J)
+            for (int part = 0; part < split; ++part) {
+                if (tiles_xy) { tiles_xy[2 * k] = (int)I | (part << 24); tiles_xy[2 * k + 1] = (int)J; }
+                ++k;
+            }
     return k;
+}
+
+/* Row parts per tile.  Measured on B200 (profiles/r01_symv_split_sweep.txt): splitting costs 2-5 %
+ * (every part repeats the tile's prologue and column-sum epilogue) and never pays once there is a
+ * tile per SM; it only serves to put every SM to work when a GPU has fewer tiles than SMs. */
+extern "C" int cgk_symv_pick_split(int64_t tiles, int sm_count)
+{
+    const int64_t sms = sm_count > 0 ? sm_count : 148;
+    if (tiles * 10 >= sms * 9) return 1;
+    if (tiles * 2 >= sms) return 2;
+    return 4;
 }
 
 extern "C" int cgk_symv(const double *A, const double *v, const double *w, double *y,
                         const void *tiles, int64_t ntiles, double *rowpart, double *colpart,
                         double *partials, double *dot_out, cgk_scalars *sc, int64_t n, int rows_in_flight,
-                        void *stream)
+                        int split, void *stream)
 {
     cudaStream_t st = (cudaStream_t)stream;
-    if (n % SY_T != 0 || ntiles < 1) return (int)cudaErrorInvalidValue;
+    if (n % SY_T != 0 || ntiles < 1 || (split != 1 && split != 2 && split != 4)) return (int)cudaErrorInvalidValue;
     const int2 *tl = (const int2 *)tiles;
     switch (rows_in_flight) {
-    case 1: symv_tile_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n); break;
-    case 4: symv_tile_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n); break;
-    default: symv_tile_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n); break;
+    case 1: symv_tile_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    case 2: symv_tile_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    default: symv_tile_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
     }
-    symv_finish_kernel<<<(unsigned)(n / SY_NT), SY_NT, 0, st>>>(rowpart, colpart, w, y, partials, dot_out, sc, (long long)n);
+    symv_finish_kernel<<<(unsigned)(n / SY_NT), SY_NT, 0, st>>>(rowpart, colpart, w, y, partials, dot_out, sc, (long long)n, split);
     return (int)cudaGetLastError();
 }
 
@@ -214,7 +229,7 @@ template <int RU>
 __global__ void __launch_bounds__(SY_NT)
 symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 *__restrict__ tiles,
                       double *__restrict__ rowpart, double *__restrict__ colpart, cgk_scalars *sc,
-                      long long m, long long n, const cgk_peers peers)
+                      long long m, long long n, int split, const cgk_peers peers)
 {
     const int stop = *(volatile int *)&sc->stop_req;
     if (stop) {
@@ -229,7 +244,8 @@ symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int2 t = tiles[blockIdx.x];
     const long long mt = m / SY_T;
-    const long long Il = t.x, J = t.y;
+    const long long Il = t.x & 0xffffff, J = t.y;
+    const int part = t.x >> 24, rows_per = SY_T / split, r_lo = part * rows_per, r_hi = r_lo + rows_per;
     const bool diag = ((long long)peers.rank * mt + Il == J);
     const int h = (int)(J / mt);
 
@@ -258,7 +274,7 @@ symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 
         for (int e = 0; e < 4; ++e) cacc[k][e] = 0.0;
 
     const double *base = A + (Il * SY_T) * n + J * SY_T + lane * 4;
-    for (int r = wid; r < SY_T; r += SY_NW * RU) {
+    for (int r = r_lo + wid; r < r_hi; r += SY_NW * RU) {
         double av[RU][4][4];
 #pragma unroll
         for (int u = 0; u < RU; ++u)
@@ -289,13 +305,13 @@ symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 
             for (int e = 0; e < 4; ++e) s_col[wid][k * 128 + lane * 4 + e] = cacc[k][e];
     }
     __syncthreads();
-    for (int i = tid; i < SY_T; i += SY_NT) rowpart[J * m + Il * SY_T + i] = s_row[i];
+    for (int i = r_lo + tid; i < r_hi; i += SY_NT) rowpart[J * m + Il * SY_T + i] = s_row[i];
     if (!diag) {
         for (int c = tid; c < SY_T; c += SY_NT) {
             double s = 0.0;
 #pragma unroll
             for (int w = 0; w < SY_NW; ++w) s += s_col[w][c];
-            colpart[Il * n + J * SY_T + c] = s;
+            colpart[(Il * split + part) * n + J * SY_T + c] = s;
         }
     }
 }
@@ -303,7 +319,7 @@ symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 
 /* grid: (m / SY_NT, nblk).  Column j of foreign block b: sum over the contributing local tile
  * rows, pushed into the owner's receive area.  The last CTA posts c_flag to every owner. */
 __global__ void __launch_bounds__(SY_NT)
-symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long m, long long n,
+symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long m, long long n, int split,
                  const cgk_symplan sp, const cgk_peers peers)
 {
     if (*(volatile int *)&sc->stop_req) return;
@@ -314,7 +330,7 @@ symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long 
     const long long jl = (long long)blockIdx.x * SY_NT + threadIdx.x;        /* column inside block h */
     if (jl >= (long long)sp.col_begin[b] * SY_T) {
         double s = 0.0;
-        for (int Il = 0; Il < sp.row_end[b]; ++Il) s += __ldcs(colpart + (long long)Il * n + (long long)h * m + jl);
+        for (int Il = 0; Il < sp.row_end[b] * split; ++Il) s += __ldcs(colpart + (long long)Il * n + (long long)h * m + jl);
         peers.crecv[h][(long long)peers.rank * m + jl] = s;
     }
     __shared__ int s_last;
@@ -336,7 +352,7 @@ symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long 
 __global__ void __launch_bounds__(SY_NT)
 symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
                         const double *w, double *__restrict__ y, double *__restrict__ partials,
-                        double *__restrict__ dot_out, cgk_scalars *sc, long long m, long long n,
+                        double *__restrict__ dot_out, cgk_scalars *sc, long long m, long long n, int split,
                         const cgk_symplan sp, const cgk_peers peers)
 {
     if (*(volatile int *)&sc->stop_req) return;
@@ -354,7 +370,7 @@ symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__rest
         if (Il < sp.row_end[b])
             for (long long J = (long long)sp.blk_rank[b] * mt + sp.col_begin[b]; J < (long long)(sp.blk_rank[b] + 1) * mt; ++J)
                 s += __ldcs(rowpart + J * m + i);
-    for (long long I2 = 0; I2 < Il; ++I2) s += __ldcs(colpart + I2 * n + (long long)peers.rank * m + i);
+    for (long long I2 = 0; I2 < Il * split; ++I2) s += __ldcs(colpart + I2 * n + (long long)peers.rank * m + i);
     /* column sums other ranks computed for my columns */
     if (tid < sp.nsrc) {
         const unsigned long long *f = &peers.mbox[peers.rank]->c_flag[sp.src_rank[tid]];
@@ -412,40 +428,43 @@ extern "C" void cgk_symv_make_plan(cgk_symplan *sp, int rank, int ranks, int64_t
     }
 }
 
-extern "C" int64_t cgk_symv_tile_list_rank(const cgk_symplan *sp, int rank, int64_t m, int *tiles_xy)
+extern "C" int64_t cgk_symv_tile_list_rank(const cgk_symplan *sp, int rank, int64_t m, int split, int *tiles_xy)
 {
     const int64_t mt = m / SY_T;
     int64_t k = 0;
     for (int64_t Il = 0; Il < mt; ++Il)
-        for (int64_t J = rank * mt + Il; J < (rank + 1) * mt; ++J) {
-            if (tiles_xy) { tiles_xy[2 * k] = (int)Il; tiles_xy[2 * k + 1] = (int)J; }
-            ++k;
-        }
-    for (int b = 0; b < sp->nblk; ++b)
-        for (int64_t Il = 0; Il < sp->row_end[b]; ++Il)
-            for (int64_t Jl = sp->col_begin[b]; Jl < mt; ++Jl) {
-                if (tiles_xy) { tiles_xy[2 * k] = (int)Il; tiles_xy[2 * k + 1] = (int)(sp->blk_rank[b] * mt + Jl); }
+        for (int64_t J = rank * mt + Il; J < (rank + 1) * mt; ++J)
+            for (int part = 0; part < split; ++part) {
+                if (tiles_xy) { tiles_xy[2 * k] = (int)Il | (part << 24); tiles_xy[2 * k + 1] = (int)J; }
                 ++k;
             }
+    for (int b = 0; b < sp->nblk; ++b)
+        for (int64_t Il = 0; Il < sp->row_end[b]; ++Il)
+            for (int64_t Jl = sp->col_begin[b]; Jl < mt; ++Jl)
+                for (int part = 0; part < split; ++part) {
+                    if (tiles_xy) { tiles_xy[2 * k] = (int)Il | (part << 24); tiles_xy[2 * k + 1] = (int)(sp->blk_rank[b] * mt + Jl); }
+                    ++k;
+                }
     return k;
 }
 
 extern "C" int cgk_symv_comm(const double *A, const double *v, const double *w, double *y, const void *tiles,
                              int64_t ntiles, double *rowpart, double *colpart, double *partials,
                              double *dot_out, cgk_scalars *sc, int64_t m, int64_t n, int rows_in_flight,
-                             const cgk_symplan *sp, const cgk_peers *peers, void *stream)
+                             int split, const cgk_symplan *sp, const cgk_peers *peers, void *stream)
 {
     cudaStream_t st = (cudaStream_t)stream;
     if (m % SY_T != 0 || n % SY_T != 0 || ntiles < 1 || !sp || !peers || !w) return (int)cudaErrorInvalidValue;
+    if (split != 1 && split != 2 && split != 4) return (int)cudaErrorInvalidValue;
     const int2 *tl = (const int2 *)tiles;
     switch (rows_in_flight) {
-    case 1: symv_tile_comm_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, *peers); break;
-    case 4: symv_tile_comm_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, *peers); break;
-    default: symv_tile_comm_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, *peers); break;
+    case 1: symv_tile_comm_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    case 2: symv_tile_comm_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    default: symv_tile_comm_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
     }
     if (sp->nblk > 0)
-        symv_push_kernel<<<dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), SY_NT, 0, st>>>(colpart, sc, (long long)m, (long long)n, *sp, *peers);
+        symv_push_kernel<<<dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), SY_NT, 0, st>>>(colpart, sc, (long long)m, (long long)n, split, *sp, *peers);
     symv_finish_comm_kernel<<<(unsigned)(m / SY_NT), SY_NT, 0, st>>>(rowpart, colpart, w, y, partials, dot_out, sc,
-                                                                     (long long)m, (long long)n, *sp, *peers);
+                                                                     (long long)m, (long long)n, split, *sp, *peers);
     return (int)cudaGetLastError();
 }

@@ -21,14 +21,15 @@ def plan_and_tiles(rank, ranks, mt):
     L = cg.lib()
     L.cgk_symv_make_plan.argtypes = [C.POINTER(SymPlan), C.c_int, C.c_int, C.c_int64]
     L.cgk_symv_make_plan.restype = None
-    L.cgk_symv_tile_list_rank.argtypes = [C.POINTER(SymPlan), C.c_int, C.c_int64, C.POINTER(C.c_int)]
+    L.cgk_symv_tile_list_rank.argtypes = [C.POINTER(SymPlan), C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_int)]
     L.cgk_symv_tile_list_rank.restype = C.c_int64
     sp = SymPlan()
     m = mt * T
     L.cgk_symv_make_plan(C.byref(sp), rank, ranks, m)
-    cnt = L.cgk_symv_tile_list_rank(C.byref(sp), rank, m, None)
+    cnt = L.cgk_symv_tile_list_rank(C.byref(sp), rank, m, 1, None)
     buf = (C.c_int * (2 * cnt))()
-    assert L.cgk_symv_tile_list_rank(C.byref(sp), rank, m, buf) == cnt
+    assert L.cgk_symv_tile_list_rank(C.byref(sp), rank, m, 1, buf) == cnt
+    assert L.cgk_symv_tile_list_rank(C.byref(sp), rank, m, 4, None) == 4 * cnt
     return sp, [(buf[2 * k], buf[2 * k + 1]) for k in range(cnt)]
 
 
