@@ -299,6 +299,22 @@ def b200_arm(args):
                      "note": "cgb_options.symmetric=1: 8(n(n+1)/2 + 2n) bytes per product instead of 8(n*n + 2n); "
                              "exact symmetry is verified on the device before use"}
 
+    # ---- opt-in recurrence: Chronopoulos-Gear CG, two kernels and one exposed reduction per iteration
+    fused = None
+    if st["comm"] in (0, 2):
+        ctx.set_x0(np.zeros(n))
+        barrier()
+        stf = ctx.solve(ignore_stop=1, max_iter=K, cg_variant=1, **gopts)
+        barrier()
+        fused = {"value": K / (max_over_ranks(stf["loop_ms"]) * 1e-3), "unit": UNIT,
+                 "note": "cgb_options.cg_variant=1, full product, graph replay; with symmetric=1 as well: see fused_symmetric"}
+        if symmetric:
+            ctx.set_x0(np.zeros(n))
+            barrier()
+            stfs = ctx.solve(ignore_stop=1, max_iter=K, cg_variant=1, symmetric=1, **gopts)
+            barrier()
+            fused["fused_symmetric"] = K / (max_over_ranks(stfs["loop_ms"]) * 1e-3)
+
     peak, peak_src = peak_hbm_gbs()
     gbytes = gemv_bytes(m, n)
     traffic, traffic_src = ncu_traffic(n, world)
@@ -328,6 +344,8 @@ def b200_arm(args):
     }
     if symmetric:
         line["symmetric_variant"] = symmetric
+    if fused:
+        line["fused_reductions_variant"] = fused
     return ctx, line, (rank, world, local, n, m, K, barrier, max_over_ranks, gopts, dist)
 
 

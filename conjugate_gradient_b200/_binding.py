@@ -36,7 +36,7 @@ class Options(C.Structure):
                 ("use_graph", C.c_int), ("check_every", C.c_int), ("time_gemv", C.c_int),
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
-                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("gemv_l2_keep_pct", C.c_int), ("symmetric", C.c_int)]
+                ("gemv_tile_cols", C.c_int), ("comm", C.c_int), ("guard", C.c_int), ("gemv_l2_keep_pct", C.c_int), ("symmetric", C.c_int), ("cg_variant", C.c_int)]
 
 
 class Stats(C.Structure):
@@ -50,11 +50,14 @@ class Stats(C.Structure):
                 ("gemv_variant", C.c_int), ("gemv_rows", C.c_int), ("gemv_unroll", C.c_int),
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
                 ("gemv_tile_cols", C.c_int), ("gemv_grid", C.c_int), ("graph_chunk", C.c_int),
-                ("comm", C.c_int), ("exit_reason", C.c_int), ("reserved", C.c_int * 1),
+                ("comm", C.c_int), ("exit_reason", C.c_int), ("cg_variant", C.c_int),
                 ("gemv_keep_rows", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+
+
+CG_CLASSIC, CG_FUSED_REDUCTIONS = 0, 1
 
 
 def header_symbols():

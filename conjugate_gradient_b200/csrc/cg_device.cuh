@@ -226,7 +226,7 @@ __device__ __forceinline__ void warp_wait_p_flags(const cgk_peers &peers, unsign
  * system-scope and cumulative over the CTA's stores (all before the preceding barrier), so
  * whatever the last CTA posts afterwards is ordered behind every CTA's peer stores.  Returns
  * true in all threads of the last CTA; *total is valid in its thread 0. */
-template <int NT>
+template <int NT, bool SYS = true>
 __device__ __forceinline__ bool cta_partials_finish_sys(double mine, double *partials, double *out,
                                                         unsigned int *ticket, double *total)
 {
@@ -235,7 +235,7 @@ __device__ __forceinline__ bool cta_partials_finish_sys(double mine, double *par
     const int tid = threadIdx.x;
     if (tid == 0) {
         partials[blockIdx.x] = mine;
-        __threadfence_system();
+        if constexpr (SYS) __threadfence_system(); else __threadfence();
         unsigned int t = atomicAdd(ticket, 1u);
         s_last = (t == gridDim.x - 1);
     }
@@ -254,7 +254,7 @@ __device__ __forceinline__ bool cta_partials_finish_sys(double mine, double *par
         *out = t;
         *total = t;
         *ticket = 0u;
-        __threadfence_system();
+        if constexpr (SYS) __threadfence_system();
     }
     return true;
 }

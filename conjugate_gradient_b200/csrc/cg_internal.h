@@ -14,7 +14,7 @@ struct cgb_graph_key {
     const void *A;
     const void *win;        /* peer window the captured kernels point into */
     int comm, guard;
-    int symv, symv_ru, symv_split, pad2_;
+    int symv, symv_ru, symv_split, cg_variant;
 };
 
 struct cgb_ctx {
@@ -29,7 +29,8 @@ struct cgb_ctx {
     /* problem (device) */
     int64_t n, m, cap_n, cap_m;
     double *A;              /* m x n row block, row-major                       */
-    double *b, *r, *Ap;     /* m                                                */
+    double *b, *r, *Ap;     /* m (fused-reductions CG: r holds the direction p, Ap holds w = A r) */
+    double *svec;           /* m: s = A p of the fused-reductions recurrence     */
     double *p_full;         /* n: gathered direction; own slice at rank*m; with ranks > 1 it
                              * lives inside `win`, the window the peers map       */
     double *x_full;         /* n: x0 on entry; own slice updated; gathered at end */

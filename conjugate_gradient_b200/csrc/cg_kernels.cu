@@ -665,6 +665,82 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
     }
 }
 
+/* See cgk_cg2_step in cg_kernels.h.  Launch k does the bookkeeping of iteration k-1 (its r.r is
+ * only complete now) and, unless the solve ends there, the updates of iteration k.  Every CTA
+ * derives the same decisions from the same scalars, none from a flag written in this launch. */
+template <bool COMM>
+__global__ void __launch_bounds__(VEC_NT)
+cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec, double *__restrict__ svec,
+                const double *__restrict__ w, double *__restrict__ partials, cgk_scalars *sc, double eps,
+                int ignore_stop, int guard, long long max_iter, long long m, const cgk_peers peers)
+{
+    if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
+    const unsigned int k = *(volatile unsigned int *)&sc->ep_xr;
+    const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+    double gamma, delta;
+    if constexpr (COMM) {
+        delta = ll_gather_sum(&peers.mbox[peers.rank]->dot[0][k & 1u][0][0], peers.ranks, cgk_tag(gen, k), sc);
+        gamma = (k == 0u) ? sc->rr[0]
+                          : ll_gather_sum(&peers.mbox[peers.rank]->dot[1][k & 1u][0][0], peers.ranks, cgk_tag(gen, k), sc);
+    } else {
+        delta = sc->pAp;
+        gamma = sc->rr[0];
+    }
+    const bool hit = (k > 0u) && sqrt(gamma) < eps;               /* the reference tests after an update only */
+    const bool brk = hit && !ignore_stop;
+    const bool spent = (long long)k >= max_iter;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (k > 0u) {
+            sc->iters = (long long)k;
+            sc->final_beta = gamma;
+            if (hit && sc->first_hit < 0) sc->first_hit = (long long)k - 1;
+        }
+        if (brk) { sc->break_k = (long long)k - 1; sc->stop_req = 1; }
+        else if (spent) sc->stop_req = 2;
+    }
+    if (brk || spent) return;
+    const double gprev = sc->cg2_gamma_prev, aprev = sc->cg2_alpha_prev;
+    const double beta = (k == 0u) ? 0.0 : gamma / gprev;
+    const double alpha = (k == 0u) ? gamma / delta : gamma / (delta - beta * gamma / aprev);
+    if (guard && !isfinite(alpha)) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) { sc->breakdown = 3; sc->stop_req = 3; }
+        return;
+    }
+    const long long lo = COMM ? (long long)peers.rank * m : 0;
+    double acc = 0.0;
+    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
+         i += (long long)gridDim.x * VEC_NT) {
+        const double pi = __dadd_rn(r_loc[i], __dmul_rn(pvec[i], beta));
+        const double si = __dadd_rn(w[i], __dmul_rn(svec[i], beta));
+        pvec[i] = pi;
+        svec[i] = si;
+        x[i] = __dadd_rn(x[i], __dmul_rn(pi, alpha));
+        const double rn = __dsub_rn(r_loc[i], __dmul_rn(si, alpha));
+        r_loc[i] = rn;
+        if constexpr (COMM) {
+            for (int g = 0; g < peers.ranks; ++g)
+                if (g != peers.rank) peers.p_full[g][lo + i] = rn;
+        }
+        acc = fma(rn, rn, acc);
+    }
+    const double mine = vec_cta_sum(acc);
+    double total = 0.0;
+    /* one rank: device-scope fences are enough (a system-scope fence costs microseconds) */
+    if (cta_partials_finish_sys<VEC_NT, COMM>(mine, partials, COMM ? &sc->rr_local : &sc->rr[0], &sc->ticket_vec, &total) &&
+        threadIdx.x == 0) {
+        if constexpr (COMM) {
+            const unsigned int e = k + 1u;
+            for (int g = 0; g < peers.ranks; ++g)
+                ll_send(&peers.mbox[g]->dot[1][e & 1u][peers.rank][0], total, cgk_tag(gen, e));
+            post_p_flags(peers, cgk_tag(gen, e));
+        }
+        sc->cg2_gamma_prev = gamma;
+        sc->cg2_alpha_prev = alpha;
+        sc->pAp = delta;
+        sc->ep_xr = k + 1u;
+    }
+}
+
 __global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
 {
     sc->rr[0] = sc->rr[1] = 0.0;
@@ -676,6 +752,7 @@ __global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
     sc->gen = gen; sc->ep_gemv = sc->ep_xr = sc->ep_p = 0u;
     sc->comm_error = 0;
     sc->breakdown = 0;
+    sc->cg2_gamma_prev = 0.0; sc->cg2_alpha_prev = 0.0;
 }
 
 template <bool COMM>
@@ -1053,6 +1130,19 @@ extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int
     else
         p_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
                                                                                 (long long)max_iter, (long long)m, k_no_peers);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_cg2_step(double *x, double *r_loc, double *pvec, double *svec, const double *w,
+                            double *partials, cgk_scalars *sc, double eps, int ignore_stop, int guard,
+                            int64_t max_iter, int64_t m, const cgk_peers *peers, void *stream)
+{
+    if (peers)
+        cg2_step_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
+                                                                               ignore_stop, guard, (long long)max_iter, (long long)m, *peers);
+    else
+        cg2_step_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
+                                                                                ignore_stop, guard, (long long)max_iter, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
 

@@ -39,6 +39,8 @@ typedef struct cgk_scalars {
     unsigned int gen;      /* solve generation: high bits of every tag, set by cgk_reset      */
     unsigned int ep_gemv, ep_xr, ep_p;
     int comm_error;        /* a spin on a peer's flag ran into CGK_SPIN_TIMEOUT_NS            */
+    double cg2_gamma_prev; /* CGB_CG_FUSED_REDUCTIONS: gamma and alpha of the previous iteration      */
+    double cg2_alpha_prev;
     int breakdown;         /* guard mode only: 3 = alpha not finite (p.Ap = 0), 4 = r0.r0 = 0;   */
                            /* written by cgk_xr_update / cgk_after_init, read by LATER kernels  */
 } cgk_scalars;
@@ -150,6 +152,18 @@ int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
 int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
                  int ignore_stop, int64_t max_iter, int64_t m, const cgk_peers *peers,
                  void *stream);
+
+/* One iteration of the Chronopoulos-Gear form of CG (the two per-iteration
+ * reductions of parallel_cg.c:294,313 merged into one exposed synchronisation).  With gamma =
+ * r.r and delta = r.(A r) of the CURRENT residual (both complete when the product w = A r ends):
+ *   stop rule on gamma (as parallel_cg.c:314-317, after iteration k-1's update);
+ *   beta = gamma/gamma_prev, alpha = gamma / (delta - beta gamma / alpha_prev)   (k = 0: 0, gamma/delta)
+ *   p = r + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  partial of the new r.r
+ * r lives in the gathered vector (r_loc = the rank's slice of it) because the NEXT product is
+ * A r; with peers the new slice is pushed to every rank and tagged like p in cgk_p_update. */
+int cgk_cg2_step(double *x, double *r_loc, double *pvec, double *svec, const double *w, double *partials,
+                 cgk_scalars *sc, double eps, int ignore_stop, int guard, int64_t max_iter, int64_t m,
+                 const cgk_peers *peers, void *stream);
 
 /* Resets the scalars for a new solve (first kernel of the init phase). */
 int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream);

@@ -188,7 +188,8 @@ static void free_problem(cgb_ctx *c)
 {
     drop_graph(c);
     close_peers(c);
-    cudaFree(c->A); cudaFree(c->b); cudaFree(c->r); cudaFree(c->Ap);
+    cudaFree(c->A); cudaFree(c->b); cudaFree(c->r); cudaFree(c->Ap); cudaFree(c->svec);
+    c->svec = NULL;
     if (c->win) cudaFree(c->win); else cudaFree(c->p_full);
     cudaFree(c->x_full); cudaFree(c->partials_gemv);
     cudaFree(c->sy_rowpart); cudaFree(c->sy_colpart); cudaFree(c->sy_tiles);
@@ -363,6 +364,7 @@ int cgb_ensure_problem(cgb_ctx *c, int64_t n)
         CU(cudaMalloc((void **)&c->b, (size_t)m * sizeof(double)));
         CU(cudaMalloc((void **)&c->r, (size_t)m * sizeof(double)));
         CU(cudaMalloc((void **)&c->Ap, (size_t)m * sizeof(double)));
+        CU(cudaMalloc((void **)&c->svec, (size_t)m * sizeof(double)));
         if (c->ranks > 1) {
             /* [mailbox | p_full] in one allocation of whole 2 MiB pages: one IPC handle */
             const size_t gran = (size_t)2 << 20;
@@ -538,6 +540,47 @@ static int prepare_symv(cgb_ctx *c, const cgb_options *o)
     return CGB_OK;
 }
 
+/* The matVec of one iteration with whatever exchange it carries: y = A_blk v into c->Ap and the
+ * (all-reduced, or pushed) dot w.y, where v is the gathered vector and w the rank's slice of it.
+ * Classic CG: v = p (parallel_cg.c:290-294).  Fused-reductions CG: v = r. */
+static int enqueue_product(cgb_ctx *c, cudaEvent_t ev_a, cudaEvent_t ev_b)
+{
+    const int multi = c->ranks > 1;
+    double *v_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
+    cudaStream_t st = c->stream;
+    if (c->comm_mode == CGB_COMM_PEER) {
+        /* the collectives live inside the kernels: slices and dot partials are pushed into the
+         * peers' windows over NVLink, consumers spin on their own mailbox */
+        if (ev_a) CU(cudaEventRecord(ev_a, st));
+        if (c->use_symv) {
+            KL(cgk_symv_comm(c->A, c->p_full, v_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
+                             c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, c->symv_ru, c->symv_split,
+                             &c->sy_plan, &c->peers, st));
+            c->launches += 2;
+        } else
+        KL(cgk_gemv_comm(&c->plan, c->A, c->p_full, v_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local,
+                         c->sc, c->m, c->n, &c->peers, st));                     /* :290-294 */
+        if (ev_b) CU(cudaEventRecord(ev_b, st));
+        c->launches += 1;
+        return CGB_OK;
+    }
+    if (multi)                                                   /* MPI_Allgather(p), :290-291 */
+        NC(ncclAllGather(v_loc, c->p_full, (size_t)c->m, ncclDouble, c->comm, st));
+    if (ev_a) CU(cudaEventRecord(ev_a, st));
+    if (c->use_symv) {                                           /* upper tiles only, two kernels */
+        KL(cgk_symv(c->A, c->p_full, v_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
+                    c->partials_gemv, &c->sc->pAp, c->sc, c->n, c->symv_ru, c->symv_split, st));
+        c->launches += 1;
+    } else
+    KL(cgk_gemv(&c->plan, c->A, c->p_full, v_loc, c->Ap, c->partials_gemv,
+                multi ? &c->sc->pAp_local : &c->sc->pAp, c->sc, c->m, c->n, st));   /* :292-293 */
+    if (ev_b) CU(cudaEventRecord(ev_b, st));
+    if (multi)                                                   /* MPI_Allreduce(alpha), :294 */
+        NC(ncclAllReduce(&c->sc->pAp_local, &c->sc->pAp, 1, ncclDouble, ncclSum, c->comm, st));
+    c->launches += 1;
+    return CGB_OK;
+}
+
 /* One CG iteration on the solver stream; `cur` is the parity of the loop index
  * (selects which rr[] slot is rho).  Mirrors parallel_cg.c:290-323. */
 static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int cur,
@@ -547,44 +590,29 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     double *x_loc = c->x_full + (size_t)c->rank * (size_t)c->m;
     cudaStream_t st = c->stream;
-    if (c->comm_mode == CGB_COMM_PEER) {
-        /* the three collectives live inside the kernels: p slices and dot partials are pushed
-         * into the peers' windows over NVLink, consumers spin on their own mailbox */
-        if (ev_a) CU(cudaEventRecord(ev_a, st));
-        if (c->use_symv) {
-            KL(cgk_symv_comm(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                             c->partials_gemv, &c->sc->pAp_local, c->sc, c->m, c->n, c->symv_ru, c->symv_split,
-                             &c->sy_plan, &c->peers, st));
-            c->launches += 2;
-        } else
-        KL(cgk_gemv_comm(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv, &c->sc->pAp_local,
-                         c->sc, c->m, c->n, &c->peers, st));                     /* :290-294 */
-        if (ev_b) CU(cudaEventRecord(ev_b, st));
+    const cgk_peers *peers = c->comm_mode == CGB_COMM_PEER ? &c->peers : NULL;
+    if (o->cg_variant == CGB_CG_FUSED_REDUCTIONS) {
+        /* [step k: bookkeeping of k-1, updates of k, new r pushed] [w = A r, delta = r.w] */
+        KL(cgk_cg2_step(x_loc, p_loc, c->r, c->svec, c->Ap, c->partials_vec, c->sc, o->eps, o->ignore_stop,
+                        o->guard, max_iter, c->m, peers, st));
+        c->launches += 1;
+        return enqueue_product(c, ev_a, ev_b);
+    }
+    int rc = enqueue_product(c, ev_a, ev_b);
+    if (rc != CGB_OK) return rc;
+    if (peers) {
         KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec, &c->sc->rr_local, c->sc, cur,
-                         o->guard, c->m, &c->peers, st));                                  /* :298-313 */
-        KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, &c->peers, st)); /* :314-323 */
-        c->launches += 3;
+                         o->guard, c->m, peers, st));                                      /* :298-313 */
+        KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, peers, st)); /* :314-323 */
+        c->launches += 2;
         return CGB_OK;
     }
-    if (multi)                                                   /* MPI_Allgather(p), :290-291 */
-        NC(ncclAllGather(p_loc, c->p_full, (size_t)c->m, ncclDouble, c->comm, st));
-    if (ev_a) CU(cudaEventRecord(ev_a, st));
-    if (c->use_symv) {                                           /* upper tiles only, two kernels */
-        KL(cgk_symv(c->A, c->p_full, p_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                    c->partials_gemv, &c->sc->pAp, c->sc, c->n, c->symv_ru, c->symv_split, st));
-        c->launches += 1;
-    } else
-    KL(cgk_gemv(&c->plan, c->A, c->p_full, p_loc, c->Ap, c->partials_gemv,
-                multi ? &c->sc->pAp_local : &c->sc->pAp, c->sc, c->m, c->n, st));   /* :292-293 */
-    if (ev_b) CU(cudaEventRecord(ev_b, st));
-    if (multi)                                                   /* MPI_Allreduce(alpha), :294 */
-        NC(ncclAllReduce(&c->sc->pAp_local, &c->sc->pAp, 1, ncclDouble, ncclSum, c->comm, st));
     KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec,
                      multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, o->guard, c->m, NULL, st)); /* :298-309 */
     if (multi)                                                   /* MPI_Allreduce(beta), :313 */
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[cur ^ 1], 1, ncclDouble, ncclSum, c->comm, st));
     KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, NULL, st)); /* :314-323 */
-    c->launches += 3;
+    c->launches += 2;
     return CGB_OK;
 }
 
@@ -596,6 +624,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan; key.guard = o->guard;
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
     key.symv = c->use_symv; key.symv_ru = c->symv_ru; key.symv_split = c->symv_split;
+    key.cg_variant = o->cg_variant;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -653,6 +682,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     CU(cudaSetDevice(c->device));
 
     /* transport of the per-iteration exchange (every rank passes the same option) */
+    if (o.cg_variant != CGB_CG_CLASSIC && o.cg_variant != CGB_CG_FUSED_REDUCTIONS) FAIL(CGB_ERR_ARG, "unknown cg_variant");
     c->comm_mode = 0;
     if (multi) {
         if (o.comm == CGB_COMM_PEER && !c->peer_ok) {
@@ -662,6 +692,8 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         c->comm_mode = (o.comm == CGB_COMM_NCCL || !c->peer_ok) ? CGB_COMM_NCCL : CGB_COMM_PEER;
     }
     const cgk_peers *peers = c->comm_mode == CGB_COMM_PEER ? &c->peers : NULL;
+    if (multi && !peers && o.cg_variant == CGB_CG_FUSED_REDUCTIONS)
+        FAIL(CGB_ERR_STATE, "cg_variant = CGB_CG_FUSED_REDUCTIONS on several ranks needs the peer-memory exchange (CGB_COMM_PEER)");
 
     cgk_gemv_plan req;
     plan_request_from_options(&req, &o);
@@ -712,6 +744,12 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[0], 1, ncclDouble, ncclSum, c->comm, st));
     KL(cgk_after_init(c->sc, o.guard, peers, st));
     c->launches += 4;
+    if (o.cg_variant == CGB_CG_FUSED_REDUCTIONS) {
+        /* w0 = A r0 and delta0 = r0.w0 belong to the set-up; s starts at 0 (beta0 = 0) */
+        CU(cudaMemsetAsync(c->svec, 0, (size_t)c->m * sizeof(double), st));
+        int rc = enqueue_product(c, NULL, NULL);
+        if (rc != CGB_OK) return rc;
+    }
     CU(cudaEventRecord(c->ev[1], st));
 
     /* ---- loop */
@@ -735,11 +773,12 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
             }
             issued += 2;
         }
-        if (o.ignore_stop && issued < max_iter) continue;      /* fixed-iteration mode: no polling */
+        /* fixed-iteration mode: no polling (the fused-reductions step k closes iteration k-1) */
+        if (o.ignore_stop && issued < max_iter + (o.cg_variant == CGB_CG_FUSED_REDUCTIONS ? 1 : 0)) continue;
         CU(cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         if (c->h_sc->stop_req != 0 || c->h_sc->comm_error != 0) break;
-        if (issued > max_iter + 4) FAIL(CGB_ERR_STATE, "solver loop did not terminate");
+        if (issued > max_iter + 2 * (int64_t)(chunk > 2 ? chunk : 2) + 4) FAIL(CGB_ERR_STATE, "solver loop did not terminate");
     }
     CU(cudaEventRecord(c->ev[2], st));
     /* every rank returns the full x, as the reference's replicated x (parallel_cg.c:299-303) */
@@ -782,6 +821,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         if (c->use_symv) { stats->gemv_variant = CGB_GEMV_SYMV; stats->gemv_unroll = c->symv_ru; stats->gemv_grid = (int)c->sy_ntiles; }
         stats->gemv_keep_rows = c->plan.keep_rows;
         stats->exit_reason = c->h_sc->stop_req;
+        stats->cg_variant = o.cg_variant;
         if (gemv_pairs_used > 0) {
             double sum = 0.0, mn = 1e300;
             for (int i = 0; i < gemv_pairs_used; ++i) {

@@ -58,6 +58,15 @@ extern "C" {
 #define CGB_COMM_NCCL 1            /* ncclAllGather + 2 x ncclAllReduce between the kernels   */
 #define CGB_COMM_PEER 2            /* fused: the kernels push over NVLink into peer memory    */
 
+/* Recurrence.  CLASSIC is the reference's (serialConjugate.c:213-245): three
+ * synchronisation points per iteration (p, p.Ap, r.r).  FUSED_REDUCTIONS is Chronopoulos-Gear
+ * CG -- the same iterates in exact arithmetic, computed as w = A r, gamma = r.r, delta = r.w,
+ * beta = gamma/gamma_prev, alpha = gamma/(delta - beta gamma/alpha_prev), p = r + beta p,
+ * s = w + beta s, x += alpha p, r -= alpha s -- with two kernels and ONE exposed reduction per
+ * iteration; same stop rule, same exit state (x, r updated).  One extra matVec per solve. */
+#define CGB_CG_CLASSIC 0
+#define CGB_CG_FUSED_REDUCTIONS 1
+
 typedef struct cgb_ctx cgb_ctx;    /* one per rank (= per GPU); owns all device state */
 
 typedef struct cgb_options {
@@ -89,6 +98,7 @@ typedef struct cgb_options {
                            /*    several ranks (peer exchange only) accept generated systems, or    */
                            /*    2 = the caller asserts symmetry.  n / ranks a multiple of 512.     */
                            /*    0 (default): the reference's full row products                     */
+    int     cg_variant;    /* CGB_CG_*                                                              */
 } cgb_options;
 
 #define CGB_EXIT_STOP_RULE 1       /* sqrt(r.r) < eps                 (parallel_cg.c:314-317)  */
@@ -123,7 +133,7 @@ typedef struct cgb_stats {
     int     graph_chunk;       /* iterations per captured graph (0: stream mode)                   */
     int     comm;              /* CGB_COMM_NCCL / CGB_COMM_PEER as used (0 with one rank)          */
     int     exit_reason;       /* CGB_EXIT_*                                                       */
-    int     reserved[1];
+    int     cg_variant;        /* CGB_CG_* as run                                                  */
     int64_t gemv_keep_rows;    /* rows of A held in L2 across iterations (0: plain streaming)      */
 } cgb_stats;
 

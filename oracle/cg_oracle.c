@@ -241,3 +241,59 @@ double orc_time_matvec_sample(int64_t n, int64_t rows, uint64_t seed, int reps,
     free(A); free(v); free(y);
     return dt;
 }
+
+/* ------------------------------------------------------------------ fused-reductions CG
+ * CPU statement of the Chronopoulos-Gear recurrence the product offers as
+ * cgb_options.cg_variant = CGB_CG_FUSED_REDUCTIONS.  The REFERENCE has no such
+ * variant, so this function is not pinned against reference code: it follows the published
+ * algorithm (Chronopoulos & Gear, "s-step iterative methods for symmetric linear systems",
+ * J. Comput. Appl. Math. 25 (1989), the s = 1 case) with the reference's stop rule and exit
+ * state (serialConjugate.c:234-238: test after the x, r update, p stale on exit).  It is
+ * validated in tests/test_oracle.py against the pinned classic oracle above: the two produce
+ * the same iterates in exact arithmetic and agree to ~1e-15 on the reference's matrix family. */
+void orc_cg_fused_f64(const double *A, const double *b, double *x, int64_t n, double eps,
+                      int64_t max_iter, int ignore_stop, orc_stats *st)
+{
+    double *r = orc_alloc((size_t)n * sizeof(double)), *w = orc_alloc((size_t)n * sizeof(double));
+    double *p = orc_alloc((size_t)n * sizeof(double)), *s = orc_alloc((size_t)n * sizeof(double));
+    const double t0 = orc_now();
+    double gamma = 0.0, delta = 0.0, gamma_prev = 0.0, alpha_prev = 0.0;
+    for (int64_t i = 0; i < n; ++i) {
+        double ax = 0.0;
+        for (int64_t j = 0; j < n; ++j) ax += A[i * n + j] * x[j];
+        r[i] = b[i] - ax;
+        p[i] = 0.0; s[i] = 0.0;
+    }
+    for (int64_t i = 0; i < n; ++i) gamma += r[i] * r[i];
+    st->rsold0 = gamma; st->final_beta = gamma;
+    st->iterations = 0; st->break_k = -1; st->first_hit_k = -1;
+    const double t1 = orc_now();
+    for (int64_t k = 0; k < max_iter; ++k) {
+        delta = 0.0;
+        for (int64_t i = 0; i < n; ++i) {
+            double wi = 0.0;
+            for (int64_t j = 0; j < n; ++j) wi += A[i * n + j] * r[j];
+            w[i] = wi;
+        }
+        for (int64_t i = 0; i < n; ++i) delta += r[i] * w[i];
+        const double beta = (k == 0) ? 0.0 : gamma / gamma_prev;
+        const double alpha = (k == 0) ? gamma / delta : gamma / (delta - beta * gamma / alpha_prev);
+        double gnew = 0.0;
+        for (int64_t i = 0; i < n; ++i) {
+            p[i] = r[i] + p[i] * beta;
+            s[i] = w[i] + s[i] * beta;
+            x[i] = x[i] + p[i] * alpha;
+            r[i] = r[i] - s[i] * alpha;
+            gnew += r[i] * r[i];
+        }
+        gamma_prev = gamma; alpha_prev = alpha; gamma = gnew;
+        st->iterations = k + 1; st->final_beta = gamma;
+        if (sqrt(gamma) < eps) {
+            if (st->first_hit_k < 0) st->first_hit_k = k;
+            if (!ignore_stop) { st->break_k = k; break; }
+        }
+    }
+    const double t2 = orc_now();
+    st->seconds = t2 - t0; st->loop_seconds = t2 - t1;
+    free(r); free(w); free(p); free(s);
+}

@@ -117,6 +117,20 @@ def conjugrad(A, b, x0, eps=1.0e-6, max_iter=None, ignore_stop=False, ranks=None
     return x, st.as_dict()
 
 
+def cg_fused(A, b, x0, eps=1.0e-6, max_iter=None, ignore_stop=False):
+    """Chronopoulos-Gear CG (oracle/cg_oracle.c orc_cg_fused_f64): the CPU statement of the product's
+    cg_variant = CGB_CG_FUSED_REDUCTIONS.  Returns (x, stats)."""
+    A = np.ascontiguousarray(A, dtype=np.float64); b = np.ascontiguousarray(b, dtype=np.float64)
+    x = np.array(x0, dtype=np.float64, copy=True)
+    n = A.shape[0]
+    st = OrcStats()
+    f = lib().orc_cg_fused_f64
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int64, C.c_int, C.POINTER(OrcStats)]
+    f.restype = None
+    f(A.ctypes.data, b.ctypes.data, x.ctypes.data, n, eps, n if max_iter is None else max_iter, int(ignore_stop), C.byref(st))
+    return x, st.as_dict()
+
+
 def team_solve_generated(n, seed, ranks, flags=0, eps=1.0e-6, max_iter=None, ignore_stop=False, want_x=True):
     x = np.empty(n, dtype=np.float64) if want_x else None
     st = OrcStats(); gs = C.c_double(0.0)

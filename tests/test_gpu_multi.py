@@ -139,6 +139,22 @@ def test_symmetric_option_on_ranks_needs_assertion_for_loaded_matrices(cg):
         cg.solve_generated(n, 1, gpus=2, symmetric=1, comm=1)
 
 
+@pytest.mark.parametrize("gpus,n,k,sym", [(2, 2048, 7, 0), (2, 2048, 4, 1), (4, 2048, 7, 0), (4, 4096, 0, 1), (8, 4096, 4, 0), (8, 4096, 4, 1)])
+def test_fused_reductions_variant_sharded(cg, gpus, n, k, sym):
+    # Chronopoulos-Gear recurrence: r is the exchanged vector, one exposed reduction per iteration
+    need(cg, gpus)
+    seed, flags = 90 + gpus, cg.GEN_KAPPA_LOG2(k)
+    x, st = cg.solve_generated(n, seed, gpus=gpus, flags=flags, cg_variant=1, symmetric=sym)
+    A, b = O.gen_A(n, seed, flags), O.gen_b(n, seed, flags)
+    xc, sc = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
+    assert st["cg_variant"] == 1 and st["comm"] == 2
+    assert relerr(x, xc) <= RTOL_X and abs(st["iterations"] - sc["iterations"]) <= 1 and st["final_residual"] < EPS
+    x2, st2 = cg.solve_generated(n, seed, gpus=gpus, flags=flags, cg_variant=1, symmetric=sym)
+    np.testing.assert_array_equal(x, x2)
+    with pytest.raises(cg.CgbError):
+        cg.solve_generated(n, seed, gpus=gpus, cg_variant=1, comm=1)
+
+
 def test_not_divisible(cg):
     need(cg, 2)
     with pytest.raises(cg.CgbError) as e:

@@ -184,6 +184,44 @@ def test_generated_spread_family_solve(cg, ctx, n, k):
     assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
 
 
+# ----------------------------------------------------------------- fused-reductions CG
+@pytest.mark.parametrize("n,k,graph,sym", [(512, 0, 1, 0), (1000, 0, 0, 0), (2048, 7, 1, 0), (1024, 4, 1, 1), (4096, 0, 1, 0)])
+def test_fused_reductions_variant_matches_reference_and_its_own_oracle(cg, ctx, n, k, graph, sym):
+    seed, flags = 70 + n, cg.GEN_KAPPA_LOG2(k)
+    ctx.generate(n, seed, flags)
+    st = ctx.solve(cg_variant=cg.CG_FUSED_REDUCTIONS, use_graph=graph, symmetric=sym)
+    x = ctx.read_x()
+    A, b = O.gen_A(n, seed, flags), O.gen_b(n, seed, flags)
+    xc, sc = O.conjugrad(A, b, np.zeros(n))                  # the reference's recurrence
+    xf, sf = O.cg_fused(A, b, np.zeros(n))                   # the variant's CPU statement
+    assert st["cg_variant"] == 1 and st["exit_reason"] == 1
+    assert relerr(x, xc) <= RTOL_X and relerr(x, xf) <= RTOL_X
+    assert abs(st["iterations"] - sc["iterations"]) <= 1 and abs(st["iterations"] - sf["iterations"]) <= 1
+    assert st["break_k"] == st["iterations"] - 1 and st["final_residual"] < EPS
+    # fixed-iteration and max_iter modes count like the classic path
+    ctx.set_x0(np.zeros(n))
+    st = ctx.solve(cg_variant=1, ignore_stop=1, max_iter=3, use_graph=graph)
+    x3, _ = O.cg_fused(A, b, np.zeros(n), max_iter=3, ignore_stop=True)
+    assert st["iterations"] == 3 and st["break_k"] == -1 and relerr(ctx.read_x(), x3) <= RTOL_X
+    ctx.set_x0(np.zeros(n))
+    st = ctx.solve(cg_variant=1, max_iter=2, eps=1e-300, use_graph=graph)
+    assert st["iterations"] == 2 and st["exit_reason"] == 2
+
+
+def test_fused_reductions_variant_guards_and_shipped_fixture(cg, ctx, golden):
+    c = golden["cases"]["g2"]
+    A, b, x0 = unhex(c["A"]).reshape(4, 4), unhex(c["b"]), unhex(c["x0"])
+    ctx.load_host(A, b, x0)
+    st = ctx.solve(cg_variant=1)
+    np.testing.assert_allclose(ctx.read_x(), [-1, 1, -1, 1], rtol=1e-12)
+    ctx.load_host(np.zeros((4, 4)), np.ones(4), np.zeros(4))
+    st = ctx.solve(cg_variant=1, guard=1)
+    assert st["iterations"] == 0 and st["exit_reason"] == 3
+    ctx.load_host(np.eye(2) * 2, np.array([2.0, 4.0]), np.array([1.0, 2.0]))
+    st = ctx.solve(cg_variant=1, guard=1)
+    assert st["iterations"] == 0 and st["exit_reason"] == 4
+
+
 # ----------------------------------------------------------------- symmetric product
 @pytest.mark.parametrize("n,k,ru", [(512, 0, 0), (1024, 0, 1), (2048, 7, 2), (1536, 4, 4)])
 def test_symmetric_upper_tile_product_solves_like_the_reference(cg, ctx, n, k, ru):
@@ -337,6 +375,36 @@ def test_full_size_gemv_properties(ctx):
     # oracle iterate at the same iteration count on this size takes ~1 s per matVec
     xo, so = O.conjugrad(O.gen_A(n, seed), O.gen_b(n, seed), np.zeros(n))
     assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+
+
+@pytest.mark.parametrize("n", [65536, 131072])
+def test_baseline_sizes_through_size_independent_properties(ctx, n):
+    """BASELINE.json configs[3] and [4] (34 GB / 137 GB): no oracle pass at these sizes (a CPU matVec
+    streams the whole matrix), so: the solve converges in the iteration count the family always needs;
+    b - A x is small on sampled rows recomputed on the CPU from the generator twin; the symmetric
+    product gives the same solution; a fixed-iteration run reproduces itself bit for bit."""
+    info = ctx.device_info()
+    if info["total_bytes"] < 8 * n * n + (4 << 30):
+        pytest.skip("GPU memory too small for this size")
+    seed = 20170209
+    ctx.generate(n, seed)
+    st = ctx.solve()
+    x = ctx.read_x()
+    assert st["final_residual"] < EPS and st["exit_reason"] == 1 and 2 <= st["iterations"] <= 8
+    for i in (0, 1, 4097, n // 2 + 3, n - 1):
+        Ai = O.gen_A(n, seed, 0, i, 1)[0]
+        assert abs(O.gen_b(n, seed, 0, i, 1)[0] - Ai @ x) < 1e-6
+    ctx.set_x0(np.zeros(n))
+    sts = ctx.solve(symmetric=1)
+    assert sts["gemv_variant"] == 3 and abs(sts["iterations"] - st["iterations"]) <= 1
+    assert relerr(ctx.read_x(), x) <= RTOL_X
+    ctx.set_x0(np.zeros(n))
+    ctx.solve(ignore_stop=1, max_iter=3)
+    x3 = ctx.read_x()
+    ctx.set_x0(np.zeros(n))
+    ctx.solve(ignore_stop=1, max_iter=3)
+    np.testing.assert_array_equal(ctx.read_x(), x3)
+    ctx.generate(512, 1)                      # release the big block for the tests that follow
 
 
 def test_cli_on_shipped_fixture(cg, golden_dir):

@@ -145,3 +145,22 @@ def test_generator_spread_family_is_spd_with_prescribed_condition():
         assert st["break_k"] >= 0 and np.linalg.norm(A @ x - O.gen_b(n, seed)) < 1e-5
         iters.append(st["iterations"])
     assert iters[0] > 20 and iters[1] > 2 * iters[0]      # ~sqrt(kappa) growth: iteration-bound workloads
+
+
+def test_fused_reductions_oracle_agrees_with_the_pinned_classic_oracle(golden):
+    # Chronopoulos-Gear CG has no counterpart in the reference: its CPU statement is validated here
+    # against the classic oracle (which IS pinned): same iterates in exact arithmetic
+    for n, seed, flags in ((512, 3, 0), (1024, 9, O.GEN_KAPPA_LOG2(4)), (768, 5, O.GEN_KAPPA_LOG2(7))):
+        A, b = O.gen_A(n, seed, flags), O.gen_b(n, seed, flags)
+        xc, sc = O.conjugrad(A, b, np.zeros(n))
+        xf, sf = O.cg_fused(A, b, np.zeros(n))
+        assert abs(sf["iterations"] - sc["iterations"]) <= 1 and sf["break_k"] >= 0
+        assert np.linalg.norm(xf - xc) / np.linalg.norm(xc) <= 1e-10
+        assert sf["rsold0"] == sc["rsold0"]
+    c = golden["cases"]["g2"]                                # the shipped 4x4 fixture
+    A, b, x0 = unhex(c["A"]).reshape(4, 4), unhex(c["b"]), unhex(c["x0"])
+    xf, sf = O.cg_fused(A, b, x0)
+    np.testing.assert_allclose(xf, [-1, 1, -1, 1], rtol=1e-12)
+    xk, sk = O.cg_fused(A, b, x0, max_iter=2, eps=1e-300)
+    xc, _ = O.conjugrad(A, b, x0, max_iter=2, eps=1e-300)
+    np.testing.assert_allclose(xk, xc, rtol=1e-12)
