@@ -32,6 +32,8 @@
  *                     --round4 so that the files hold exactly the system that is solved
  *   --symmetric       matVec from the upper tiles only (half the bytes); the matrix must be exactly
  *                     symmetric (checked on the GPU; with --gpus > 1 only for --gen systems)
+ *   --cg classic|fused  recurrence: the reference's (default) or Chronopoulos-Gear CG with one
+ *                     exposed reduction per iteration (same iterates in exact arithmetic)
  *   --guard           end the solve on p.Ap = 0 / exact x0 instead of iterating NaNs to the
  *                     loop bound as the reference does (parallel_cg.c:298,318)
  *   --run-record FILE machine-readable record of the run (JSON: iterations, sqrt(r.r), exit
@@ -52,7 +54,7 @@
 
 typedef struct {
     const char *fileA, *fileB, *fileX, *dims, *write_x, *record, *emit;
-    int gpus, print_x, stats, round4, gemv, comm, kappa_log2, guard, symmetric;
+    int gpus, print_x, stats, round4, gemv, comm, kappa_log2, guard, symmetric, cg_variant;
     int64_t gen_n, max_iter, bench_iters;
     uint64_t seed;
     double eps;
@@ -85,6 +87,12 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         else if (!strcmp(a, "--seed")) { c->seed = strtoull(v, NULL, 10); ++i; }
         else if (!strcmp(a, "--bench-iters")) { c->bench_iters = atoll(v); ++i; }
         else if (!strcmp(a, "--gemv")) { c->gemv = atoi(v); ++i; }
+        else if (!strcmp(a, "--cg")) {
+            if (!strcmp(v, "classic")) c->cg_variant = CGB_CG_CLASSIC;
+            else if (!strcmp(v, "fused")) c->cg_variant = CGB_CG_FUSED_REDUCTIONS;
+            else { fprintf(stderr, "--cg takes classic or fused\n"); return -1; }
+            ++i;
+        }
         else if (!strcmp(a, "--kappa-log2")) { c->kappa_log2 = atoi(v); ++i; }
         else if (!strcmp(a, "--comm")) {
             if (!strcmp(v, "nccl")) c->comm = CGB_COMM_NCCL;
@@ -217,6 +225,7 @@ int main(int argc, char **argv)
     opt.comm = cli.comm;
     opt.guard = cli.guard;
     opt.symmetric = cli.symmetric;
+    opt.cg_variant = cli.cg_variant;
     if (cli.bench_iters > 0) { opt.ignore_stop = 1; opt.max_iter = cli.bench_iters; }
 
     cgb_stats st;
