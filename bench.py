@@ -383,6 +383,25 @@ def e2e_leg(ctx, line, env):
                    "h2d_gbs_per_gpu": h2d / max(st.h2d_seconds, 1e-12) / 1e9,
                    "solve_seconds": max_over_ranks(st.solve_seconds), "iterations": int(st.iterations),
                    "api": "cgb_conjugrad_rank (C ABI, pinned host buffers, one upload of A per call)"}
+    if "symmetric_variant" in line:
+        # the same call with the matrix asserted symmetric (symmetric = 2): the tiles the product
+        # never reads stay on the host, so about half the bytes cross PCIe
+        o3 = B.make_options(ignore_stop=1, max_iter=K, symmetric=2, **gopts)
+
+        def sym_call():
+            hx.zero_()
+            barrier()
+            t0 = time.perf_counter()
+            B._check(L.cgb_conjugrad_rank(ctx._h, hA.data_ptr(), hb.data_ptr(), hx.data_ptr(), m, C.byref(o3), C.byref(st)))
+            torch.cuda.synchronize()
+            return max_over_ranks(time.perf_counter() - t0)
+
+        sym_call()
+        dt3 = sym_call()
+        line["symmetric_variant"]["e2e"] = {"value": K / dt3, "unit": UNIT, "h2d_bytes_per_step": float(st.h2d_bytes) / K,
+                                            "d2h_bytes_per_step": 8.0 * n / K, "seconds_per_call": dt3,
+                                            "h2d_seconds": max_over_ranks(st.h2d_seconds),
+                                            "api": "cgb_conjugrad_rank with cgb_options.symmetric = 2"}
     # the converging solve a user of the reference CLI runs: upload + ~5 iterations + download
     o2 = B.make_options(**gopts)
     hx.zero_()

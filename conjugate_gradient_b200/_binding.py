@@ -51,7 +51,7 @@ class Stats(C.Structure):
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
                 ("gemv_tile_cols", C.c_int), ("gemv_grid", C.c_int), ("graph_chunk", C.c_int),
                 ("comm", C.c_int), ("exit_reason", C.c_int), ("cg_variant", C.c_int),
-                ("gemv_keep_rows", C.c_int64)]
+                ("gemv_keep_rows", C.c_int64), ("h2d_bytes", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
@@ -98,6 +98,7 @@ def lib():
         "cgb_create_rank": ([C.POINTER(vp), C.c_int, C.c_int, C.c_int, vp], C.c_int),
         "cgb_destroy": ([vp], C.c_int),
         "cgb_load_host": ([vp, i64, vp, vp, vp], C.c_int),
+        "cgb_load_host_symmetric": ([vp, i64, vp, vp, vp], C.c_int),
         "cgb_load_text": ([vp, i64, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
         "cgb_conjugrad_files": ([C.c_char_p, C.c_char_p, C.c_char_p, i64, C.c_int, op, vp, sp], C.c_int),
         "cgb_generate": ([vp, i64, u64, C.c_uint], C.c_int), "cgb_set_x0": ([vp, vp], C.c_int),
@@ -196,6 +197,17 @@ class Context:
         assert A.size == m * n, "A_rows must be the rank's (n/ranks) x n block"
         b = _f64(b_rows, (m,))
         _check(lib().cgb_load_host(self._h, n, A.ctypes.data, b.ctypes.data, x0.ctypes.data))
+        self.n = n
+
+    def load_host_symmetric(self, A_rows, b_rows, x0_full):
+        """load_host for a matrix asserted symmetric: only the tiles the symmetric product reads travel."""
+        x0 = _f64(x0_full)
+        n = x0.shape[0]
+        m = n // self.ranks
+        A = A_rows if (isinstance(A_rows, np.ndarray) and A_rows.dtype == np.float64 and A_rows.flags.c_contiguous) else _f64(A_rows)
+        assert A.size == m * n, "A_rows must be the rank's (n/ranks) x n block"
+        b = _f64(b_rows, (m,))
+        _check(lib().cgb_load_host_symmetric(self._h, n, A.ctypes.data, b.ctypes.data, x0.ctypes.data))
         self.n = n
 
     def load_host_ptr(self, n, A_ptr, b_ptr, x0_ptr):

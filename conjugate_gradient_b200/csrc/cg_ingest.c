@@ -193,6 +193,8 @@ done:
         c->h2d_seconds = now_s() - t0;
         c->loaded = 1;
         c->sym_state = 0;
+        c->tiles_only = 0;
+        c->h2d_bytes = 0;
     }
 out:
     if (have_text) cgb_text_close(&tx);

@@ -45,6 +45,8 @@ struct cgb_ctx {
     struct cgb_graph_key graph_key;
     int64_t launches;
     double h2d_seconds, d2h_seconds;
+    int64_t h2d_bytes;
+    int64_t graph_launches;           /* kernels per replay of the captured graph */
     /* peer-memory exchange (ranks > 1): this rank's window [cgk_mailbox | p_full], the peers'
      * windows as mapped here (same-process peer access or CUDA IPC), and the table the kernels get */
     void *win;
@@ -58,6 +60,7 @@ struct cgb_ctx {
     char peer_why[160];               /* why peer_ok == 0                                */
     /* symmetric product (cg_symv.cu) */
     int sym_state;                    /* 0 not checked, 1 exactly symmetric, -1 not      */
+    int tiles_only;                   /* cgb_load_host_symmetric: only the tiles the symmetric product reads are on the device */
     int use_symv, symv_ru, symv_split;
     double *sy_rowpart, *sy_colpart;  /* (n / T) * n each                                */
     void *sy_tiles;

@@ -405,8 +405,71 @@ int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_r
     }
     CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = now_s() - t0;
+    c->h2d_bytes = (int64_t)(total + (size_t)(n + m) * sizeof(double));
     c->loaded = 1;
     c->sym_state = 0;
+    c->tiles_only = 0;
+    return CGB_OK;
+}
+
+/* Can this context run the symmetric product on an n x n system (prepare_symv's shape rules)? */
+static int symv_shape_ok(const cgb_ctx *c, int64_t n)
+{
+    const int T = cgk_symv_tile();
+    if (n < 1 || n % c->ranks != 0) return 0;
+    if (n % T != 0 || (n / c->ranks) % T != 0) return 0;
+    return c->ranks == 1 || c->peer_ok;
+}
+
+/* A caller that asserts a_ij == a_ji (cgb_options.symmetric = 2) need not send what the
+ * symmetric product never reads: only the rank's tiles of the tile list travel (for one rank
+ * the 512 x 512 tiles on and above the diagonal, n (n + 512) / 2 values instead of n^2).
+ * Strided copies, one per run of adjacent tiles in a tile row. */
+int cgb_load_host_symmetric(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows,
+                            const double *x0_full)
+{
+    if (!c || !A_rows || !b_rows || !x0_full) FAIL(CGB_ERR_ARG, "cgb_load_host_symmetric: null argument");
+    int rc = cgb_ensure_problem(c, n);
+    if (rc != CGB_OK) return rc;
+    if (!symv_shape_ok(c, n)) {
+        snprintf(tl_err, sizeof tl_err, "cgb_load_host_symmetric needs n / ranks to be a multiple of %d and, on several ranks, "
+                 "the peer-memory exchange (n = %lld, ranks = %d)", cgk_symv_tile(), (long long)n, c->ranks);
+        return CGB_ERR_ARG;
+    }
+    const int64_t m = c->m, T = cgk_symv_tile();
+    const int multi = c->ranks > 1;
+    cgk_symplan sp;
+    if (multi) cgk_symv_make_plan(&sp, c->rank, c->ranks, m);
+    const int64_t cnt = multi ? cgk_symv_tile_list_rank(&sp, c->rank, m, 1, NULL) : cgk_symv_tile_list(n, 1, NULL);
+    int *tl = malloc((size_t)cnt * 2 * sizeof(int));
+    if (!tl) FAIL(CGB_ERR_NOMEM, "out of host memory for the tile list");
+    if (multi) cgk_symv_tile_list_rank(&sp, c->rank, m, 1, tl); else cgk_symv_tile_list(n, 1, tl);
+    double t0 = now_s();
+    cudaError_t ce = cudaMemcpyAsync(c->x_full, x0_full, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(c->b, b_rows, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+    int64_t sent = 0;
+    for (int64_t k = 0; k < cnt && ce == cudaSuccess; ) {
+        const int64_t I = tl[2 * k] & 0xffffff, J0 = tl[2 * k + 1];
+        int64_t q = k + 1;
+        while (q < cnt && (tl[2 * q] & 0xffffff) == I && tl[2 * q + 1] == J0 + (q - k)) ++q;
+        const size_t off = (size_t)(I * T) * (size_t)n + (size_t)(J0 * T);
+        ce = cudaMemcpy2DAsync(c->A + off, (size_t)n * sizeof(double), A_rows + off, (size_t)n * sizeof(double),
+                               (size_t)((q - k) * T) * sizeof(double), (size_t)T, cudaMemcpyHostToDevice, c->stream);
+        sent += (q - k) * T * T;
+        k = q;
+    }
+    free(tl);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);
+    if (ce != cudaSuccess) {
+        (void)cudaGetLastError();
+        snprintf(tl_err, sizeof tl_err, "cgb_load_host_symmetric: %s", cudaGetErrorString(ce));
+        return CGB_ERR_CUDA;
+    }
+    c->h2d_seconds = now_s() - t0;
+    c->h2d_bytes = (sent + n + m) * (int64_t)sizeof(double);
+    c->loaded = 1;
+    c->sym_state = 1;          /* asserted by the caller, as cgb_options.symmetric = 2 */
+    c->tiles_only = 1;
     return CGB_OK;
 }
 
@@ -421,7 +484,9 @@ int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
     CU(cudaMemsetAsync(c->x_full, 0, (size_t)n * sizeof(double), c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = 0.0;
+    c->h2d_bytes = 0;
     c->loaded = 1;
+    c->tiles_only = 0;
     c->sym_state = 1;          /* 0.5 (u_ij + u_ji): IEEE addition commutes, exactly symmetric */
     return CGB_OK;
 }
@@ -633,6 +698,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     for (int k = 0; k < chunk && rc == CGB_OK; ++k)
         rc = enqueue_iteration(c, o, max_iter, k & 1, NULL, NULL);
     cudaError_t e = cudaStreamEndCapture(c->stream, &c->graph);
+    c->graph_launches = c->launches - before;          /* kernels of this library in one replay */
     c->launches = before;
     if (rc != CGB_OK) { if (c->graph) { cudaGraphDestroy(c->graph); c->graph = NULL; } return rc; }
     CU(e);
@@ -704,6 +770,9 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     if ((int64_t)c->plan.grid > cgk_gemv_max_ctas(c->m)) FAIL(CGB_ERR_STATE, "gemv grid exceeds workspace");
     if ((++c->gen & 0x3ffu) == 0u) ++c->gen;              /* tags never collide with zeroed memory */
     c->use_symv = 0;
+    if (c->tiles_only && !o.symmetric)
+        FAIL(CGB_ERR_STATE, "the matrix came through cgb_load_host_symmetric: only the symmetric product's tiles are on the "
+                            "device, solve with cgb_options.symmetric set");
     if (o.symmetric) {
         int rc = prepare_symv(c, &o);
         if (rc != CGB_OK) return rc;
@@ -759,7 +828,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         if (use_graph) {
             CU(cudaGraphLaunch(c->graph_exec, st));
             issued += chunk;
-            c->launches += 3 * (int64_t)chunk;
+            c->launches += c->graph_launches;
         } else {
             /* stream mode: two iterations per poll keeps the rr[] parity aligned */
             for (int k = 0; k < 2; ++k) {
@@ -806,7 +875,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->rsold0 = c->h_sc->rsold0;
         stats->solve_seconds = t1 - t0;
         stats->loop_ms = ms_loop; stats->init_ms = ms_init;
-        stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds;
+        stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds; stats->h2d_bytes = c->h2d_bytes;
         stats->gemv_bytes = 8.0 * ((double)c->m * (double)c->n + (double)c->n + (double)c->m);
         if (c->use_symv)      /* declared change of algorithmic bytes: the rank's half of its row block
                                * (the upper triangle on one rank), p once, Ap once */
@@ -844,12 +913,19 @@ int cgb_conjugrad_rank(cgb_ctx *c, const double *local_A, const double *local_b,
     if (!c || !local_A || !local_b || !local_x || local_row < 1)
         FAIL(CGB_ERR_ARG, "cgb_conjugrad_rank: bad argument");
     const int64_t n = local_row * c->ranks;
-    int rc = cgb_load_host(c, n, local_A, local_b, local_x);
+    int rc = CGB_OK;
+    if (opt && opt->symmetric == 2) {            /* asserted symmetric: the unread half stays on the host */
+        rc = cgb_ensure_problem(c, n);
+        if (rc != CGB_OK) return rc;
+        const int peer = c->ranks == 1 || (opt->comm != CGB_COMM_NCCL && c->peer_ok);
+        rc = (peer && symv_shape_ok(c, n)) ? cgb_load_host_symmetric(c, n, local_A, local_b, local_x)
+                                           : cgb_load_host(c, n, local_A, local_b, local_x);
+    } else rc = cgb_load_host(c, n, local_A, local_b, local_x);
     if (rc != CGB_OK) return rc;
     rc = cgb_solve(c, opt, stats);
     if (rc != CGB_OK) return rc;
     rc = cgb_read_x(c, local_x);
-    if (rc == CGB_OK && stats) { stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds; }
+    if (rc == CGB_OK && stats) { stats->h2d_seconds = c->h2d_seconds; stats->d2h_seconds = c->d2h_seconds; stats->h2d_bytes = c->h2d_bytes; }
     return rc;
 }
 

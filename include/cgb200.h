@@ -96,7 +96,9 @@ typedef struct cgb_options {
                            /*    8f-4).  Needs a_ij == a_ji bit for bit -- verified on the device   */
                            /*    once per loaded matrix on one rank (CGB_ERR_ARG otherwise);        */
                            /*    several ranks (peer exchange only) accept generated systems, or    */
-                           /*    2 = the caller asserts symmetry.  n / ranks a multiple of 512.     */
+                           /*    2 = the caller asserts symmetry (cgb_conjugrad* then upload only   */
+                           /*    the tiles the product reads, see cgb_load_host_symmetric).          */
+                           /*    n / ranks a multiple of 512.                                        */
                            /*    0 (default): the reference's full row products                     */
     int     cg_variant;    /* CGB_CG_*                                                              */
 } cgb_options;
@@ -135,6 +137,7 @@ typedef struct cgb_stats {
     int     exit_reason;       /* CGB_EXIT_*                                                       */
     int     cg_variant;        /* CGB_CG_* as run                                                  */
     int64_t gemv_keep_rows;    /* rows of A held in L2 across iterations (0: plain streaming)      */
+    int64_t h2d_bytes;         /* bytes the last cgb_load_host / cgb_load_host_symmetric copied    */
 } cgb_stats;
 
 /* ---- library / device ------------------------------------------------------ */
@@ -161,6 +164,15 @@ int cgb_destroy(cgb_ctx *ctx);
  * caller-owned, copied to the GPU (pinned buffers copy at PCIe rate). */
 int cgb_load_host(cgb_ctx *ctx, int64_t n, const double *A_rows, const double *b_rows,
                   const double *x0_full);
+/* cgb_load_host for a matrix the caller asserts to be symmetric (a_ij == a_ji bit for bit, as
+ * cgb_options.symmetric = 2): only the 512 x 512 tiles the symmetric product reads are copied
+ * -- on one rank those on and above the tile diagonal, n (n + 512) / 2 values; entries below
+ * are never referenced (BLAS dsymv's uplo = 'U', at tile granularity).  Same buffers and
+ * layout as cgb_load_host (the full row block; the unread part is simply skipped).  The
+ * problem must then be solved with cgb_options.symmetric set (CGB_ERR_STATE otherwise).
+ * CGB_ERR_ARG unless n / ranks is a multiple of 512 (several ranks: peer-memory exchange). */
+int cgb_load_host_symmetric(cgb_ctx *ctx, int64_t n, const double *A_rows, const double *b_rows,
+                            const double *x0_full);
 /* The same three inputs as the reference's TEXT files (initialize(), parallel_cg.c:147-168,
  * "%f%*c" token rules): the rank locates the bytes of its own m rows in matrixA.txt, streams
  * them through pinned memory and the GPU tokenises and converts them (bit-identical to

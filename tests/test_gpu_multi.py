@@ -139,6 +139,34 @@ def test_symmetric_option_on_ranks_needs_assertion_for_loaded_matrices(cg):
         cg.solve_generated(n, 1, gpus=2, symmetric=1, comm=1)
 
 
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_asserted_symmetric_upload_on_ranks_reads_only_each_ranks_tiles(cg, gpus):
+    # symmetric = 2 through the reference-facing call: a rank uploads the tiles of its tile list only;
+    # everything no rank reads is poisoned with NaN in the host matrix and must not matter
+    need(cg, gpus)
+    from test_symplan import plan_and_tiles, T
+    mt = 2
+    n = gpus * mt * T
+    A, b = O.spd_with_condition(n, 30.0, seed=20 + gpus)
+    xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
+    read = np.zeros((n // T, n // T), dtype=bool)
+    per_rank = 0
+    for r in range(gpus):
+        tiles = plan_and_tiles(r, gpus, mt)[1]
+        per_rank = max(per_rank, len(tiles))
+        for il, j in tiles:
+            read[r * mt + il, j] = True
+    P = A.copy()
+    for I in range(n // T):
+        for J in range(n // T):
+            if not read[I, J]:
+                P[I * T:(I + 1) * T, J * T:(J + 1) * T] = np.nan
+    assert read.sum() == (n // T) * (n // T + 1) // 2
+    x, st = cg.conjugrad_host(P, b, np.zeros(n), gpus=gpus, symmetric=2)
+    assert st["gemv_variant"] == 3 and relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    assert st["h2d_bytes"] <= 8 * (per_rank * T * T + n + n // gpus)
+
+
 @pytest.mark.parametrize("gpus,n,k,sym", [(2, 2048, 7, 0), (2, 2048, 4, 1), (4, 2048, 7, 0), (4, 4096, 0, 1), (8, 4096, 4, 0), (8, 4096, 4, 1)])
 def test_fused_reductions_variant_sharded(cg, gpus, n, k, sym):
     # Chronopoulos-Gear recurrence: r is the exchanged vector, one exposed reduction per iteration

@@ -273,6 +273,39 @@ def test_symmetric_option_checks_its_preconditions(cg, ctx):
     assert e.value.code == -1 and "multiple of 512" in str(e.value)
 
 
+def test_asserted_symmetric_upload_sends_only_the_tiles_the_product_reads(cg, ctx):
+    # cgb_options.symmetric = 2 through the reference-facing call: tiles below the tile diagonal
+    # never leave the host (poisoned here with NaN to prove it), h2d bytes = n (n + 512) / 2 + 2n
+    n, T = 2048, 512
+    A, b = O.spd_with_condition(n, 30.0, seed=5)
+    xo, so = O.conjugrad(A, b, np.zeros(n))
+    P = A.copy()
+    for I in range(n // T):
+        P[I * T:(I + 1) * T, :I * T] = np.nan
+    x = np.zeros(n)
+    st = ctx.conjugrad_rank(P, b, x, symmetric=2)
+    assert st["gemv_variant"] == 3 and relerr(x, xo) <= RTOL_X
+    assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
+    assert st["h2d_bytes"] == 8 * (n * (n + T) // 2 + 2 * n)
+    with pytest.raises(cg.CgbError) as e:                    # the full product has nothing to read
+        ctx.solve()
+    assert e.value.code == -6 and "cgb_load_host_symmetric" in str(e.value)
+    ctx.set_x0(np.zeros(n))
+    assert ctx.solve(symmetric=1, cg_variant=cg.CG_FUSED_REDUCTIONS)["gemv_variant"] == 3
+    assert relerr(ctx.read_x(), xo) <= RTOL_X
+    # shapes the symmetric product does not take fall back to the full upload and the full product
+    n2 = 700
+    A2, b2 = O.spd_with_condition(n2, 10.0, seed=6)
+    x2 = np.zeros(n2)
+    with pytest.raises(cg.CgbError):
+        ctx.conjugrad_rank(A2, b2, x2, symmetric=2)
+    with pytest.raises(cg.CgbError) as e:
+        ctx.load_host_symmetric(A2, b2, x2)
+    assert e.value.code == -1 and "multiple of 512" in str(e.value)
+    ctx.load_host(A, b, np.zeros(n))                         # a full load clears the restriction
+    assert st["h2d_bytes"] < ctx.solve()["h2d_bytes"] == 8 * (n * n + 2 * n)
+
+
 def test_nonzero_initial_guess_and_restart(ctx):
     n, seed = 768, 9
     A, b = O.gen_A(n, seed), O.gen_b(n, seed)
