@@ -99,6 +99,8 @@ def lib():
         "cgb_destroy": ([vp], C.c_int),
         "cgb_load_host": ([vp, i64, vp, vp, vp], C.c_int),
         "cgb_load_host_symmetric": ([vp, i64, vp, vp, vp], C.c_int),
+        "cgb_debug_check_guards": ([vp], C.c_int),
+        "cgb_debug_poke": ([vp, C.c_int, i64, C.c_double], C.c_int),
         "cgb_load_text": ([vp, i64, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
         "cgb_conjugrad_files": ([C.c_char_p, C.c_char_p, C.c_char_p, i64, C.c_int, op, vp, sp], C.c_int),
         "cgb_generate": ([vp, i64, u64, C.c_uint], C.c_int), "cgb_set_x0": ([vp, vp], C.c_int),
@@ -299,6 +301,13 @@ class Context:
         avg, mn = C.c_double(), C.c_double()
         _check(lib().cgb_time_gemv(self._h, C.byref(o), warmup, reps, int(flush_l2), C.byref(avg), C.byref(mn)))
         return avg.value, mn.value
+
+    def check_guards(self):
+        """CGB_DEBUG_GUARDS=1: raise CgbError if a kernel wrote outside one of the context's device arrays."""
+        _check(lib().cgb_debug_check_guards(self._h))
+
+    def debug_poke(self, what, offset, value):
+        _check(lib().cgb_debug_poke(self._h, what, offset, value))
 
     def debug_read(self, what, offset, count):
         out = np.empty(count, dtype=np.float64)

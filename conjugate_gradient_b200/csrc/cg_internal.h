@@ -17,6 +17,10 @@ struct cgb_graph_key {
     int symv, symv_ru, symv_split, cg_variant;
 };
 
+#define CGB_MAX_GUARDS 24
+#define CGB_GUARD_BYTES 256
+#define CGB_GUARD_BYTE 0xA5
+
 struct cgb_ctx {
     int device, rank, ranks, sm_count, has_comm, loaded;
     int64_t l2_bytes;
@@ -66,6 +70,10 @@ struct cgb_ctx {
     void *sy_tiles;
     int64_t sy_ntiles;
     cgk_symplan sy_plan;              /* ranks > 1: which half of the row block this rank reads */
+    /* guard bands (CGB_DEBUG_GUARDS=1 at cgb_create): 256 B of a fixed byte before and after every
+     * solver array, verified by cgb_debug_check_guards -- the out-of-bounds-write check of the tests */
+    int guards_on, n_guards;
+    struct { void *user; size_t bytes; const char *name; } guards[CGB_MAX_GUARDS];
 };
 
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);

@@ -84,9 +84,80 @@ void cgb_default_options(cgb_options *o)
     o->use_graph = 1;
 }
 
+/* ------------------------------------------------------------------ guarded device arrays
+ * With CGB_DEBUG_GUARDS=1 every solver array sits between two 256-byte bands of a fixed byte,
+ * which cgb_debug_check_guards() reads back: a kernel writing one element outside its array is
+ * caught by the tests (compute-sanitizer's job where it is available).  Off by default: plain
+ * cudaMalloc / cudaFree. */
+static cudaError_t galloc(cgb_ctx *c, void **out, size_t bytes, const char *name)
+{
+    *out = NULL;
+    if (!c->guards_on) return cudaMalloc(out, bytes);
+    if (c->n_guards >= CGB_MAX_GUARDS) return cudaErrorMemoryAllocation;
+    char *base = NULL;
+    cudaError_t e = cudaMalloc((void **)&base, bytes + 2 * CGB_GUARD_BYTES);
+    if (e != cudaSuccess) return e;
+    e = cudaMemset(base, CGB_GUARD_BYTE, CGB_GUARD_BYTES);
+    if (e == cudaSuccess) e = cudaMemset(base + CGB_GUARD_BYTES + bytes, CGB_GUARD_BYTE, CGB_GUARD_BYTES);
+    if (e != cudaSuccess) { cudaFree(base); return e; }
+    c->guards[c->n_guards].user = base + CGB_GUARD_BYTES;
+    c->guards[c->n_guards].bytes = bytes;
+    c->guards[c->n_guards].name = name;
+    c->n_guards++;
+    *out = base + CGB_GUARD_BYTES;
+    return cudaSuccess;
+}
+
+static void gfree(cgb_ctx *c, void *user)
+{
+    if (!user) return;
+    for (int i = 0; i < c->n_guards; ++i)
+        if (c->guards[i].user == user) {
+            cudaFree((char *)user - CGB_GUARD_BYTES);
+            c->guards[i] = c->guards[--c->n_guards];
+            return;
+        }
+    cudaFree(user);
+}
+
+int cgb_debug_check_guards(cgb_ctx *c)
+{
+    if (!c) FAIL(CGB_ERR_ARG, "cgb_debug_check_guards: null context");
+    if (!c->guards_on) FAIL(CGB_ERR_STATE, "guard bands are off: create the context with CGB_DEBUG_GUARDS=1 in the environment");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    unsigned char h[2][CGB_GUARD_BYTES];
+    for (int i = 0; i < c->n_guards; ++i) {
+        char *u = c->guards[i].user;
+        CU(cudaMemcpy(h[0], u - CGB_GUARD_BYTES, CGB_GUARD_BYTES, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(h[1], u + c->guards[i].bytes, CGB_GUARD_BYTES, cudaMemcpyDeviceToHost));
+        for (int side = 0; side < 2; ++side)
+            for (int k = 0; k < CGB_GUARD_BYTES; ++k)
+                if (h[side][k] != CGB_GUARD_BYTE) {
+                    snprintf(tl_err, sizeof tl_err, "guard band %s array `%s` (%zu bytes) was overwritten at byte %d",
+                             side ? "after" : "before", c->guards[i].name, c->guards[i].bytes, side ? k : k - CGB_GUARD_BYTES);
+                    return CGB_ERR_STATE;
+                }
+    }
+    if (c->win) {                                     /* the slack after [mailbox | p_full | crecv] */
+        const size_t used = CGK_WINDOW_HEADER_BYTES + 2 * (size_t)c->cap_n * sizeof(double);
+        CU(cudaMemcpy(h[0], (char *)c->win + used, CGB_GUARD_BYTES, cudaMemcpyDeviceToHost));
+        for (int k = 0; k < CGB_GUARD_BYTES; ++k)
+            if (h[0][k] != CGB_GUARD_BYTE) {
+                snprintf(tl_err, sizeof tl_err, "guard band after the peer window was overwritten at byte %d", k);
+                return CGB_ERR_STATE;
+            }
+    }
+    return CGB_OK;
+}
+
 /* ------------------------------------------------------------------ contexts */
 static int ctx_init_common(cgb_ctx *c, int device)
 {
+    {
+        const char *e = getenv("CGB_DEBUG_GUARDS");
+        c->guards_on = e && *e && *e != '0';
+    }
     struct cudaDeviceProp prop;
     CU(cudaSetDevice(device));
     CU(cudaGetDeviceProperties(&prop, device));
@@ -111,10 +182,10 @@ static int ctx_init_common(cgb_ctx *c, int device)
     CU(cudaEventCreate(&c->ev[0]));
     CU(cudaEventCreate(&c->ev[1]));
     CU(cudaEventCreate(&c->ev[2]));
-    CU(cudaMalloc((void **)&c->sc, sizeof(cgk_scalars)));
+    CU(galloc(c, (void **)&c->sc, sizeof(cgk_scalars), "scalars"));
     CU(cudaMemset(c->sc, 0, sizeof(cgk_scalars)));
     CU(cudaHostAlloc((void **)&c->h_sc, sizeof(cgk_scalars), cudaHostAllocDefault));
-    CU(cudaMalloc((void **)&c->partials_vec, (size_t)cgk_vec_max_ctas(1) * sizeof(double)));
+    CU(galloc(c, (void **)&c->partials_vec, (size_t)cgk_vec_max_ctas(1) * sizeof(double), "partials_vec"));
     return CGB_OK;
 }
 
@@ -188,11 +259,11 @@ static void free_problem(cgb_ctx *c)
 {
     drop_graph(c);
     close_peers(c);
-    cudaFree(c->A); cudaFree(c->b); cudaFree(c->r); cudaFree(c->Ap); cudaFree(c->svec);
+    gfree(c, c->A); gfree(c, c->b); gfree(c, c->r); gfree(c, c->Ap); gfree(c, c->svec);
     c->svec = NULL;
-    if (c->win) cudaFree(c->win); else cudaFree(c->p_full);
-    cudaFree(c->x_full); cudaFree(c->partials_gemv);
-    cudaFree(c->sy_rowpart); cudaFree(c->sy_colpart); cudaFree(c->sy_tiles);
+    if (c->win) cudaFree(c->win); else gfree(c, c->p_full);
+    gfree(c, c->x_full); gfree(c, c->partials_gemv);
+    gfree(c, c->sy_rowpart); gfree(c, c->sy_colpart); gfree(c, c->sy_tiles);
     c->sy_rowpart = c->sy_colpart = NULL; c->sy_tiles = NULL; c->sy_ntiles = 0; c->sym_state = 0;
     c->A = c->b = c->r = c->Ap = c->p_full = c->x_full = c->partials_gemv = NULL;
     c->win = NULL; c->win_bytes = 0;
@@ -317,7 +388,7 @@ int cgb_destroy(cgb_ctx *c)
     for (int i = 0; i < 3; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < c->n_gemv_ev; ++i) cudaEventDestroy(c->gemv_ev[i]);
     free(c->gemv_ev);
-    cudaFree(c->sc); cudaFree(c->partials_vec); cudaFree(c->flush_buf);
+    gfree(c, c->sc); gfree(c, c->partials_vec); cudaFree(c->flush_buf);
     if (c->h_sc) cudaFreeHost(c->h_sc);
     if (c->stream) cudaStreamDestroy(c->stream);
     (void)cudaGetLastError();
@@ -354,33 +425,35 @@ int cgb_ensure_problem(cgb_ctx *c, int64_t n)
     if (n != c->cap_n || m != c->cap_m) {
         free_problem(c);
         const size_t abytes = (size_t)m * (size_t)n * sizeof(double);
-        cudaError_t e = cudaMalloc((void **)&c->A, abytes);
+        cudaError_t e = galloc(c, (void **)&c->A, abytes, "A");
         if (e != cudaSuccess) {
             (void)cudaGetLastError();
             snprintf(tl_err, sizeof tl_err, "can't allocate memory for matrix block: %zu bytes on GPU %d (%s)",
                      abytes, c->device, cudaGetErrorString(e));
             return CGB_ERR_NOMEM;
         }
-        CU(cudaMalloc((void **)&c->b, (size_t)m * sizeof(double)));
-        CU(cudaMalloc((void **)&c->r, (size_t)m * sizeof(double)));
-        CU(cudaMalloc((void **)&c->Ap, (size_t)m * sizeof(double)));
-        CU(cudaMalloc((void **)&c->svec, (size_t)m * sizeof(double)));
+        CU(galloc(c, (void **)&c->b, (size_t)m * sizeof(double), "b"));
+        CU(galloc(c, (void **)&c->r, (size_t)m * sizeof(double), "r"));
+        CU(galloc(c, (void **)&c->Ap, (size_t)m * sizeof(double), "Ap"));
+        CU(galloc(c, (void **)&c->svec, (size_t)m * sizeof(double), "s"));
         if (c->ranks > 1) {
             /* [mailbox | p_full] in one allocation of whole 2 MiB pages: one IPC handle */
             const size_t gran = (size_t)2 << 20;
             /* [mailbox | p_full (n) | column-sum receive area (ranks x m = n)] */
-            c->win_bytes = (CGK_WINDOW_HEADER_BYTES + 2 * (size_t)n * sizeof(double) + gran - 1) / gran * gran;
+            const size_t used = CGK_WINDOW_HEADER_BYTES + 2 * (size_t)n * sizeof(double);
+            c->win_bytes = (used + CGB_GUARD_BYTES + gran - 1) / gran * gran;
             CU(cudaMalloc(&c->win, c->win_bytes));
             CU(cudaMemsetAsync(c->win, 0, c->win_bytes, c->stream));
+            CU(cudaMemsetAsync((char *)c->win + used, CGB_GUARD_BYTE, CGB_GUARD_BYTES, c->stream));
             CU(cudaStreamSynchronize(c->stream));
             c->p_full = (double *)((char *)c->win + CGK_WINDOW_HEADER_BYTES);
             int rc = exchange_windows(c, n);
             if (rc != CGB_OK) return rc;
         } else {
-            CU(cudaMalloc((void **)&c->p_full, (size_t)n * sizeof(double)));
+            CU(galloc(c, (void **)&c->p_full, (size_t)n * sizeof(double), "p"));
         }
-        CU(cudaMalloc((void **)&c->x_full, (size_t)n * sizeof(double)));
-        CU(cudaMalloc((void **)&c->partials_gemv, (size_t)cgk_gemv_max_ctas(m) * sizeof(double)));
+        CU(galloc(c, (void **)&c->x_full, (size_t)n * sizeof(double), "x"));
+        CU(galloc(c, (void **)&c->partials_gemv, (size_t)cgk_gemv_max_ctas(m) * sizeof(double), "partials_gemv"));
         c->cap_n = n; c->cap_m = m;
     }
     c->n = n; c->m = m;
@@ -534,6 +607,28 @@ int cgb_debug_read(cgb_ctx *c, int what, int64_t offset, int64_t count, double *
     return CGB_OK;
 }
 
+/* Guard-band self test: one double stored at element `offset` of an array, where offset may lie up
+ * to 32 elements outside it.  Refused unless the context was created with CGB_DEBUG_GUARDS=1. */
+int cgb_debug_poke(cgb_ctx *c, int what, int64_t offset, double value)
+{
+    if (!c) FAIL(CGB_ERR_ARG, "cgb_debug_poke: null context");
+    if (!c->guards_on) FAIL(CGB_ERR_STATE, "cgb_debug_poke: only with CGB_DEBUG_GUARDS=1");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_debug_poke: no problem loaded");
+    double *dst = NULL; int64_t lim = 0;
+    switch (what) {
+    case 1: dst = c->b; lim = c->m; break;
+    case 2: dst = c->x_full; lim = c->n; break;
+    case 3: dst = c->r; lim = c->m; break;
+    case 5: dst = c->Ap; lim = c->m; break;
+    default: FAIL(CGB_ERR_ARG, "cgb_debug_poke: unknown array");
+    }
+    if (offset < -32 || offset >= lim + 32) FAIL(CGB_ERR_ARG, "cgb_debug_poke: offset beyond the guard band");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(dst + offset, &value, sizeof value, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return CGB_OK;
+}
+
 /* ------------------------------------------------------------------ solver */
 static void plan_request_from_options(cgk_gemv_plan *p, const cgb_options *o)
 {
@@ -587,14 +682,14 @@ static int prepare_symv(cgb_ctx *c, const cgb_options *o)
         int *h = malloc((size_t)cnt * 2 * sizeof(int));
         if (!h) FAIL(CGB_ERR_NOMEM, "out of host memory for the tile list");
         if (multi) cgk_symv_tile_list_rank(&c->sy_plan, c->rank, c->m, split, h); else cgk_symv_tile_list(c->n, split, h);
-        cudaError_t ce = cudaMalloc(&c->sy_tiles, (size_t)cnt * 2 * sizeof(int));
+        cudaError_t ce = galloc(c, &c->sy_tiles, (size_t)cnt * 2 * sizeof(int), "symv tile list");
         if (ce == cudaSuccess) ce = cudaMemcpy(c->sy_tiles, h, (size_t)cnt * 2 * sizeof(int), cudaMemcpyHostToDevice);
         free(h);
-        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_rowpart, (size_t)(c->n / T) * (size_t)c->m * sizeof(double));
-        if (ce == cudaSuccess) ce = cudaMalloc((void **)&c->sy_colpart, (size_t)split * (size_t)ntl * (size_t)c->n * sizeof(double));
+        if (ce == cudaSuccess) ce = galloc(c, (void **)&c->sy_rowpart, (size_t)(c->n / T) * (size_t)c->m * sizeof(double), "symv row partials");
+        if (ce == cudaSuccess) ce = galloc(c, (void **)&c->sy_colpart, (size_t)split * (size_t)ntl * (size_t)c->n * sizeof(double), "symv column partials");
         if (ce != cudaSuccess) {
             (void)cudaGetLastError();
-            cudaFree(c->sy_tiles); cudaFree(c->sy_rowpart); cudaFree(c->sy_colpart);
+            gfree(c, c->sy_tiles); gfree(c, c->sy_rowpart); gfree(c, c->sy_colpart);
             c->sy_tiles = NULL; c->sy_rowpart = c->sy_colpart = NULL;
             FAIL(CGB_ERR_NOMEM, "can't allocate memory for the symmetric-product workspaces");
         }
@@ -903,6 +998,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
             stats->gemv_timed = gemv_pairs_used;
         }
     }
+    if (c->guards_on) return cgb_debug_check_guards(c);      /* CGB_DEBUG_GUARDS=1: every solve is checked */
     return CGB_OK;
 }
 
@@ -982,9 +1078,9 @@ int cgb_time_gemv(cgb_ctx *c, const cgb_options *opt, int warmup, int reps, int 
 }
 
 /* ------------------------------------------------------------------ single-kernel operators */
-static int dev_dup(double **d, const double *h, int64_t count, cudaStream_t st)
+static int dev_dup(cgb_ctx *c, double **d, const double *h, int64_t count, cudaStream_t st)
 {
-    CU(cudaMalloc((void **)d, (size_t)(count > 0 ? count : 1) * sizeof(double)));
+    CU(galloc(c, (void **)d, (size_t)(count > 0 ? count : 1) * sizeof(double), "operator scratch"));
     if (h) CU(cudaMemcpyAsync(*d, h, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, st));
     return CGB_OK;
 }
@@ -999,10 +1095,10 @@ int cgb_op_matvec(cgb_ctx *c, const double *A, const double *v, const double *w,
     cudaStream_t st = c->stream;
     double *dA = NULL, *dv = NULL, *dw = NULL, *dy = NULL, *dpart = NULL;
     int rc;
-    if ((rc = dev_dup(&dA, A, m * n, st)) || (rc = dev_dup(&dv, v, n, st)) ||
-        (rc = dev_dup(&dy, NULL, m, st)) || (rc = dev_dup(&dpart, NULL, cgk_gemv_max_ctas(m), st)))
+    if ((rc = dev_dup(c, &dA, A, m * n, st)) || (rc = dev_dup(c, &dv, v, n, st)) ||
+        (rc = dev_dup(c, &dy, NULL, m, st)) || (rc = dev_dup(c, &dpart, NULL, cgk_gemv_max_ctas(m), st)))
         goto out;
-    if (w && (rc = dev_dup(&dw, w, m, st))) goto out;
+    if (w && (rc = dev_dup(c, &dw, w, m, st))) goto out;
     cgk_gemv_plan plan;
     plan_request_from_options(&plan, &o);
     rc = CGB_ERR_CUDA;
@@ -1022,7 +1118,8 @@ int cgb_op_matvec(cgb_ctx *c, const double *A, const double *v, const double *w,
     c->plan = plan;
     rc = CGB_OK;
 out:
-    cudaFree(dA); cudaFree(dv); cudaFree(dw); cudaFree(dy); cudaFree(dpart);
+    if (rc == CGB_OK && c->guards_on) rc = cgb_debug_check_guards(c);
+    gfree(c, dA); gfree(c, dv); gfree(c, dw); gfree(c, dy); gfree(c, dpart);
     return rc;
 }
 
@@ -1034,8 +1131,8 @@ int cgb_op_init_residual(cgb_ctx *c, const double *b, const double *Ax, double *
     cudaStream_t st = c->stream;
     double *db = NULL, *dAx = NULL, *dr = NULL, *dp = NULL;
     int rc;
-    if ((rc = dev_dup(&db, b, m, st)) || (rc = dev_dup(&dAx, Ax, m, st)) ||
-        (rc = dev_dup(&dr, NULL, m, st)) || (rc = dev_dup(&dp, NULL, m, st)))
+    if ((rc = dev_dup(c, &db, b, m, st)) || (rc = dev_dup(c, &dAx, Ax, m, st)) ||
+        (rc = dev_dup(c, &dr, NULL, m, st)) || (rc = dev_dup(c, &dp, NULL, m, st)))
         goto out;
     rc = CGB_ERR_CUDA;
     if (cgk_reset(c->sc, c->gen, st) != 0) goto out;
@@ -1048,7 +1145,8 @@ int cgb_op_init_residual(cgb_ctx *c, const double *b, const double *Ax, double *
     rc = CGB_OK;
 out:
     if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in init_residual op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
-    cudaFree(db); cudaFree(dAx); cudaFree(dr); cudaFree(dp);
+    if (rc == CGB_OK && c->guards_on) rc = cgb_debug_check_guards(c);
+    gfree(c, db); gfree(c, dAx); gfree(c, dr); gfree(c, dp);
     return rc;
 }
 
@@ -1060,8 +1158,8 @@ int cgb_op_xr_update(cgb_ctx *c, double rho, double pAp, double *x, double *r, c
     cudaStream_t st = c->stream;
     double *dx = NULL, *dr = NULL, *dp = NULL, *dAp = NULL;
     int rc;
-    if ((rc = dev_dup(&dx, x, m, st)) || (rc = dev_dup(&dr, r, m, st)) ||
-        (rc = dev_dup(&dp, p, m, st)) || (rc = dev_dup(&dAp, Ap, m, st)))
+    if ((rc = dev_dup(c, &dx, x, m, st)) || (rc = dev_dup(c, &dr, r, m, st)) ||
+        (rc = dev_dup(c, &dp, p, m, st)) || (rc = dev_dup(c, &dAp, Ap, m, st)))
         goto out;
     rc = CGB_ERR_CUDA;
     if (cgk_reset(c->sc, c->gen, st) != 0) goto out;
@@ -1077,7 +1175,8 @@ int cgb_op_xr_update(cgb_ctx *c, double rho, double pAp, double *x, double *r, c
     rc = CGB_OK;
 out:
     if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in xr_update op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
-    cudaFree(dx); cudaFree(dr); cudaFree(dp); cudaFree(dAp);
+    if (rc == CGB_OK && c->guards_on) rc = cgb_debug_check_guards(c);
+    gfree(c, dx); gfree(c, dr); gfree(c, dp); gfree(c, dAp);
     return rc;
 }
 
@@ -1089,7 +1188,7 @@ int cgb_op_p_update(cgb_ctx *c, double rho, double beta, double eps, double *p, 
     cudaStream_t st = c->stream;
     double *dp = NULL, *dr = NULL;
     int rc;
-    if ((rc = dev_dup(&dp, p, m, st)) || (rc = dev_dup(&dr, r, m, st))) goto out;
+    if ((rc = dev_dup(c, &dp, p, m, st)) || (rc = dev_dup(c, &dr, r, m, st))) goto out;
     rc = CGB_ERR_CUDA;
     memset(c->h_sc, 0, sizeof *c->h_sc);
     c->h_sc->rr[0] = rho; c->h_sc->rr[1] = beta; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
@@ -1102,7 +1201,8 @@ int cgb_op_p_update(cgb_ctx *c, double rho, double beta, double eps, double *p, 
     rc = CGB_OK;
 out:
     if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in p_update op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
-    cudaFree(dp); cudaFree(dr);
+    if (rc == CGB_OK && c->guards_on) rc = cgb_debug_check_guards(c);
+    gfree(c, dp); gfree(c, dr);
     return rc;
 }
 
@@ -1115,13 +1215,13 @@ int cgb_op_generate(cgb_ctx *c, int64_t n, int64_t row0, int64_t m, uint64_t see
     double *dA = NULL, *db = NULL;
     int rc = CGB_OK;
     if (A_rows) {
-        if ((rc = dev_dup(&dA, NULL, m * n, st))) goto out;
+        if ((rc = dev_dup(c, &dA, NULL, m * n, st))) goto out;
         rc = CGB_ERR_CUDA;
         if (cgk_generate_A(dA, n, row0, m, seed, flags, st) != 0) goto out;
         if (cudaMemcpyAsync(A_rows, dA, (size_t)m * (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     }
     if (b_rows) {
-        if ((rc = dev_dup(&db, NULL, m, st))) goto out;
+        if ((rc = dev_dup(c, &db, NULL, m, st))) goto out;
         rc = CGB_ERR_CUDA;
         if (cgk_generate_b(db, n, row0, m, seed, flags, st) != 0) goto out;
         if (cudaMemcpyAsync(b_rows, db, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
@@ -1129,6 +1229,7 @@ int cgb_op_generate(cgb_ctx *c, int64_t n, int64_t row0, int64_t m, uint64_t see
     rc = cudaStreamSynchronize(st) == cudaSuccess ? CGB_OK : CGB_ERR_CUDA;
 out:
     if (rc == CGB_ERR_CUDA) cgb_set_error("%s%s (cg_solver.c:%d)", "CUDA error in generate op: ", cudaGetErrorString(cudaGetLastError()), __LINE__);
-    cudaFree(dA); cudaFree(db);
+    if (rc == CGB_OK && c->guards_on) rc = cgb_debug_check_guards(c);
+    gfree(c, dA); gfree(c, db);
     return rc;
 }

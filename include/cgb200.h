@@ -140,6 +140,16 @@ typedef struct cgb_stats {
     int64_t h2d_bytes;         /* bytes the last cgb_load_host / cgb_load_host_symmetric copied    */
 } cgb_stats;
 
+/* ---- debugging -------------------------------------------------------------- */
+/* With CGB_DEBUG_GUARDS=1 in the environment at cgb_create*(), every device array of the
+ * context lies between two 256-byte guard bands; this reads them back after the stream has
+ * drained.  CGB_OK: untouched.  CGB_ERR_STATE: a kernel wrote outside an array (the message
+ * names it), or the bands are off. */
+int cgb_debug_check_guards(cgb_ctx *ctx);
+/* Self test of the above (refused without CGB_DEBUG_GUARDS=1): stores one double at element
+ * `offset` of array `what` (1 b, 2 x, 3 r, 5 Ap), -32 <= offset < length + 32. */
+int cgb_debug_poke(cgb_ctx *ctx, int what, int64_t offset, double value);
+
 /* ---- library / device ------------------------------------------------------ */
 int         cgb_version(void);
 int         cgb_device_count(void);               /* < 0: CUDA unusable                */
