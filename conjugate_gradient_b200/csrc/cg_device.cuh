@@ -90,6 +90,12 @@ __device__ __forceinline__ void cta_partials_finish(double mine, double *partial
     __shared__ int s_last;
     __shared__ double s_red[NT / 32];
     const int tid = threadIdx.x;
+    if (out == nullptr) {
+        /* deferred: the consumer kernel adds the partials itself (cta_sum_partials), which
+         * takes the store -> fence -> ticket -> reload chain off the end of this kernel */
+        if (tid == 0) partials[blockIdx.x] = mine;
+        return;
+    }
     if (tid == 0) {
         partials[blockIdx.x] = mine;
         __threadfence();
@@ -113,6 +119,32 @@ __device__ __forceinline__ void cta_partials_finish(double mine, double *partial
     }
 }
 
+
+/* The consumer side of a deferred reduction: the whole CTA adds partials[0..count) of the
+ * PREVIOUS kernel with a fixed thread -> index mapping and a fixed tree and every thread gets
+ * the total.  Every CTA (of any kernel with the same NT) computes the same bits, so all take
+ * the same branches on it. */
+template <int NT>
+__device__ __forceinline__ double cta_sum_partials(const double *partials, int count)
+{
+    __shared__ double s_cp[NT / 32];
+    __shared__ double s_total;
+    const int tid = threadIdx.x;
+    double s = 0.0;
+#pragma unroll 4
+    for (int i = tid; i < count; i += NT) s += __ldcg(partials + i);
+    s = warp_sum(s);
+    if ((tid & 31) == 0) s_cp[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < NT / 32; ++q) t += s_cp[q];
+        s_total = t;
+    }
+    __syncthreads();
+    return s_total;
+}
 
 /* ------------------------------------------------------------------ peer exchange */
 __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long *p)

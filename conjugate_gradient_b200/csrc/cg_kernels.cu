@@ -558,8 +558,16 @@ __global__ void __launch_bounds__(VEC_NT)
 xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
                  const double *p_loc, const double *__restrict__ Ap,
                  double *__restrict__ partials, double *__restrict__ rr_out,
-                 cgk_scalars *sc, int cur, int guard, long long m, const cgk_peers peers)
+                 cgk_scalars *sc, int cur, int guard, long long m, const cgk_peers peers,
+                 const double *__restrict__ dot_partials, int n_dot)
 {
+    /* the first trip's operands are requested before anything is waited for: the scalars (or the
+     * peers' partials) and the vectors then cost one memory round trip, not two */
+    long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
+    const bool first = i < m;
+    double x0 = 0.0, p0 = 0.0, r0 = 0.0, a0 = 0.0;
+    if (first) { x0 = x[i]; p0 = p_loc[i]; r0 = r[i]; a0 = Ap[i]; }
+    const double rho = sc->rr[cur];
     if (*(volatile int *)&sc->stop_req) return;
     unsigned int ep = 0u, gen = 0u;
     double pAp;
@@ -567,10 +575,14 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
         ep = *(volatile unsigned int *)&sc->ep_xr;
         gen = *(volatile unsigned int *)&sc->gen;
         pAp = ll_gather_sum(&peers.mbox[peers.rank]->dot[0][ep & 1u][0][0], peers.ranks, cgk_tag(gen, ep), sc);
+    } else if (n_dot > 0) {
+        /* deferred p.Ap: the GEMV left one partial per CTA (fixed order, same bits in every CTA) */
+        pAp = cta_sum_partials<VEC_NT>(dot_partials, n_dot);
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc->pAp = pAp;
     } else {
         pAp = sc->pAp;
     }
-    const double alpha = sc->rr[cur] / pAp;
+    const double alpha = rho / pAp;
     if (guard && !isfinite(alpha)) {
         /* every thread of every rank sees the same alpha: all leave x, r alone.  Later kernels
          * read the flags (p_update of this iteration: breakdown; the next GEMV: stop_req). */
@@ -578,8 +590,14 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
         return;
     }
     double s = 0.0;
-    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
-         i += (long long)gridDim.x * VEC_NT) {
+    if (first) {
+        x[i] = __dadd_rn(x0, __dmul_rn(p0, alpha));
+        const double ri = __dsub_rn(r0, __dmul_rn(a0, alpha));
+        r[i] = ri;
+        s = fma(ri, ri, s);
+        i += (long long)gridDim.x * VEC_NT;
+    }
+    for (; i < m; i += (long long)gridDim.x * VEC_NT) {
         x[i] = __dadd_rn(x[i], __dmul_rn(p_loc[i], alpha));
         const double ri = __dsub_rn(r[i], __dmul_rn(Ap[i], alpha));
         r[i] = ri;
@@ -612,17 +630,24 @@ template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
 p_update_kernel(double *p_loc, const double *__restrict__ r,
                 cgk_scalars *sc, int cur, double eps, int ignore_stop,
-                long long max_iter, long long m, const cgk_peers peers)
+                long long max_iter, long long m, const cgk_peers peers,
+                const double *__restrict__ rr_partials, int n_rr)
 {
+    long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
+    const bool first = i < m;
+    double r0 = 0.0, p0 = 0.0;
+    if (first) { r0 = r[i]; p0 = p_loc[i]; }                   /* requested before the scalars are waited for */
+    const double rho = sc->rr[cur];
     if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
     unsigned int ep = 0u, gen = 0u;
-    const double rho = sc->rr[cur];
     double beta;
     if constexpr (COMM) {
         ep = *(volatile unsigned int *)&sc->ep_p;
         gen = *(volatile unsigned int *)&sc->gen;
         const unsigned int e = ep + 1u;
         beta = ll_gather_sum(&peers.mbox[peers.rank]->dot[1][e & 1u][0][0], peers.ranks, cgk_tag(gen, e), sc);
+    } else if (n_rr > 0) {
+        beta = cta_sum_partials<VEC_NT>(rr_partials, n_rr);   /* deferred r.r of xr_update */
     } else {
         beta = sc->rr[cur ^ 1];
     }
@@ -632,7 +657,7 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
         const long long k = sc->iters;
         sc->iters = k + 1;
         sc->final_beta = beta;
-        if constexpr (COMM) sc->rr[cur ^ 1] = beta;       /* read as rho by the NEXT iteration only */
+        if (COMM || n_rr > 0) sc->rr[cur ^ 1] = beta;     /* read as rho by the NEXT iteration only */
         if (hit && sc->first_hit < 0) sc->first_hit = k;
         if (brk) { sc->break_k = k; sc->stop_req = 1; }
         else if (k + 1 >= max_iter) sc->stop_req = 2;
@@ -640,9 +665,8 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
     if (brk) return;
     const double coef = beta / rho;
     const long long lo = COMM ? (long long)peers.rank * m : 0;
-    for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
-         i += (long long)gridDim.x * VEC_NT) {
-        const double pi = __dadd_rn(r[i], __dmul_rn(p_loc[i], coef));
+    for (bool head = first; i < m; i += (long long)gridDim.x * VEC_NT, head = false) {
+        const double pi = head ? __dadd_rn(r0, __dmul_rn(p0, coef)) : __dadd_rn(r[i], __dmul_rn(p_loc[i], coef));
         p_loc[i] = pi;
         if constexpr (COMM) {
             for (int g = 0; g < peers.ranks; ++g)
@@ -1109,27 +1133,32 @@ extern "C" int cgk_init_residual(const double *b, const double *Ax, double *r, d
 
 extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
                              double *partials, double *rr_out, cgk_scalars *sc, int cur, int guard,
-                             int64_t m, const cgk_peers *peers, void *stream)
+                             int64_t m, const cgk_peers *peers, const double *dot_partials, int n_dot,
+                             void *stream)
 {
     if (peers)
         xr_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                                sc, cur, guard, (long long)m, *peers);
+                                                                                sc, cur, guard, (long long)m, *peers, nullptr, 0);
     else
         xr_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                                 sc, cur, guard, (long long)m, k_no_peers);
+                                                                                 sc, cur, guard, (long long)m, k_no_peers,
+                                                                                 dot_partials, n_dot);
     return (int)cudaGetLastError();
 }
 
+extern "C" int cgk_vec_grid(int64_t m) { return vec_grid(m); }
+
 extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
                             int ignore_stop, int64_t max_iter, int64_t m, const cgk_peers *peers,
-                            void *stream)
+                            const double *rr_partials, int n_rr, void *stream)
 {
     if (peers)
         p_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
-                                                                               (long long)max_iter, (long long)m, *peers);
+                                                                               (long long)max_iter, (long long)m, *peers, nullptr, 0);
     else
         p_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
-                                                                                (long long)max_iter, (long long)m, k_no_peers);
+                                                                                (long long)max_iter, (long long)m, k_no_peers,
+                                                                                rr_partials, n_rr);
     return (int)cudaGetLastError();
 }
 

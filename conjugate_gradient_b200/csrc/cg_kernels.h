@@ -144,14 +144,22 @@ int cgk_init_residual(const double *b, const double *Ax, double *r, double *p_lo
 /* alpha = rr[cur]/pAp; x += alpha p; r -= alpha Ap; r.r partials -> *rr_out.
  * guard != 0 (not in the reference, which iterates NaNs to the loop bound):
  * a non-finite alpha leaves x and r untouched and ends the solve (stop_req = breakdown = 3). */
+/* Deferred reductions (one rank; takes the store -> fence -> ticket -> reload chain off the end
+ * of every producer, worth ~4 us per iteration where an iteration is ~20 us): a producer
+ * called with a NULL result pointer (cgk_gemv: dot_out, cgk_xr_update: rr_out) leaves its
+ * per-CTA partials only, and the consumer adds them itself in a fixed order --
+ * cgk_xr_update takes the n_dot GEMV partials (n_dot = the GEMV's grid; 0: read sc->pAp),
+ * cgk_p_update the n_rr = cgk_vec_grid(m) partials of cgk_xr_update (0: read sc->rr). */
 int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
                   double *partials, double *rr_out, cgk_scalars *sc, int cur, int guard,
-                  int64_t m, const cgk_peers *peers, void *stream);
+                  int64_t m, const cgk_peers *peers, const double *dot_partials, int n_dot,
+                  void *stream);
+int cgk_vec_grid(int64_t m);      /* CTAs (= partials) of the vector kernels for m elements */
 
 /* beta = rr[cur^1]: bookkeeping + stop rule on thread 0; p = r + (beta/rho) p. */
 int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, double eps,
                  int ignore_stop, int64_t max_iter, int64_t m, const cgk_peers *peers,
-                 void *stream);
+                 const double *rr_partials, int n_rr, void *stream);
 
 /* One iteration of the Chronopoulos-Gear form of CG (the two per-iteration
  * reductions of parallel_cg.c:294,313 merged into one exposed synchronisation).  With gamma =
@@ -186,6 +194,7 @@ int cgk_l2_flush(void *buf, int64_t bytes, void *stream);
 int     cgk_symv_tile(void);
 int64_t cgk_symv_tile_list(int64_t n, int split, int *tiles_xy);   /* split: CTAs (row parts) per tile: 1, 2, 4 */
 int     cgk_symv_pick_split(int64_t tiles, int sm_count);
+int     cgk_symv_finish_grid(int64_t n);   /* CTAs (= dot partials) of the finishing kernel */
 int cgk_symv(const double *A, const double *v, const double *w, double *y, const void *tiles,
              int64_t ntiles, double *rowpart, double *colpart, double *partials, double *dot_out,
              cgk_scalars *sc, int64_t n, int rows_in_flight, int split, void *stream);

@@ -729,11 +729,11 @@ static int enqueue_product(cgb_ctx *c, cudaEvent_t ev_a, cudaEvent_t ev_b)
     if (ev_a) CU(cudaEventRecord(ev_a, st));
     if (c->use_symv) {                                           /* upper tiles only, two kernels */
         KL(cgk_symv(c->A, c->p_full, v_loc, c->Ap, c->sy_tiles, c->sy_ntiles, c->sy_rowpart, c->sy_colpart,
-                    c->partials_gemv, &c->sc->pAp, c->sc, c->n, c->symv_ru, c->symv_split, st));
+                    c->partials_gemv, c->n_dot ? NULL : &c->sc->pAp, c->sc, c->n, c->symv_ru, c->symv_split, st));
         c->launches += 1;
     } else
     KL(cgk_gemv(&c->plan, c->A, c->p_full, v_loc, c->Ap, c->partials_gemv,
-                multi ? &c->sc->pAp_local : &c->sc->pAp, c->sc, c->m, c->n, st));   /* :292-293 */
+                multi ? &c->sc->pAp_local : (c->n_dot ? NULL : &c->sc->pAp), c->sc, c->m, c->n, st));   /* :292-293 */
     if (ev_b) CU(cudaEventRecord(ev_b, st));
     if (multi)                                                   /* MPI_Allreduce(alpha), :294 */
         NC(ncclAllReduce(&c->sc->pAp_local, &c->sc->pAp, 1, ncclDouble, ncclSum, c->comm, st));
@@ -762,16 +762,18 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     if (rc != CGB_OK) return rc;
     if (peers) {
         KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec, &c->sc->rr_local, c->sc, cur,
-                         o->guard, c->m, peers, st));                                      /* :298-313 */
-        KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, peers, st)); /* :314-323 */
+                         o->guard, c->m, peers, NULL, 0, st));                             /* :298-313 */
+        KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, peers, NULL, 0, st)); /* :314-323 */
         c->launches += 2;
         return CGB_OK;
     }
     KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec,
-                     multi ? &c->sc->rr_local : &c->sc->rr[cur ^ 1], c->sc, cur, o->guard, c->m, NULL, st)); /* :298-309 */
+                     multi ? &c->sc->rr_local : (c->defer_rr ? NULL : &c->sc->rr[cur ^ 1]), c->sc, cur, o->guard, c->m, NULL,
+                     c->partials_gemv, c->n_dot, st));                                     /* :298-309 */
     if (multi)                                                   /* MPI_Allreduce(beta), :313 */
         NC(ncclAllReduce(&c->sc->rr_local, &c->sc->rr[cur ^ 1], 1, ncclDouble, ncclSum, c->comm, st));
-    KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, NULL, st)); /* :314-323 */
+    KL(cgk_p_update(p_loc, c->r, c->sc, cur, o->eps, o->ignore_stop, max_iter, c->m, NULL,
+                    c->defer_rr ? c->partials_vec : NULL, c->defer_rr ? cgk_vec_grid(c->m) : 0, st)); /* :314-323 */
     c->launches += 2;
     return CGB_OK;
 }
@@ -784,7 +786,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan; key.guard = o->guard;
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
     key.symv = c->use_symv; key.symv_ru = c->symv_ru; key.symv_split = c->symv_split;
-    key.cg_variant = o->cg_variant;
+    key.cg_variant = o->cg_variant; key.n_dot = c->n_dot; key.defer_rr = c->defer_rr;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -871,6 +873,18 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     if (o.symmetric) {
         int rc = prepare_symv(c, &o);
         if (rc != CGB_OK) return rc;
+    }
+
+    /* one rank, classic recurrence: the two dot products are finished by their consumers
+     * (cg_kernels.h, "Deferred reductions"); CGB_DEFER=0 keeps the producers' last-CTA sums */
+    c->n_dot = 0; c->defer_rr = 0;
+    {
+        const char *e = getenv("CGB_DEFER");
+        if (!multi && o.cg_variant == CGB_CG_CLASSIC && !(e && *e == '0')) {
+            c->defer_rr = 1;
+            if (c->use_symv) c->n_dot = cgk_symv_finish_grid(c->n);
+            else if (c->plan.variant == CGK_GEMV_LDG && c->plan.grid <= 4096) c->n_dot = c->plan.grid;
+        }
     }
 
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
@@ -1166,7 +1180,7 @@ int cgb_op_xr_update(cgb_ctx *c, double rho, double pAp, double *x, double *r, c
     memset(c->h_sc, 0, sizeof *c->h_sc);
     c->h_sc->rr[0] = rho; c->h_sc->pAp = pAp; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
     if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
-    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, 0, m, NULL, st) != 0) goto out;
+    if (cgk_xr_update(dx, dr, dp, dAp, c->partials_vec, &c->sc->rr[1], c->sc, 0, 0, m, NULL, NULL, 0, st) != 0) goto out;
     if (cudaMemcpyAsync(x, dx, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(r, dr, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
@@ -1193,7 +1207,7 @@ int cgb_op_p_update(cgb_ctx *c, double rho, double beta, double eps, double *p, 
     memset(c->h_sc, 0, sizeof *c->h_sc);
     c->h_sc->rr[0] = rho; c->h_sc->rr[1] = beta; c->h_sc->first_hit = -1; c->h_sc->break_k = -1;
     if (cudaMemcpyAsync(c->sc, c->h_sc, sizeof(cgk_scalars), cudaMemcpyHostToDevice, st) != cudaSuccess) goto out;
-    if (cgk_p_update(dp, dr, c->sc, 0, eps, 0, (int64_t)1 << 40, m, NULL, st) != 0) goto out;
+    if (cgk_p_update(dp, dr, c->sc, 0, eps, 0, (int64_t)1 << 40, m, NULL, NULL, 0, st) != 0) goto out;
     if (cudaMemcpyAsync(p, dp, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaMemcpyAsync(c->h_sc, c->sc, sizeof(cgk_scalars), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     if (cudaStreamSynchronize(st) != cudaSuccess) goto out;
