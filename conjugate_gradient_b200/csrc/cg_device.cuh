@@ -146,6 +146,34 @@ __device__ __forceinline__ double cta_sum_partials(const double *partials, int c
     return s_total;
 }
 
+/* Two such sums in one pass (one pair of barriers). */
+template <int NT>
+__device__ __forceinline__ void cta_sum_partials2(const double *pa, int na, const double *pb, int nb,
+                                                  double *sum_a, double *sum_b)
+{
+    __shared__ double s_cp2[2][NT / 32];
+    __shared__ double s_tot2[2];
+    const int tid = threadIdx.x;
+    double a = 0.0, b = 0.0;
+#pragma unroll 4
+    for (int i = tid; i < na; i += NT) a += __ldcg(pa + i);
+#pragma unroll 4
+    for (int i = tid; i < nb; i += NT) b += __ldcg(pb + i);
+    a = warp_sum(a);
+    b = warp_sum(b);
+    if ((tid & 31) == 0) { s_cp2[0][tid >> 5] = a; s_cp2[1][tid >> 5] = b; }
+    __syncthreads();
+    if (tid < 2) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < NT / 32; ++q) t += s_cp2[tid][q];
+        s_tot2[tid] = t;
+    }
+    __syncthreads();
+    *sum_a = s_tot2[0];
+    *sum_b = s_tot2[1];
+}
+
 /* ------------------------------------------------------------------ peer exchange */
 __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long *p)
 {

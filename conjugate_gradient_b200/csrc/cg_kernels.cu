@@ -765,6 +765,69 @@ cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec
     }
 }
 
+/* cg2_step on one rank, deferred reductions: no ticket, no last-CTA phase.  gamma and delta are
+ * added up by every CTA from the partials the previous step / the product left; the step's
+ * own state moves between the two parity slots of cgk_scalars. */
+__global__ void __launch_bounds__(VEC_NT)
+cg2_step_one_kernel(double *__restrict__ x, double *__restrict__ r_loc, double *__restrict__ pvec,
+                    double *__restrict__ svec, const double *__restrict__ w, double *partials,
+                    cgk_scalars *sc, int cur, double eps, int ignore_stop, int guard, long long max_iter,
+                    long long m, const double *__restrict__ dot_partials, int n_dot)
+{
+    long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
+    const bool first = i < m;
+    double r0 = 0.0, p0 = 0.0, w0 = 0.0, s0 = 0.0, x0 = 0.0;
+    if (first) { r0 = r_loc[i]; p0 = pvec[i]; w0 = w[i]; s0 = svec[i]; x0 = x[i]; }
+    const unsigned int k = sc->cg2_k[cur];
+    const double gprev = sc->cg2_gprev[cur], aprev = sc->cg2_aprev[cur];
+    if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
+    double gamma, delta;
+    cta_sum_partials2<VEC_NT>(partials + (size_t)cur * CGK_MAX_VEC_CTAS, k == 0u ? 0 : (int)gridDim.x,
+                              dot_partials, n_dot, &gamma, &delta);
+    if (k == 0u) gamma = sc->rr[0];
+    if (n_dot == 0) delta = sc->pAp;
+    const bool hit = (k > 0u) && sqrt(gamma) < eps;               /* the reference tests after an update only */
+    const bool brk = hit && !ignore_stop;
+    const bool spent = (long long)k >= max_iter;
+    const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+    if (lead) {
+        if (k > 0u) {
+            sc->iters = (long long)k;
+            sc->final_beta = gamma;
+            if (hit && sc->first_hit < 0) sc->first_hit = (long long)k - 1;
+        }
+        if (brk) { sc->break_k = (long long)k - 1; sc->stop_req = 1; }
+        else if (spent) sc->stop_req = 2;
+    }
+    if (brk || spent) return;
+    const double beta = (k == 0u) ? 0.0 : gamma / gprev;
+    const double alpha = (k == 0u) ? gamma / delta : gamma / (delta - beta * gamma / aprev);
+    if (guard && !isfinite(alpha)) {
+        if (lead) { sc->breakdown = 3; sc->stop_req = 3; }
+        return;
+    }
+    if (lead) {
+        sc->cg2_k[cur ^ 1] = k + 1u;
+        sc->cg2_gprev[cur ^ 1] = gamma;
+        sc->cg2_aprev[cur ^ 1] = alpha;
+        if (n_dot > 0) sc->pAp = delta;
+    }
+    double acc = 0.0;
+    for (bool head = first; i < m; i += (long long)gridDim.x * VEC_NT, head = false) {
+        const double ri = head ? r0 : r_loc[i];
+        const double pi = __dadd_rn(ri, __dmul_rn(head ? p0 : pvec[i], beta));
+        const double si = __dadd_rn(head ? w0 : w[i], __dmul_rn(head ? s0 : svec[i], beta));
+        pvec[i] = pi;
+        svec[i] = si;
+        x[i] = __dadd_rn(head ? x0 : x[i], __dmul_rn(pi, alpha));
+        const double rn = __dsub_rn(ri, __dmul_rn(si, alpha));
+        r_loc[i] = rn;
+        acc = fma(rn, rn, acc);
+    }
+    const double mine = vec_cta_sum(acc);
+    if (threadIdx.x == 0) partials[(size_t)(cur ^ 1) * CGK_MAX_VEC_CTAS + blockIdx.x] = mine;
+}
+
 __global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
 {
     sc->rr[0] = sc->rr[1] = 0.0;
@@ -777,6 +840,9 @@ __global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
     sc->comm_error = 0;
     sc->breakdown = 0;
     sc->cg2_gamma_prev = 0.0; sc->cg2_alpha_prev = 0.0;
+    sc->cg2_k[0] = sc->cg2_k[1] = 0u;
+    sc->cg2_gprev[0] = sc->cg2_gprev[1] = 0.0;
+    sc->cg2_aprev[0] = sc->cg2_aprev[1] = 0.0;
 }
 
 template <bool COMM>
@@ -1172,6 +1238,16 @@ extern "C" int cgk_cg2_step(double *x, double *r_loc, double *pvec, double *svec
     else
         cg2_step_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
                                                                                 ignore_stop, guard, (long long)max_iter, (long long)m, k_no_peers);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_cg2_step_one(double *x, double *r_loc, double *pvec, double *svec, const double *w, double *partials,
+                                cgk_scalars *sc, int cur, double eps, int ignore_stop, int guard, int64_t max_iter,
+                                int64_t m, const double *dot_partials, int n_dot, void *stream)
+{
+    cg2_step_one_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, cur, eps,
+                                                                          ignore_stop, guard, (long long)max_iter,
+                                                                          (long long)m, dot_partials, n_dot);
     return (int)cudaGetLastError();
 }
 

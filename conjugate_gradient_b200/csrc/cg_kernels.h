@@ -43,6 +43,10 @@ typedef struct cgk_scalars {
     double cg2_alpha_prev;
     int breakdown;         /* guard mode only: 3 = alpha not finite (p.Ap = 0), 4 = r0.r0 = 0;   */
                            /* written by cgk_xr_update / cgk_after_init, read by LATER kernels  */
+    /* CGB_CG_FUSED_REDUCTIONS on one rank (deferred reductions, no last-CTA phase): the step of
+     * parity c reads slot [c] and CTA 0 writes slot [c ^ 1], so no launch reads what it writes */
+    unsigned int cg2_k[2];
+    double cg2_gprev[2], cg2_aprev[2];
 } cgk_scalars;
 
 /* ---- peer-memory exchange over NVLink (replaces MPI_Allgather(p) parallel_cg.c:290-291 and the
@@ -172,6 +176,13 @@ int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int cur, doubl
 int cgk_cg2_step(double *x, double *r_loc, double *pvec, double *svec, const double *w, double *partials,
                  cgk_scalars *sc, double eps, int ignore_stop, int guard, int64_t max_iter, int64_t m,
                  const cgk_peers *peers, void *stream);
+/* The same step on one rank with deferred reductions: `cur` = parity of the launch; gamma is
+ * the sum of the previous step's partials (partials[cur][...], this launch writes
+ * partials[cur ^ 1][...]: `partials` holds 2 x cgk_vec_max_ctas doubles), delta the sum of the
+ * product's n_dot partials (0: read sc->pAp). */
+int cgk_cg2_step_one(double *x, double *r_loc, double *pvec, double *svec, const double *w, double *partials,
+                     cgk_scalars *sc, int cur, double eps, int ignore_stop, int guard, int64_t max_iter,
+                     int64_t m, const double *dot_partials, int n_dot, void *stream);
 
 /* Resets the scalars for a new solve (first kernel of the init phase). */
 int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream);

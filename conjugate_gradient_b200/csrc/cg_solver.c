@@ -185,7 +185,7 @@ static int ctx_init_common(cgb_ctx *c, int device)
     CU(galloc(c, (void **)&c->sc, sizeof(cgk_scalars), "scalars"));
     CU(cudaMemset(c->sc, 0, sizeof(cgk_scalars)));
     CU(cudaHostAlloc((void **)&c->h_sc, sizeof(cgk_scalars), cudaHostAllocDefault));
-    CU(galloc(c, (void **)&c->partials_vec, (size_t)cgk_vec_max_ctas(1) * sizeof(double), "partials_vec"));
+    CU(galloc(c, (void **)&c->partials_vec, 2 * (size_t)cgk_vec_max_ctas(1) * sizeof(double), "partials_vec"));
     return CGB_OK;
 }
 
@@ -753,6 +753,10 @@ static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter,
     const cgk_peers *peers = c->comm_mode == CGB_COMM_PEER ? &c->peers : NULL;
     if (o->cg_variant == CGB_CG_FUSED_REDUCTIONS) {
         /* [step k: bookkeeping of k-1, updates of k, new r pushed] [w = A r, delta = r.w] */
+        if (c->defer_rr)      /* one rank: no ticket phase, parity-slot state (cgk_cg2_step_one) */
+            KL(cgk_cg2_step_one(x_loc, p_loc, c->r, c->svec, c->Ap, c->partials_vec, c->sc, cur, o->eps, o->ignore_stop,
+                                o->guard, max_iter, c->m, c->partials_gemv, c->n_dot, st));
+        else
         KL(cgk_cg2_step(x_loc, p_loc, c->r, c->svec, c->Ap, c->partials_vec, c->sc, o->eps, o->ignore_stop,
                         o->guard, max_iter, c->m, peers, st));
         c->launches += 1;
@@ -880,7 +884,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     c->n_dot = 0; c->defer_rr = 0;
     {
         const char *e = getenv("CGB_DEFER");
-        if (!multi && o.cg_variant == CGB_CG_CLASSIC && !(e && *e == '0')) {
+        if (!multi && !(e && *e == '0')) {
             c->defer_rr = 1;
             if (c->use_symv) c->n_dot = cgk_symv_finish_grid(c->n);
             else if (c->plan.variant == CGK_GEMV_LDG && c->plan.grid <= 4096) c->n_dot = c->plan.grid;
