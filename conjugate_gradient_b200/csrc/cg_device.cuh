@@ -72,6 +72,30 @@ template <> struct Ld<4> {      /* 256-bit LDG: new on sm_100 */
     }
 };
 
+/* Programmatic dependent launch (one rank; cgk_set_pdl): a kernel launched with the attribute
+ * may start while its predecessor in the stream is still running.  Rule kept by every kernel
+ * of the iteration: before pdl_wait() only data that the IMMEDIATE predecessor does not write
+ * (the matrix, vectors last written two kernels back); pdl_wait() returns once the
+ * predecessor has completed and flushed; pdl_launch_dependents() comes AFTER the wait, so the
+ * successor cannot start before this kernel's own predecessor is complete (completion is then
+ * transitive along the chain).  Without the launch attribute both are no-ops. */
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+extern "C" int cgk_pdl_enabled(void);
+template <typename... P, typename... Args>
+static inline void cgk_launch(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = cgk_pdl_enabled() ? 1 : 0;
+    (void)cudaLaunchKernelEx(&cfg, kern, P(args)...);
+}
+
 __device__ __forceinline__ double warp_sum(double v)
 {
 #pragma unroll

@@ -15,7 +15,7 @@ struct cgb_graph_key {
     const void *win;        /* peer window the captured kernels point into */
     int comm, guard;
     int symv, symv_ru, symv_split, cg_variant;
-    int n_dot, defer_rr;
+    int n_dot, defer_rr, pdl;
 };
 
 #define CGB_MAX_GUARDS 24
@@ -53,6 +53,7 @@ struct cgb_ctx {
     int64_t h2d_bytes;
     int64_t graph_launches;           /* kernels per replay of the captured graph */
     int n_dot, defer_rr;              /* deferred reductions of the current solve (cg_kernels.h) */
+    int pdl;                          /* iteration kernels launched with programmatic dependent launch */
     /* peer-memory exchange (ranks > 1): this rank's window [cgk_mailbox | p_full], the peers'
      * windows as mapped here (same-process peer access or CUDA IPC), and the table the kernels get */
     void *win;

@@ -15,6 +15,12 @@
 #include "cg_kernels.h"
 #include "spd_gen.cuh"
 
+/* Launch mode of the calling thread: 1 = kernels of the iteration carry the programmatic-
+ * dependent-launch attribute (cg_device.cuh).  Set by the solver around one rank's iterations. */
+static thread_local int tl_pdl = 0;
+extern "C" void cgk_set_pdl(int on) { tl_pdl = on ? 1 : 0; }
+extern "C" int cgk_pdl_enabled(void) { return tl_pdl; }
+
 #define CGK_MAX_VEC_CTAS 592          /* 148 SMs x 4 */
 
 #include "cg_device.cuh"
@@ -136,19 +142,21 @@ gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
  * before its reuse, so the plain kernel pays full HBM traffic every iteration.  Here the
  * first keep_rows rows are loaded evict_last and stay resident from one iteration to the
  * next; the remaining rows stream past them evict_first.  Same arithmetic, same order. */
+/* 7 CTAs of 128 threads per SM (<= 72 registers) where the tile is small: at n = 4096 the grid
+ * of 1024 CTAs then fits the 148 SMs in ONE wave (6 per SM would leave a second wave of 136) */
 template <int R, int U, int NT, int VW>
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, (NT == 128 && R * U * VW <= 16) ? 7 : 0)
 gemv_ldg_keep_kernel(const double *__restrict__ A, const double *__restrict__ v,
                      const double *__restrict__ w, double *__restrict__ y,
                      double *__restrict__ partials, double *__restrict__ dot_out,
                      cgk_scalars *__restrict__ sc, long long m, long long n, long long keep_rows)
 {
-    const int stop = *(volatile int *)&sc->stop_req;
-    if (stop) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
-        return;
-    }
+    /* This is also the GEMV of the programmatic-dependent-launch chain (cg_device.cuh): the
+     * first tile of A (never written during a solve) is requested BEFORE the wait, so the
+     * kernel's launch and its first memory round trip overlap the tail of the vector kernel;
+     * v and w are read after the wait with ordinary (not .nc) loads. */
     constexpr int NW = NT / 32;
+    constexpr long long STEP = (long long)NT * VW, TILE = STEP * U;
     __shared__ double s_row[R][NW];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const long long row0 = (long long)blockIdx.x * R;
@@ -160,12 +168,45 @@ gemv_ldg_keep_kernel(const double *__restrict__ A, const double *__restrict__ v,
         if (row > m - 1) row = m - 1;
         a[r] = A + row * n;
     }
+    const bool held = row0 + R <= keep_rows;
+    const bool pre = n >= TILE;                       /* a full first tile exists */
+    double av0[R][U][VW];
+    if (pre) {
+        const long long c0 = (long long)tid * VW;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (held) Ld<VW>::hold(a[r] + c0 + u * STEP, av0[r][u]);
+                else Ld<VW>::stream(a[r] + c0 + u * STEP, av0[r][u]);
+            }
+    }
+    pdl_wait();
+    pdl_launch_dependents();
+    const int stop = *(volatile int *)&sc->stop_req;
+    if (stop) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
+        return;
+    }
     double acc[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) acc[r] = 0.0;
+    if (pre) {                                        /* the loop's first trip, same order of adds */
+        const long long c0 = (long long)tid * VW;
+        double pv[U][VW];
+#pragma unroll
+        for (int u = 0; u < U; ++u) Ld<VW>::coherent(v + c0 + u * STEP, pv[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int e = 0; e < VW; ++e)
+#pragma unroll
+                for (int r = 0; r < R; ++r) acc[r] = fma(av0[r][u][e], pv[u][e], acc[r]);
+    }
+    const long long cb = pre ? TILE : 0;
 
-    if (row0 + R <= keep_rows) gemv_accumulate<R, U, NT, VW, false, true>(acc, a, v, 0, n, tid);
-    else gemv_accumulate<R, U, NT, VW, false, false>(acc, a, v, 0, n, tid);
+    if (held) gemv_accumulate<R, U, NT, VW, true, true>(acc, a, v, cb, n, tid);
+    else gemv_accumulate<R, U, NT, VW, true, false>(acc, a, v, cb, n, tid);
 
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -181,7 +222,7 @@ gemv_ldg_keep_kernel(const double *__restrict__ A, const double *__restrict__ v,
         const long long row = row0 + tid;
         if (row < m) {
             y[row] = s;
-            if (w != nullptr) contrib = s * w[row];
+            if (w != nullptr) contrib = s * __ldcg(w + row);
         }
     }
     if (w == nullptr) return;
@@ -566,8 +607,11 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
     long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
     const bool first = i < m;
     double x0 = 0.0, p0 = 0.0, r0 = 0.0, a0 = 0.0;
-    if (first) { x0 = x[i]; p0 = p_loc[i]; r0 = r[i]; a0 = Ap[i]; }
+    if (first) { x0 = x[i]; p0 = p_loc[i]; r0 = r[i]; }        /* last written two kernels back */
     const double rho = sc->rr[cur];
+    pdl_wait();                                                /* Ap, the dot partials, the flags: the product */
+    pdl_launch_dependents();
+    if (first) a0 = __ldcg(Ap + i);
     if (*(volatile int *)&sc->stop_req) return;
     unsigned int ep = 0u, gen = 0u;
     double pAp;
@@ -599,7 +643,7 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
     }
     for (; i < m; i += (long long)gridDim.x * VEC_NT) {
         x[i] = __dadd_rn(x[i], __dmul_rn(p_loc[i], alpha));
-        const double ri = __dsub_rn(r[i], __dmul_rn(Ap[i], alpha));
+        const double ri = __dsub_rn(r[i], __dmul_rn(__ldcg(Ap + i), alpha));
         r[i] = ri;
         s = fma(ri, ri, s);
     }
@@ -636,8 +680,11 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
     long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
     const bool first = i < m;
     double r0 = 0.0, p0 = 0.0;
-    if (first) { r0 = r[i]; p0 = p_loc[i]; }                   /* requested before the scalars are waited for */
+    if (first) p0 = p_loc[i];                                  /* last written three kernels back */
     const double rho = sc->rr[cur];
+    pdl_wait();                                                /* r, the r.r partials, the flags: xr_update */
+    pdl_launch_dependents();
+    if (first) r0 = __ldcg(r + i);
     if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
     unsigned int ep = 0u, gen = 0u;
     double beta;
@@ -666,7 +713,7 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
     const double coef = beta / rho;
     const long long lo = COMM ? (long long)peers.rank * m : 0;
     for (bool head = first; i < m; i += (long long)gridDim.x * VEC_NT, head = false) {
-        const double pi = head ? __dadd_rn(r0, __dmul_rn(p0, coef)) : __dadd_rn(r[i], __dmul_rn(p_loc[i], coef));
+        const double pi = head ? __dadd_rn(r0, __dmul_rn(p0, coef)) : __dadd_rn(__ldcg(r + i), __dmul_rn(p_loc[i], coef));
         p_loc[i] = pi;
         if constexpr (COMM) {
             for (int g = 0; g < peers.ranks; ++g)
@@ -777,9 +824,12 @@ cg2_step_one_kernel(double *__restrict__ x, double *__restrict__ r_loc, double *
     long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
     const bool first = i < m;
     double r0 = 0.0, p0 = 0.0, w0 = 0.0, s0 = 0.0, x0 = 0.0;
-    if (first) { r0 = r_loc[i]; p0 = pvec[i]; w0 = w[i]; s0 = svec[i]; x0 = x[i]; }
+    if (first) { r0 = r_loc[i]; p0 = pvec[i]; s0 = svec[i]; x0 = x[i]; }     /* the previous step's */
     const unsigned int k = sc->cg2_k[cur];
     const double gprev = sc->cg2_gprev[cur], aprev = sc->cg2_aprev[cur];
+    pdl_wait();                                                /* w, delta's partials, the flags: the product */
+    pdl_launch_dependents();
+    if (first) w0 = __ldcg(w + i);
     if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
     double gamma, delta;
     cta_sum_partials2<VEC_NT>(partials + (size_t)cur * CGK_MAX_VEC_CTAS, k == 0u ? 0 : (int)gridDim.x,
@@ -816,7 +866,7 @@ cg2_step_one_kernel(double *__restrict__ x, double *__restrict__ r_loc, double *
     for (bool head = first; i < m; i += (long long)gridDim.x * VEC_NT, head = false) {
         const double ri = head ? r0 : r_loc[i];
         const double pi = __dadd_rn(ri, __dmul_rn(head ? p0 : pvec[i], beta));
-        const double si = __dadd_rn(head ? w0 : w[i], __dmul_rn(head ? s0 : svec[i], beta));
+        const double si = __dadd_rn(head ? w0 : __ldcg(w + i), __dmul_rn(head ? s0 : svec[i], beta));
         pvec[i] = pi;
         svec[i] = si;
         x[i] = __dadd_rn(head ? x0 : x[i], __dmul_rn(pi, alpha));
@@ -1108,11 +1158,14 @@ extern "C" int cgk_gemv(const cgk_gemv_plan *plan, const double *A, const double
                                                                         sc, (long long)m, (long long)n);
         return (int)cudaGetLastError();
     }
-    if (plan->keep_rows > 0) {
+    /* the L2-keep kernel doubles as the GEMV of the dependent-launch chain (small systems) */
+    if (plan->keep_rows > 0 ||
+        (tl_pdl && plan->l2_bytes > 0 && 8.0 * (double)m * (double)n <= 3.0 * (double)plan->l2_bytes &&
+         find_keep(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec))) {
         const keep_cfg *k = find_keep(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec);
         if (!k) return (int)cudaErrorInvalidValue;
-        k->fn<<<plan->grid, plan->threads, 0, st>>>(A, v, w, y, partials, dot_out, sc, (long long)m, (long long)n,
-                                                    plan->keep_rows);
+        cgk_launch(k->fn, dim3(plan->grid), dim3(plan->threads), 0, st, A, v, w, y, partials, dot_out, sc, (long long)m,
+                   (long long)n, (long long)plan->keep_rows);
         return (int)cudaGetLastError();
     }
     gemv_fn fn = pick_ldg(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec);
@@ -1206,9 +1259,8 @@ extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const do
         xr_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
                                                                                 sc, cur, guard, (long long)m, *peers, nullptr, 0);
     else
-        xr_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                                 sc, cur, guard, (long long)m, k_no_peers,
-                                                                                 dot_partials, n_dot);
+        cgk_launch(xr_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
+                   rr_out, sc, cur, guard, (long long)m, k_no_peers, dot_partials, n_dot);
     return (int)cudaGetLastError();
 }
 
@@ -1222,9 +1274,8 @@ extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int
         p_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
                                                                                (long long)max_iter, (long long)m, *peers, nullptr, 0);
     else
-        p_update_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
-                                                                                (long long)max_iter, (long long)m, k_no_peers,
-                                                                                rr_partials, n_rr);
+        cgk_launch(p_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
+                   ignore_stop, (long long)max_iter, (long long)m, k_no_peers, rr_partials, n_rr);
     return (int)cudaGetLastError();
 }
 
@@ -1245,9 +1296,8 @@ extern "C" int cgk_cg2_step_one(double *x, double *r_loc, double *pvec, double *
                                 cgk_scalars *sc, int cur, double eps, int ignore_stop, int guard, int64_t max_iter,
                                 int64_t m, const double *dot_partials, int n_dot, void *stream)
 {
-    cg2_step_one_kernel<<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, cur, eps,
-                                                                          ignore_stop, guard, (long long)max_iter,
-                                                                          (long long)m, dot_partials, n_dot);
+    cgk_launch(cg2_step_one_kernel, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r_loc, pvec, svec, w, partials,
+               sc, cur, eps, ignore_stop, guard, (long long)max_iter, (long long)m, dot_partials, n_dot);
     return (int)cudaGetLastError();
 }
 

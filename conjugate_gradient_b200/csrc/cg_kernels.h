@@ -158,6 +158,10 @@ int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
                   double *partials, double *rr_out, cgk_scalars *sc, int cur, int guard,
                   int64_t m, const cgk_peers *peers, const double *dot_partials, int n_dot,
                   void *stream);
+/* Programmatic dependent launch for the calling thread's following launches of the one-rank
+ * iteration kernels (cg_device.cuh explains the rule the kernels keep); 0 = plain launches. */
+void cgk_set_pdl(int on);
+int cgk_pdl_enabled(void);
 int cgk_vec_grid(int64_t m);      /* CTAs (= partials) of the vector kernels for m elements */
 
 /* beta = rr[cur^1]: bookkeeping + stop rule on thread 0; p = r + (beta/rho) p. */

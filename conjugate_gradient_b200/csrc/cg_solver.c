@@ -743,8 +743,19 @@ static int enqueue_product(cgb_ctx *c, cudaEvent_t ev_a, cudaEvent_t ev_b)
 
 /* One CG iteration on the solver stream; `cur` is the parity of the loop index
  * (selects which rr[] slot is rho).  Mirrors parallel_cg.c:290-323. */
+static int enqueue_iteration_body(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int cur,
+                                  cudaEvent_t ev_a, cudaEvent_t ev_b);
 static int enqueue_iteration(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int cur,
                              cudaEvent_t ev_a, cudaEvent_t ev_b)
+{
+    cgk_set_pdl(c->pdl);              /* one rank: the iteration's kernels overlap their launches */
+    const int rc = enqueue_iteration_body(c, o, max_iter, cur, ev_a, ev_b);
+    cgk_set_pdl(0);
+    return rc;
+}
+
+static int enqueue_iteration_body(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int cur,
+                                  cudaEvent_t ev_a, cudaEvent_t ev_b)
 {
     const int multi = c->ranks > 1;
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
@@ -790,7 +801,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     key.ignore_stop = o->ignore_stop; key.chunk = chunk; key.plan = c->plan; key.guard = o->guard;
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
     key.symv = c->use_symv; key.symv_ru = c->symv_ru; key.symv_split = c->symv_split;
-    key.cg_variant = o->cg_variant; key.n_dot = c->n_dot; key.defer_rr = c->defer_rr;
+    key.cg_variant = o->cg_variant; key.n_dot = c->n_dot; key.defer_rr = c->defer_rr; key.pdl = c->pdl;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -881,7 +892,11 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
 
     /* one rank, classic recurrence: the two dot products are finished by their consumers
      * (cg_kernels.h, "Deferred reductions"); CGB_DEFER=0 keeps the producers' last-CTA sums */
-    c->n_dot = 0; c->defer_rr = 0;
+    c->n_dot = 0; c->defer_rr = 0; c->pdl = 0;
+    {
+        const char *e = getenv("CGB_PDL");
+        if (!multi && !(e && *e == '0')) c->pdl = 1;
+    }
     {
         const char *e = getenv("CGB_DEFER");
         if (!multi && !(e && *e == '0')) {
@@ -897,6 +912,11 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     if (use_graph) {
         chunk = pick_chunk(c, &o);
         int rc = build_graph(c, &o, max_iter, chunk);
+        if (rc != CGB_OK && c->pdl) {          /* a driver that cannot capture programmatic edges */
+            (void)cudaGetLastError();
+            c->pdl = 0;
+            rc = build_graph(c, &o, max_iter, chunk);
+        }
         if (rc != CGB_OK) return rc;
     }
     int timed_pairs = 0;
@@ -1004,6 +1024,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->gemv_keep_rows = c->plan.keep_rows;
         stats->exit_reason = c->h_sc->stop_req;
         stats->cg_variant = o.cg_variant;
+        stats->pdl = c->pdl;
         if (gemv_pairs_used > 0) {
             double sum = 0.0, mn = 1e300;
             for (int i = 0; i < gemv_pairs_used; ++i) {

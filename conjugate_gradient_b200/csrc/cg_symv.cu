@@ -30,6 +30,8 @@ symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
                  const int2 *__restrict__ tiles, double *__restrict__ rowpart,
                  double *__restrict__ colpart, cgk_scalars *__restrict__ sc, long long n, int split)
 {
+    pdl_wait();                       /* p and the flags come from the previous kernel */
+    pdl_launch_dependents();
     const int stop = *(volatile int *)&sc->stop_req;
     if (stop) {
         if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
@@ -48,8 +50,8 @@ symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
 
     double pj[4][4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) Ld<4>::keep(p + J * SY_T + k * 128 + lane * 4, pj[k]);
-    for (int i = tid; i < SY_T; i += SY_NT) s_pI[i] = p[I * SY_T + i];
+    for (int k = 0; k < 4; ++k) Ld<4>::coherent(p + J * SY_T + k * 128 + lane * 4, pj[k]);   /* not .nc: see pdl_wait */
+    for (int i = tid; i < SY_T; i += SY_NT) s_pI[i] = __ldcg(p + I * SY_T + i);
     __syncthreads();
 
     double cacc[4][4];
@@ -114,6 +116,8 @@ symv_finish_kernel(const double *__restrict__ rowpart, const double *__restrict_
                    double *__restrict__ partials, double *__restrict__ dot_out,
                    cgk_scalars *__restrict__ sc, long long n, int split)
 {
+    pdl_wait();
+    pdl_launch_dependents();
     if (*(volatile int *)&sc->stop_req) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const long long i = (long long)blockIdx.x * SY_FR + lane;            /* n % SY_T == 0: always < n */
@@ -134,7 +138,7 @@ symv_finish_kernel(const double *__restrict__ rowpart, const double *__restrict_
 #pragma unroll
         for (int q = 0; q < SY_NW; ++q) t += s_part[q][lane];
         y[i] = t;
-        if (w != nullptr) mine = warp_sum(t * w[i]);
+        if (w != nullptr) mine = warp_sum(t * __ldcg(w + i));
     }
     if (w == nullptr) return;
     cta_partials_finish<SY_NT>(mine, partials, dot_out, &sc->ticket_gemv);
@@ -206,11 +210,11 @@ extern "C" int cgk_symv(const double *A, const double *v, const double *w, doubl
     if (n % SY_T != 0 || ntiles < 1 || (split != 1 && split != 2 && split != 4)) return (int)cudaErrorInvalidValue;
     const int2 *tl = (const int2 *)tiles;
     switch (rows_in_flight) {
-    case 1: symv_tile_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
-    case 2: symv_tile_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
-    default: symv_tile_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    case 1: cgk_launch(symv_tile_kernel<1>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    case 2: cgk_launch(symv_tile_kernel<2>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    default: cgk_launch(symv_tile_kernel<4>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
     }
-    symv_finish_kernel<<<(unsigned)(n / SY_FR), SY_NT, 0, st>>>(rowpart, colpart, w, y, partials, dot_out, sc, (long long)n, split);
+    cgk_launch(symv_finish_kernel, dim3((unsigned)(n / SY_FR)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc, (long long)n, split);
     return (int)cudaGetLastError();
 }
 

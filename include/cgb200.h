@@ -138,6 +138,9 @@ typedef struct cgb_stats {
     int     cg_variant;        /* CGB_CG_* as run                                                  */
     int64_t gemv_keep_rows;    /* rows of A held in L2 across iterations (0: plain streaming)      */
     int64_t h2d_bytes;         /* bytes the last cgb_load_host / cgb_load_host_symmetric copied    */
+    int     pdl;               /* 1: the iteration kernels overlapped their launches (programmatic */
+                               /* dependent launch; one rank, CGB_PDL=0 in the environment: off)   */
+    int     reserved_;
 } cgb_stats;
 
 /* ---- debugging -------------------------------------------------------------- */
