@@ -327,7 +327,9 @@ gemv_ldg_comm_kernel(const double *__restrict__ A, const double *v,
     }
     if (wid == 0) contrib = warp_sum(contrib);
     double total = 0.0;
-    if (cta_partials_finish_sys<NT>(contrib, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {
+    /* device-scope fences: the CTAs store nothing into peer memory, and the dot the last CTA
+     * sends is a self-validating {data, tag} pair (a system-scope fence per CTA costs microseconds) */
+    if (cta_partials_finish_sys<NT, false>(contrib, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {
         for (int g = 0; g < peers.ranks; ++g)
             ll_send(&peers.mbox[g]->dot[0][ep & 1u][peers.rank][0], total, tag);
         sc->ep_gemv = ep + 1u;
@@ -650,7 +652,8 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
     const double mine = vec_cta_sum(s);
     if constexpr (COMM) {
         double total = 0.0;
-        if (cta_partials_finish_sys<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec, &total) && threadIdx.x == 0) {
+        /* x and r are local: device-scope fences (see gemv_ldg_comm_kernel) */
+        if (cta_partials_finish_sys<VEC_NT, false>(mine, partials, rr_out, &sc->ticket_vec, &total) && threadIdx.x == 0) {
             const unsigned int e = ep + 1u;                       /* r.r events: 0 = init, k+1 = iteration k */
             for (int g = 0; g < peers.ranks; ++g)
                 ll_send(&peers.mbox[g]->dot[1][e & 1u][peers.rank][0], total, cgk_tag(gen, e));

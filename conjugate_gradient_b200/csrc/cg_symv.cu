@@ -412,7 +412,7 @@ symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__rest
     if (tid == 0)
         for (int q = 0; q < SY_NW; ++q) mine += s_w[q];
     double total = 0.0;
-    if (cta_partials_finish_sys<SY_NT>(mine, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {
+    if (cta_partials_finish_sys<SY_NT, false>(mine, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {   /* local stores only */
         const unsigned int tag = cgk_tag(gen, ep);
         for (int g = 0; g < peers.ranks; ++g)
             ll_send(&peers.mbox[g]->dot[0][ep & 1u][peers.rank][0], total, tag);
