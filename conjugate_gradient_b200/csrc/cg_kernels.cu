@@ -244,6 +244,8 @@ gemv_ldg_comm_kernel(const double *__restrict__ A, const double *v,
                      double *__restrict__ partials, double *__restrict__ dot_out,
                      cgk_scalars *sc, long long m, long long n, const cgk_peers peers)
 {
+    pdl_wait();                       /* launch overlap only: everything below depends on the previous kernel */
+    pdl_launch_dependents();
     const int stop = *(volatile int *)&sc->stop_req;
     if (stop) {
         if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
@@ -748,6 +750,8 @@ cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec
                 const double *__restrict__ w, double *__restrict__ partials, cgk_scalars *sc, double eps,
                 int ignore_stop, int guard, long long max_iter, long long m, const cgk_peers peers)
 {
+    pdl_wait();
+    pdl_launch_dependents();
     if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
     const unsigned int k = *(volatile unsigned int *)&sc->ep_xr;
     const unsigned int gen = *(volatile unsigned int *)&sc->gen;
@@ -785,7 +789,7 @@ cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec
     for (long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x; i < m;
          i += (long long)gridDim.x * VEC_NT) {
         const double pi = __dadd_rn(r_loc[i], __dmul_rn(pvec[i], beta));
-        const double si = __dadd_rn(w[i], __dmul_rn(svec[i], beta));
+        const double si = __dadd_rn(__ldcg(w + i), __dmul_rn(svec[i], beta));   /* written by the previous kernel: not .nc */
         pvec[i] = pi;
         svec[i] = si;
         x[i] = __dadd_rn(x[i], __dmul_rn(pi, alpha));
@@ -1235,7 +1239,7 @@ extern "C" int cgk_gemv_comm(const cgk_gemv_plan *plan, const double *A, const d
 {
     const comm_cfg *c = find_comm(plan->rows_per_cta, plan->unroll, plan->threads, plan->vec);
     if (!c || !peers || !w) return (int)cudaErrorInvalidValue;
-    c->fn<<<plan->grid, plan->threads, 0, (cudaStream_t)stream>>>(A, v, w, y, partials, dot_out, sc,
+    cgk_launch(c->fn, dim3(plan->grid), dim3(plan->threads), 0, (cudaStream_t)stream, A, v, w, y, partials, dot_out, sc,
                                                                   (long long)m, (long long)n, *peers);
     return (int)cudaGetLastError();
 }
@@ -1259,8 +1263,8 @@ extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const do
                              void *stream)
 {
     if (peers)
-        xr_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r, p_loc, Ap, partials, rr_out,
-                                                                                sc, cur, guard, (long long)m, *peers, nullptr, 0);
+        cgk_launch(xr_update_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
+                   rr_out, sc, cur, guard, (long long)m, *peers, (const double *)nullptr, 0);
     else
         cgk_launch(xr_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
                    rr_out, sc, cur, guard, (long long)m, k_no_peers, dot_partials, n_dot);
@@ -1274,8 +1278,8 @@ extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int
                             const double *rr_partials, int n_rr, void *stream)
 {
     if (peers)
-        p_update_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(p_loc, r, sc, cur, eps, ignore_stop,
-                                                                               (long long)max_iter, (long long)m, *peers, nullptr, 0);
+        cgk_launch(p_update_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
+                   ignore_stop, (long long)max_iter, (long long)m, *peers, (const double *)nullptr, 0);
     else
         cgk_launch(p_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
                    ignore_stop, (long long)max_iter, (long long)m, k_no_peers, rr_partials, n_rr);
@@ -1287,8 +1291,8 @@ extern "C" int cgk_cg2_step(double *x, double *r_loc, double *pvec, double *svec
                             int64_t max_iter, int64_t m, const cgk_peers *peers, void *stream)
 {
     if (peers)
-        cg2_step_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
-                                                                               ignore_stop, guard, (long long)max_iter, (long long)m, *peers);
+        cgk_launch(cg2_step_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r_loc, pvec, svec, w,
+                   partials, sc, eps, ignore_stop, guard, (long long)max_iter, (long long)m, *peers);
     else
         cg2_step_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
                                                                                 ignore_stop, guard, (long long)max_iter, (long long)m, k_no_peers);

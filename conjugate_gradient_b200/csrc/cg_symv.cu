@@ -248,6 +248,8 @@ symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 
                       double *__restrict__ rowpart, double *__restrict__ colpart, cgk_scalars *sc,
                       long long m, long long n, int split, const cgk_peers peers)
 {
+    pdl_wait();
+    pdl_launch_dependents();
     const int stop = *(volatile int *)&sc->stop_req;
     if (stop) {
         if (blockIdx.x == 0 && threadIdx.x == 0) sc->stopped = stop;
@@ -339,6 +341,8 @@ __global__ void __launch_bounds__(SY_NT)
 symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long m, long long n, int split,
                  const cgk_symplan sp, const cgk_peers peers)
 {
+    pdl_wait();
+    pdl_launch_dependents();
     if (*(volatile int *)&sc->stop_req) return;
     const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
     const unsigned int gen = *(volatile unsigned int *)&sc->gen;
@@ -372,6 +376,8 @@ symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__rest
                         double *__restrict__ dot_out, cgk_scalars *sc, long long m, long long n, int split,
                         const cgk_symplan sp, const cgk_peers peers)
 {
+    pdl_wait();
+    pdl_launch_dependents();
     if (*(volatile int *)&sc->stop_req) return;
     const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
     const unsigned int gen = *(volatile unsigned int *)&sc->gen;
@@ -475,13 +481,13 @@ extern "C" int cgk_symv_comm(const double *A, const double *v, const double *w, 
     if (split != 1 && split != 2 && split != 4) return (int)cudaErrorInvalidValue;
     const int2 *tl = (const int2 *)tiles;
     switch (rows_in_flight) {
-    case 1: symv_tile_comm_kernel<1><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
-    case 2: symv_tile_comm_kernel<2><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
-    default: symv_tile_comm_kernel<4><<<(unsigned)ntiles, SY_NT, 0, st>>>(A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    case 1: cgk_launch(symv_tile_comm_kernel<1>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    case 2: cgk_launch(symv_tile_comm_kernel<2>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    default: cgk_launch(symv_tile_comm_kernel<4>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
     }
     if (sp->nblk > 0)
-        symv_push_kernel<<<dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), SY_NT, 0, st>>>(colpart, sc, (long long)m, (long long)n, split, *sp, *peers);
-    symv_finish_comm_kernel<<<(unsigned)(m / SY_NT), SY_NT, 0, st>>>(rowpart, colpart, w, y, partials, dot_out, sc,
-                                                                     (long long)m, (long long)n, split, *sp, *peers);
+        cgk_launch(symv_push_kernel, dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), dim3(SY_NT), 0, st, colpart, sc, (long long)m, (long long)n, split, *sp, *peers);
+    cgk_launch(symv_finish_comm_kernel, dim3((unsigned)(m / SY_NT)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc,
+               (long long)m, (long long)n, split, *sp, *peers);
     return (int)cudaGetLastError();
 }
