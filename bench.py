@@ -327,7 +327,11 @@ def b200_arm(args):
                    "seed": SEED, "rows_per_gpu": m, "parallelism": f"row-block x{world}" if world > 1 else "single GPU",
                    "exchange": {0: "none (one rank)", 1: "nccl all-gather + 2 all-reduce per iteration",
                                 2: "fused peer-memory pushes over NVLink inside the solver kernels"}[st["comm"]],
-                   "l2": f"A block is {8.0 * m * n / 1e9:.2f} GB per GPU, far larger than the 126 MB L2: no flush needed",
+                   "l2": (f"A block is {8.0 * m * n / 1e9:.2f} GB per GPU, far larger than the 126 MB L2: no flush needed"
+                          if 8.0 * m * n > 3 * 126e6 else
+                          f"A block is {8.0 * m * n / 1e6:.0f} MB per GPU, within a few L2 sizes: every iteration re-reads the same "
+                          "matrix, so L2 residency is part of the workload (DESIGN.md 4.2) and is NOT flushed"),
+                   "launch": {"programmatic_dependent_launch": int(stg.get("pdl", 0)), "graph_iterations": stg["graph_chunk"]},
                    "gemv_kernel": {k: st[k] for k in ("gemv_variant", "gemv_rows", "gemv_unroll", "gemv_threads",
                                                       "gemv_vec", "gemv_stages", "gemv_tile_cols", "gemv_grid")}},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

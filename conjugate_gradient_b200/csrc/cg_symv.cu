@@ -381,19 +381,34 @@ symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__rest
     if (*(volatile int *)&sc->stop_req) return;
     const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
     const unsigned int gen = *(volatile unsigned int *)&sc->gen;
-    const int tid = threadIdx.x;
+    /* 32 local rows per CTA; the 8 warps take every 8th term of the row's list of partials
+     * (as symv_finish_kernel: 8 x the CTAs, an 8 x shorter chain of loads per thread) */
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const long long mt = m / SY_T;
-    const long long i = (long long)blockIdx.x * SY_NT + tid;                 /* local row, < m */
-    const long long Il = i / SY_T;
+    const long long i = (long long)blockIdx.x * SY_FR + lane;                /* local row, < m */
+    const long long Il = i / SY_T;                                           /* the same for the whole CTA */
     double s = 0.0;
-    /* everything this rank computed itself first (hides the wait for the peers' sums) */
-    for (long long J = (long long)peers.rank * mt + Il; J < (long long)(peers.rank + 1) * mt; ++J)
-        s += __ldcs(rowpart + J * m + i);
+    /* everything this rank computed itself first (hides the wait for the peers' sums): the flat
+     * list [own block's row partials | each foreign block's | own column partials], stride 8 */
+    long long k = wid;
+    {
+        const long long cnt = mt - Il, J0 = (long long)peers.rank * mt + Il;
+#pragma unroll 4
+        for (; k < cnt; k += SY_NW) s += __ldcs(rowpart + (J0 + k) * m + i);
+        k -= cnt;
+    }
     for (int b = 0; b < sp.nblk; ++b)
-        if (Il < sp.row_end[b])
-            for (long long J = (long long)sp.blk_rank[b] * mt + sp.col_begin[b]; J < (long long)(sp.blk_rank[b] + 1) * mt; ++J)
-                s += __ldcs(rowpart + J * m + i);
-    for (long long I2 = 0; I2 < Il * split; ++I2) s += __ldcs(colpart + I2 * n + (long long)peers.rank * m + i);
+        if (Il < sp.row_end[b]) {
+            const long long cnt = mt - sp.col_begin[b], J0 = (long long)sp.blk_rank[b] * mt + sp.col_begin[b];
+#pragma unroll 4
+            for (; k < cnt; k += SY_NW) s += __ldcs(rowpart + (J0 + k) * m + i);
+            k -= cnt;
+        }
+    {
+        const long long cnt = Il * split;
+#pragma unroll 4
+        for (; k < cnt; k += SY_NW) s += __ldcs(colpart + k * n + (long long)peers.rank * m + i);
+    }
     /* column sums other ranks computed for my columns */
     if (tid < sp.nsrc) {
         const unsigned long long *f = &peers.mbox[peers.rank]->c_flag[sp.src_rank[tid]];
@@ -406,17 +421,18 @@ symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__rest
     }
     __syncthreads();
     const double *rx = peers.crecv[peers.rank];
-    for (int q = 0; q < sp.nsrc; ++q)
-        if (Il >= sp.src_col_begin[q]) s += __ldcg(rx + (long long)sp.src_rank[q] * m + i);
-    y[i] = s;
-    double contrib = s * w[i];
-    __shared__ double s_w[SY_NW];
-    contrib = warp_sum(contrib);
-    if ((tid & 31) == 0) s_w[tid >> 5] = contrib;
+    if (wid < sp.nsrc && Il >= sp.src_col_begin[wid]) s += __ldcg(rx + (long long)sp.src_rank[wid] * m + i);   /* nsrc <= 4 < 8 warps */
+    __shared__ double s_part[SY_NW][SY_FR];
+    s_part[wid][lane] = s;
     __syncthreads();
     double mine = 0.0;
-    if (tid == 0)
-        for (int q = 0; q < SY_NW; ++q) mine += s_w[q];
+    if (wid == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < SY_NW; ++q) t += s_part[q][lane];
+        y[i] = t;
+        mine = warp_sum(t * w[i]);
+    }
     double total = 0.0;
     if (cta_partials_finish_sys<SY_NT, false>(mine, partials, dot_out, &sc->ticket_gemv, &total) && tid == 0) {   /* local stores only */
         const unsigned int tag = cgk_tag(gen, ep);
@@ -487,7 +503,7 @@ extern "C" int cgk_symv_comm(const double *A, const double *v, const double *w, 
     }
     if (sp->nblk > 0)
         cgk_launch(symv_push_kernel, dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), dim3(SY_NT), 0, st, colpart, sc, (long long)m, (long long)n, split, *sp, *peers);
-    cgk_launch(symv_finish_comm_kernel, dim3((unsigned)(m / SY_NT)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc,
+    cgk_launch(symv_finish_comm_kernel, dim3((unsigned)(m / SY_FR)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc,
                (long long)m, (long long)n, split, *sp, *peers);
     return (int)cudaGetLastError();
 }
