@@ -109,3 +109,48 @@ def test_numpy_emulation_of_the_three_kernels_gives_A_times_p(ranks, mt):
                     s += recv[r, sp.src_rank[q], i]
             y[r * m + i] = s
     np.testing.assert_allclose(y, A @ p, rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.parametrize("ranks", [2, 3, 4, 8])
+@pytest.mark.parametrize("mt", [1, 2, 4, 16])
+@pytest.mark.parametrize("split", [1, 2, 4])
+def test_finish_kernels_split_the_partial_list_exactly_once(ranks, mt, split):
+    """symv_finish_comm_kernel (cg_symv.cu) walks the flat list [own block's row partials | each foreign
+    block's | own column partials] with 8 warps at stride 8, carrying the offset from one segment into
+    the next (k -= cnt).  Restated here: every term is visited by exactly one warp, whatever the
+    segment lengths."""
+    NW = 8
+    for r in range(ranks):
+        sp, _ = plan_and_tiles(r, ranks, mt)
+        for il in range(mt):
+            want = [("row", r * mt + il + k) for k in range(mt - il)]
+            for b in range(sp.nblk):
+                if il < sp.row_end[b]:
+                    want += [("row", sp.blk_rank[b] * mt + sp.col_begin[b] + k) for k in range(mt - sp.col_begin[b])]
+            want += [("col", k) for k in range(il * split)]
+            got = []
+            for wid in range(NW):
+                k = wid
+                cnt, j0 = mt - il, r * mt + il
+                while k < cnt:
+                    got.append(("row", j0 + k)); k += NW
+                k -= cnt
+                for b in range(sp.nblk):
+                    if il < sp.row_end[b]:
+                        cnt, j0 = mt - sp.col_begin[b], sp.blk_rank[b] * mt + sp.col_begin[b]
+                        while k < cnt:
+                            got.append(("row", j0 + k)); k += NW
+                        k -= cnt
+                cnt = il * split
+                while k < cnt:
+                    got.append(("col", k)); k += NW
+            assert sorted(got) == sorted(want) and len(set(got)) == len(got)
+
+
+def test_grid_helpers_of_the_deferred_reductions():
+    L = cg.lib()
+    L.cgk_symv_finish_grid.argtypes = [C.c_int64]; L.cgk_symv_finish_grid.restype = C.c_int
+    L.cgk_vec_grid.argtypes = [C.c_int64]; L.cgk_vec_grid.restype = C.c_int
+    assert L.cgk_symv_finish_grid(4096) == 4096 // 32       # 32 rows per CTA
+    assert L.cgk_vec_grid(1) == 1 and L.cgk_vec_grid(256) == 1 and L.cgk_vec_grid(257) == 2
+    assert L.cgk_vec_grid(10 ** 9) == 592                    # capped: the consumer adds at most 592 partials
