@@ -8,6 +8,10 @@
  *   cgk_xr_update     scalarVec+vecAdd (:299,303), scalarVec+vecSub (:304,308), vecVec :309
  *   cgk_p_update      stop test :314-317, scalarVec+vecAdd :318,322, rsold=beta :323
  *   cgk_generate      generateSPDmatrix.m:4-17
+ * Not in the reference: cgk_symv* (symmetric upper-tile product), cgk_cg2_step*
+ * (fused-reductions recurrence), cgk_gemv_comm / the <COMM> vector kernels (exchange over peer
+ * memory), cgk_ingest_* (text parser).  Launch-latency machinery shared by all of them: deferred
+ * reductions and programmatic dependent launch (cgk_set_pdl), both described where declared.
  */
 #ifndef CG_KERNELS_H
 #define CG_KERNELS_H
