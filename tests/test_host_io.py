@@ -1,0 +1,123 @@
+"""CPU tests of the host text path (cg_io.c): the parser that replaces initialize()'s
+fscanf("%f%*c") loop (serialConjugate.c:85-105, parallel_cg.c:147-168) for b, x0 and irregular
+files, and the writer of generateSPDmatrix.m's file format (:28-43).  The parser is
+multi-threaded (the file is cut at separators and the pieces are converted in parallel), so the
+properties are checked on files long enough to be split as well as on short ones.  Bit-exactness
+bar: every value equals Python's float() of the same token (correctly rounded, as strtod)."""
+import os
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+import conjugate_gradient_b200 as cg
+
+
+def parse(tmp_path, text, count, name="f.txt"):
+    p = tmp_path / name
+    p.write_bytes(text if isinstance(text, bytes) else text.encode())
+    return cg.read_values(str(p), count)
+
+
+@pytest.mark.parametrize("fmt", ["%.4f", "%.1f", "%.17g", "%.6e", "%+.10E", "%g"])
+def test_parser_matches_float_bit_for_bit(tmp_path, fmt):
+    rng = np.random.default_rng(7)
+    v = np.concatenate([rng.random(2000), rng.standard_normal(2000) * 1e3, rng.standard_normal(500) * 1e-300,
+                        rng.standard_normal(500) * 1e300, [0.0, -0.0, 1.0, 4096.5, 5e-324, 1.7976931348623157e308]])
+    toks = [fmt % x for x in v]
+    got = parse(tmp_path, "\n".join(toks) + "\n", len(toks))
+    want = np.array([float(t) for t in toks])
+    assert got.tobytes() == want.tobytes()
+
+
+def test_generator_file_format_round_trip(tmp_path):
+    # generateSPDmatrix.m:29,35,41: "%.4f\n" for A and b, "%.1f\n" for x
+    rng = np.random.default_rng(3)
+    n = 300
+    A = rng.random((n, n)); A = 0.5 * (A + A.T) + n * np.eye(n)
+    fa, fx = str(tmp_path / "A.txt"), str(tmp_path / "x.txt")
+    cg.write_values(fa, A, 4)
+    lines = open(fa).read().split("\n")
+    assert lines[-1] == "" and len(lines) == n * n + 1
+    assert lines[0] == "%.4f" % A[0, 0] and lines[n * n - 1] == "%.4f" % A[-1, -1]
+    back = cg.read_values(fa, n * n).reshape(n, n)
+    assert np.abs(back - A).max() <= 0.5e-4 + 1e-12
+    assert back.tobytes() == np.array([float("%.4f" % a) for a in A.ravel()]).reshape(n, n).tobytes()
+    cg.write_values(fx, np.zeros(n), 1)
+    assert open(fx).read() == "0.0\n" * n
+    assert cg.lib().cgb_count_values(os.fsencode(fa)) == n * n
+
+
+def test_large_file_is_split_between_threads_consistently(tmp_path):
+    # 2 M tokens of uneven length: piece boundaries fall inside runs of separators and next to signs
+    rng = np.random.default_rng(11)
+    n = 2_000_000
+    v = rng.standard_normal(n) * 10.0 ** rng.integers(-8, 8, n)
+    seps = np.array(["\n", " ", ",", "\r\n", "\t", ";", " \n "])[rng.integers(0, 7, n)]
+    toks = ["%.12g" % x for x in v]
+    text = "".join(t + s for t, s in zip(toks, seps))
+    got = parse(tmp_path, text, n)
+    assert got.tobytes() == np.array([float(t) for t in toks]).tobytes()
+    assert cg.lib().cgb_count_values(os.fsencode(str(tmp_path / "f.txt"))) == n
+    with pytest.raises(cg.CgbError) as e:
+        parse(tmp_path, text, n + 1)
+    assert f"found {n}" in str(e.value)
+
+
+@pytest.mark.parametrize("text,count,want", [
+    (b"1 2 3", 3, [1, 2, 3]),                                   # no trailing newline
+    (b"\n\n  1.5\n\n\n2.5   \n", 2, [1.5, 2.5]),                 # blank lines, trailing blanks
+    (b"\xef\xbb\xbf0.5\n0.25\n", 2, [0.5, 0.25]),               # BOM first (the reference's initialguess1.txt)
+    (b"1e3,1E-3;+7,-.5,5.", 5, [1000.0, 0.001, 7.0, -0.5, 5.0]),  # exponent forms, bare dot
+    (b"inf -inf\n", 2, [np.inf, -np.inf]),
+    (b"0x10\n", 1, [16.0]),                                      # strtod grammar: what "%lf" accepts
+    (b"3 4 5 6", 2, [3, 4]),                                     # more tokens than asked for: the first `count`
+])
+def test_token_rules(tmp_path, text, count, want):
+    np.testing.assert_array_equal(parse(tmp_path, text, count), np.array(want, dtype=float))
+
+
+@pytest.mark.parametrize("text,count", [(b"", 1), (b"\n \n", 1), (b"1.0 2.0", 3), (b"1.0 abc 2.0", 3), (b"1.0 2.0x 3.0", 3)])
+def test_short_or_malformed_files_are_errors_not_garbage(tmp_path, text, count):
+    # serialConjugate.c:92-98 ignores fscanf's return value and leaves the tail uninitialised
+    with pytest.raises(cg.CgbError) as e:
+        parse(tmp_path, text, count)
+    assert e.value.code == -3 or "expected" in str(e.value)
+
+
+def test_dimensions_file(tmp_path):
+    p = tmp_path / "dimensions.txt"
+    p.write_text("4096\n4096\n4096\n1\n")
+    assert cg.read_dimensions(str(p)) == (4096, 4096, 4096, 1)
+    p.write_text("2 2\r\n2 1")
+    assert cg.read_dimensions(str(p)) == (2, 2, 2, 1)
+    p.write_text("2\n2\n2\n")
+    with pytest.raises(cg.CgbError):
+        cg.read_dimensions(str(p))
+    with pytest.raises(cg.CgbError):
+        cg.read_dimensions(str(tmp_path / "missing.txt"))
+
+
+finite = st.floats(allow_nan=False, allow_infinity=False, width=64)
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.lists(finite, min_size=1, max_size=60),
+       st.lists(st.sampled_from(["\n", " ", ",", "\r\n", "\t", ";", "\n\n", " , "[1:2]]), min_size=60, max_size=60),
+       st.sampled_from(["%r", "%.17g", "%.4f", "%.3e", "%+.8g"]))
+def test_parser_property_any_doubles_any_separators(tmp_path_factory, values, seps, fmt):
+    toks = [(repr(x) if fmt == "%r" else fmt % x) for x in values]
+    text = "".join(t + s for t, s in zip(toks, seps))
+    d = tmp_path_factory.mktemp("prop")
+    got = parse(d, text, len(toks))
+    assert got.tobytes() == np.array([float(t) for t in toks]).tobytes()
+
+
+def test_writer_round_trips_every_double(tmp_path):
+    rng = np.random.default_rng(5)
+    bits = rng.integers(0, 2 ** 63, 20000, dtype=np.int64)
+    v = bits.view(np.float64)
+    v = v[np.isfinite(v)]
+    f = str(tmp_path / "rt.txt")
+    cg.write_values(f, v, -1)                                    # "%.17g"
+    assert cg.read_values(f, v.shape[0]).tobytes() == v.tobytes()
