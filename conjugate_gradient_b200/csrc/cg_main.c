@@ -60,6 +60,20 @@ typedef struct {
     double eps;
 } cli_t;
 
+/* Whole-token numeric options: "--gpus 0", "--gpus x" or "--eps -1" are usage errors, not
+ * silently a default (and never a division by zero in the divisibility test). */
+static int parse_ll(const char *opt, const char *v, long long lo, long long *out)
+{
+    char *end = NULL;
+    const long long x = strtoll(v, &end, 10);
+    if (end == v || *end != '\0' || x < lo) {
+        fprintf(stderr, "option %s takes an integer >= %lld (got \"%s\")\n", opt, lo, v);
+        return -1;
+    }
+    *out = x;
+    return 0;
+}
+
 static int parse_cli(int argc, char **argv, cli_t *c)
 {
     const char *pos[3] = {0, 0, 0};
@@ -80,12 +94,22 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         else if (!strcmp(a, "--write-x")) { c->write_x = v; ++i; }
         else if (!strcmp(a, "--run-record")) { c->record = v; ++i; }
         else if (!strcmp(a, "--emit-files")) { c->emit = v; c->round4 = 1; ++i; }
-        else if (!strcmp(a, "--gpus")) { c->gpus = atoi(v); ++i; }
-        else if (!strcmp(a, "--eps")) { c->eps = atof(v); ++i; }
-        else if (!strcmp(a, "--max-iter")) { c->max_iter = atoll(v); ++i; }
-        else if (!strcmp(a, "--gen")) { c->gen_n = atoll(v); ++i; }
+        else if (!strcmp(a, "--gpus")) {
+            long long g = 0;
+            if (parse_ll(a, v, 1, &g)) return -1;
+            if (g > 1024) { fprintf(stderr, "option --gpus: too many\n"); return -1; }
+            c->gpus = (int)g; ++i;
+        }
+        else if (!strcmp(a, "--eps")) {
+            char *end = NULL;
+            c->eps = strtod(v, &end);
+            if (end == v || *end != '\0' || !(c->eps > 0.0)) { fprintf(stderr, "option --eps takes a positive number (got \"%s\")\n", v); return -1; }
+            ++i;
+        }
+        else if (!strcmp(a, "--max-iter")) { long long k; if (parse_ll(a, v, 1, &k)) return -1; c->max_iter = k; ++i; }
+        else if (!strcmp(a, "--gen")) { long long k; if (parse_ll(a, v, 1, &k)) return -1; c->gen_n = k; ++i; }
         else if (!strcmp(a, "--seed")) { c->seed = strtoull(v, NULL, 10); ++i; }
-        else if (!strcmp(a, "--bench-iters")) { c->bench_iters = atoll(v); ++i; }
+        else if (!strcmp(a, "--bench-iters")) { long long k; if (parse_ll(a, v, 1, &k)) return -1; c->bench_iters = k; ++i; }
         else if (!strcmp(a, "--gemv")) { c->gemv = atoi(v); ++i; }
         else if (!strcmp(a, "--cg")) {
             if (!strcmp(v, "classic")) c->cg_variant = CGB_CG_CLASSIC;
@@ -93,7 +117,12 @@ static int parse_cli(int argc, char **argv, cli_t *c)
             else { fprintf(stderr, "--cg takes classic or fused\n"); return -1; }
             ++i;
         }
-        else if (!strcmp(a, "--kappa-log2")) { c->kappa_log2 = atoi(v); ++i; }
+        else if (!strcmp(a, "--kappa-log2")) {
+            long long k = 0;
+            if (parse_ll(a, v, 0, &k)) return -1;
+            if (k > 63) { fprintf(stderr, "option --kappa-log2: at most 63\n"); return -1; }
+            c->kappa_log2 = (int)k; ++i;
+        }
         else if (!strcmp(a, "--comm")) {
             if (!strcmp(v, "nccl")) c->comm = CGB_COMM_NCCL;
             else if (!strcmp(v, "peer")) c->comm = CGB_COMM_PEER;

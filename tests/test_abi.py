@@ -78,6 +78,24 @@ def test_cli_messages_without_gpu(golden_dir):
     assert r.returncode != 0 and "Could not open file" in r.stdout           # serialConjugate.c:103
 
 
+@pytest.mark.parametrize("args,msg", [
+    (["--gpus", "0"], "--gpus takes an integer >= 1"),          # was a division by zero in the n % gpus test
+    (["--gpus", "two"], "--gpus takes an integer >= 1"),
+    (["--eps", "-1"], "--eps takes a positive number"),
+    (["--max-iter", "x"], "--max-iter takes an integer >= 1"),
+    (["--gen", "0"], "--gen takes an integer >= 1"),
+    (["--kappa-log2", "99"], "at most 63"),
+    (["--cg", "pipelined"], "--cg takes classic or fused"),
+    (["--comm", "mpi"], "--comm takes nccl, peer or auto"),
+    (["--no-such-flag", "1"], "unknown option"),
+    (["--dims"], "needs a value"),
+])
+def test_cli_usage_errors(golden_dir, args, msg):
+    files = [os.path.join(golden_dir, f) for f in ("g2_matrixA.txt", "g2_vectorb.txt", "g2_x0.txt")]
+    r = subprocess.run([B.CLI_PATH] + files + args, capture_output=True, text=True)
+    assert r.returncode == 2 and msg in r.stderr, (r.returncode, r.stderr)
+
+
 def test_compute_fails_loudly_without_gpu():
     if cg.device_count() > 0:
         pytest.skip("a GPU is present")
