@@ -309,6 +309,7 @@ int cgb_read_values(const char *path, double *dst, int64_t count, int64_t *got)
 {
     text_t tx;
     if (got) *got = 0;
+    if (!path || count < 0 || (count > 0 && !dst)) return CGB_ERR_ARG;
     if (cgb_text_open(path, &tx) != 0) return CGB_ERR_IO;
     int64_t k = parse_parallel(tx.p, tx.len, dst, count);
     int bad = 0;

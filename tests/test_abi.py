@@ -103,3 +103,57 @@ def test_compute_fails_loudly_without_gpu():
         cg.Context(0)
     with pytest.raises(cg.CgbError):
         cg.conjugrad_host(np.eye(2), np.ones(2), np.zeros(2))
+
+
+def test_invalid_arguments_are_status_codes_not_crashes(golden_dir):
+    """Every entry point answers a bad argument with a CGB_ERR_* code and a message (the reference
+    would exit(0) or crash: serialConjugate.c:48-57,78-82); nothing here needs a GPU."""
+    import ctypes as C
+    L = cg.lib()
+    A, b, x = np.eye(2), np.ones(2), np.zeros(2)
+    o, st = B.make_options(), B.Stats()
+    ARG, NODEV, NOTDIV, STATE, IO = -1, -2, -4, -6, -7
+    host = L.cgb_conjugrad_host_opt
+    for n in (0, -1):
+        for gpus in (-1, 0, 1, 3, 100000):
+            assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, n, gpus, C.byref(o), C.byref(st)) == ARG
+    assert host(None, b.ctypes.data, x.ctypes.data, 2, 1, C.byref(o), C.byref(st)) == ARG
+    assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, 2, 3, C.byref(o), C.byref(st)) == NOTDIV   # parallel_cg.c:86-90
+    assert b"2 is not divisible by 3" in L.cgb_last_error()
+    assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, 2, 17, C.byref(o), C.byref(st)) == ARG
+    assert L.cgb_solve_generated(0, 1, 0, 1, C.byref(o), None, C.byref(st)) == ARG
+    assert L.cgb_solve_generated(4, 1, 0, 3, C.byref(o), None, C.byref(st)) == NOTDIV
+    files = [os.fsencode(os.path.join(golden_dir, f)) for f in ("g1_matrixA.txt", "g1_vectorb.txt", "g1_x0.txt")]
+    assert L.cgb_conjugrad_files(None, None, None, 2, 1, C.byref(o), x.ctypes.data, C.byref(st)) == ARG
+    assert L.cgb_conjugrad_files(*files, 0, 1, C.byref(o), x.ctypes.data, C.byref(st)) == ARG
+    assert L.cgb_conjugrad_files(*files, 2, 3, C.byref(o), x.ctypes.data, C.byref(st)) == NOTDIV
+    h = C.c_void_p()
+    assert L.cgb_create(None, 0) == ARG
+    assert L.cgb_create_rank(C.byref(h), 0, 3, 2, None) == ARG
+    assert L.cgb_create_rank(C.byref(h), 0, 0, 2, None) == ARG
+    assert L.cgb_destroy(None) == 0
+    for call in (lambda: L.cgb_solve(None, None, None),
+                 lambda: L.cgb_load_host(None, 2, A.ctypes.data, b.ctypes.data, x.ctypes.data),
+                 lambda: L.cgb_load_host_symmetric(None, 2, A.ctypes.data, b.ctypes.data, x.ctypes.data),
+                 lambda: L.cgb_load_text(None, 2, b"a", b"b", b"c"),
+                 lambda: L.cgb_generate(None, 2, 1, 0),
+                 lambda: L.cgb_read_x(None, x.ctypes.data),
+                 lambda: L.cgb_set_x0(None, x.ctypes.data),
+                 lambda: L.cgb_debug_check_guards(None),
+                 lambda: L.cgb_debug_poke(None, 1, 0, 1.0),
+                 lambda: L.cgb_debug_read(None, 0, 0, 1, x.ctypes.data),
+                 lambda: L.cgb_unique_id(None)):
+        assert call() == ARG
+        assert len(L.cgb_last_error()) > 0
+    assert L.cgb_last_stats(None) == STATE
+    d = (C.c_int64 * 4)()
+    assert L.cgb_read_dimensions(None, d) == IO
+    vb = files[1]
+    assert L.cgb_read_values(None, x.ctypes.data, 2, None) == ARG
+    assert L.cgb_read_values(vb, None, 2, None) == ARG
+    assert L.cgb_read_values(vb, x.ctypes.data, -3, None) == ARG
+    assert L.cgb_read_values(vb, x.ctypes.data, 0, None) == 0
+    assert L.cgb_write_values(None, x.ctypes.data, 2, 4) == IO
+    assert L.cgb_write_values(b"/nonexistent_dir/x.txt", x.ctypes.data, 2, 4) == IO
+    assert L.cgb_count_values(None) == -1
+    assert L.cgb_shutdown() == 0 and L.cgb_release_rank() == 0
