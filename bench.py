@@ -23,6 +23,14 @@ matrices converge in ~5 iterations.
            host cores: oracle/_ref (the real source over the MPI shim) when it
            was built for this n, else the 64-bit-index port in oracle/ (the
            reference's `int` indexing cannot address n > 46340).
+  graph_replay, symmetric_variant, fused_reductions_variant
+           the same K iterations replayed from the captured CUDA graph (what a
+           converging solve runs), and the two opt-in variants of SURVEY.md 8f-4
+           beside the headline -- the symmetric product declares its own
+           algorithmic bytes and carries its own `e2e` (asserted-symmetric upload).
+  config.launch
+           whether the iteration kernels used programmatic dependent launch, and
+           the iterations per graph.
 """
 import argparse
 import json
