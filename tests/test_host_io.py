@@ -121,3 +121,100 @@ def test_writer_round_trips_every_double(tmp_path):
     f = str(tmp_path / "rt.txt")
     cg.write_values(f, v, -1)                                    # "%.17g"
     assert cg.read_values(f, v.shape[0]).tobytes() == v.tobytes()
+
+
+# ---- the pieces the GPU ingest path shares with the host parser (cg_io.h) ----------------------
+import ctypes as C
+
+
+class Text(C.Structure):
+    _fields_ = [("p", C.c_void_p), ("len", C.c_size_t), ("mapped", C.c_int)]
+
+
+def _io():
+    L = cg.lib()
+    L.cgb_text_open.argtypes = [C.c_char_p, C.POINTER(Text)]; L.cgb_text_open.restype = C.c_int
+    L.cgb_text_close.argtypes = [C.POINTER(Text)]; L.cgb_text_close.restype = None
+    L.cgb_text_locate.argtypes = [C.POINTER(Text), C.c_int64, C.c_int64, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
+    L.cgb_text_locate.restype = C.c_int64
+    L.cgb_token_to_double.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_double)]; L.cgb_token_to_double.restype = C.c_int
+    return L
+
+
+@pytest.mark.parametrize("ranks", [1, 2, 3, 8])
+def test_locating_a_ranks_rows_in_the_text(tmp_path, ranks):
+    """cgb_load_text: every rank finds the BYTES of its own m x n values without parsing the rest
+    (what MPI_Scatter of the parsed matrix does in parallel_cg.c:112-115).  The ranges must start
+    at the first byte of the rank's first value, contain exactly its values, and tile the file."""
+    L = _io()
+    rng = np.random.default_rng(ranks)
+    n = 24 * ranks
+    vals = rng.standard_normal(n * n) * 10.0 ** rng.integers(-3, 4, n * n)
+    seps = np.array(["\n", " ", ",", "\r\n", "\t", "\n\n"])[rng.integers(0, 6, n * n)]
+    toks = ["%.6g" % x for x in vals]
+    raw = ("  \n" + "".join(t + s for t, s in zip(toks, seps))).encode()        # leading blanks too
+    f = tmp_path / "A.txt"
+    f.write_bytes(raw)
+    tx = Text()
+    assert L.cgb_text_open(os.fsencode(str(f)), C.byref(tx)) == 0
+    try:
+        m = n // ranks
+        prev_end = None
+        for r in range(ranks):
+            beg, end = C.c_size_t(), C.c_size_t()
+            total = L.cgb_text_locate(C.byref(tx), r * m * n, m * n, C.byref(beg), C.byref(end))
+            assert total == n * n
+            piece = raw[beg.value:end.value].decode()
+            got = piece.replace(",", " ").split()
+            assert got == toks[r * m * n:(r + 1) * m * n]
+            assert not chr(raw[beg.value]).isspace() and raw[beg.value:beg.value + len(toks[r * m * n])].decode() == toks[r * m * n]
+            if prev_end is not None:
+                assert prev_end <= beg.value and raw[prev_end:beg.value].decode().replace(",", " ").strip() == ""
+            prev_end = end.value
+        # asking for more values than the file holds: the count says so
+        beg, end = C.c_size_t(), C.c_size_t()
+        assert L.cgb_text_locate(C.byref(tx), 0, n * n + 5, C.byref(beg), C.byref(end)) == n * n
+    finally:
+        L.cgb_text_close(C.byref(tx))
+
+
+def test_locate_defers_files_with_a_bom_to_the_sequential_parser(tmp_path):
+    L = _io()
+    f = tmp_path / "bom.txt"
+    f.write_bytes(b"\xef\xbb\xbf1.0\n2.0\n")
+    tx = Text()
+    assert L.cgb_text_open(os.fsencode(str(f)), C.byref(tx)) == 0
+    beg, end = C.c_size_t(), C.c_size_t()
+    assert L.cgb_text_locate(C.byref(tx), 0, 2, C.byref(beg), C.byref(end)) == -1
+    L.cgb_text_close(C.byref(tx))
+    np.testing.assert_array_equal(cg.read_values(str(f), 2), [1.0, 2.0])       # which handles it
+
+
+@pytest.mark.parametrize("tok,ok", [("1.5", True), ("-0.0001", True), ("+3", True), ("1e-7", True), ("6.02E+23", True),
+                                    (".5", True), ("5.", True), ("123456789012345678901234567890", True),
+                                    ("1-2", False), ("abc", False), ("1.2.3", False), ("", False), ("--1", False),
+                                    ("1e", False), ("e5", False)])
+def test_single_token_conversion(tok, ok):
+    L = _io()
+    b = tok.encode()
+    buf = C.create_string_buffer(b, len(b) + 1)
+    base = C.addressof(buf)
+    out = C.c_double(-777.0)
+    r = L.cgb_token_to_double(C.cast(base, C.c_char_p), C.cast(base + len(b), C.c_char_p), C.byref(out))
+    assert bool(r) == ok
+    if ok:
+        assert out.value == float(tok)
+
+
+def test_appending_writer_builds_a_matrix_file_block_by_block(tmp_path):
+    # --emit-files writes the row blocks of a generated matrix in turn (cgb_write_values_mode, append)
+    L = cg.lib()
+    L.cgb_write_values_mode.argtypes = [C.c_char_p, C.c_void_p, C.c_int64, C.c_int, C.c_int]
+    L.cgb_write_values_mode.restype = C.c_int
+    rng = np.random.default_rng(2)
+    A = rng.random((6, 5))
+    f = str(tmp_path / "blocks.txt")
+    for k, blk in enumerate(np.array_split(A, 3)):
+        blk = np.ascontiguousarray(blk)
+        assert L.cgb_write_values_mode(os.fsencode(f), blk.ctypes.data, blk.size, 4, 1 if k else 0) == 0
+    assert open(f).read() == "".join("%.4f\n" % a for a in A.ravel())
