@@ -1,0 +1,130 @@
+"""CPU-only, static evidence about the machine code in libcgb200.so (cuobjdump on the built
+library; nothing is executed): the library carries sm_100a code only, the headline GEMV streams
+A with the 256-bit evict-first loads DESIGN.md §4.1 names, the bulk variant really uses the TMA
+engine (UBLKCP + mbarrier SYNCS), the small-n kernel keeps rows with evict-last, the iteration's
+kernels carry the programmatic-dependent-launch instructions, the dot products use no FP64
+atomics (bitwise reproducible sums), nothing touches a tensor core (a single-vector GEMV is not a
+contraction) and the hot kernels do not spill.  Mnemonics as listed in B200_PROFILING.md."""
+import re
+import shutil
+import subprocess
+
+import pytest
+
+import conjugate_gradient_b200 as cg
+
+CUOBJDUMP = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+pytestmark = pytest.mark.skipif(shutil.which(CUOBJDUMP) is None, reason="cuobjdump not installed")
+
+
+@pytest.fixture(scope="module")
+def sass():
+    """{demangled kernel name without the argument list: SASS text of the function}"""
+    txt = subprocess.run([CUOBJDUMP, "-sass", cg.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    parts = re.split(r"^\s*Function : (\S+)\s*$", txt, flags=re.M)
+    mangled = parts[1::2]
+    names = subprocess.run(["c++filt"], input="\n".join(mangled), capture_output=True, text=True, check=True).stdout.split("\n")
+    out = {}
+    for nm, body in zip(names, parts[2::2]):
+        nm = re.sub(r"^void ", "", nm)
+        nm = nm[:nm.index("(")] if "(" in nm else nm
+        out[nm.replace(" ", "")] = body
+    return out
+
+
+def ops(body):
+    """opcode (with modifiers) of every instruction line"""
+    return re.findall(r"^\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", body, flags=re.M)
+
+
+def test_only_sm_100a_code():
+    out = subprocess.run([CUOBJDUMP, "-lelf", cg.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    elfs = re.findall(r"ELF file\s+\d+: (\S+)", out)
+    assert elfs and all(e.endswith(".sm_100a.cubin") for e in elfs), elfs
+    ptx = subprocess.run([CUOBJDUMP, "-lptx", cg.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_9" not in ptx and "sm_8" not in ptx
+
+
+def test_every_kernel_family_is_present(sass):
+    fam = {re.sub(r"<.*", "", k) for k in sass}
+    want = {"gemv_ldg_kernel", "gemv_ldg_keep_kernel", "gemv_ldg_comm_kernel", "gemv_bulk_kernel",
+            "xr_update_kernel", "p_update_kernel", "init_residual_kernel", "after_init_kernel", "reset_kernel",
+            "cg2_step_kernel", "cg2_step_one_kernel", "generate_A_kernel", "generate_b_kernel",
+            "symv_tile_kernel", "symv_tile_comm_kernel", "symv_finish_kernel", "symv_finish_comm_kernel",
+            "symv_push_kernel", "symmetry_check_kernel", "ingest_scan_kernel", "ingest_count_kernel",
+            "ingest_parse_kernel", "scatter_kernel", "l2_flush_kernel"}
+    assert want <= fam, want - fam
+
+
+def test_headline_gemv_streams_with_256_bit_evict_first_loads(sass):
+    body = sass["gemv_ldg_kernel<8,2,512,4>"]          # the n = 65536 default (profiles/r01_summary.md §2)
+    o = ops(body)
+    wide = [x for x in o if x.startswith("LDG.") and ".256" in x]
+    # R * U = 16 independent 32-byte loads of A in flight per thread, all no-allocate + evict-first
+    assert sum(x == "LDG.E.NA.EFL2.256.CONSTANT" for x in wide) >= 16, wide
+    assert not any(x.startswith(("LDL", "STL")) for x in o), "the headline GEMV spills"
+    assert sum(x.startswith("DFMA") for x in o) >= 64
+    assert any(x.startswith("SHFL.BFLY") for x in o)     # warp-shuffle row reduction
+
+
+def test_default_gemv_shapes_do_not_spill(sass):
+    # the shapes cgk_gemv_make_plan picks by itself (tests/test_plans.py); the register-capped keep
+    # kernel and a few selectable 512-thread shapes carry 8-24 bytes of stack (profiles/r01_kernel_resources.txt)
+    for name in ("gemv_ldg_kernel<8,2,512,4>", "gemv_ldg_kernel<2,1,256,4>", "gemv_ldg_kernel<4,1,128,4>",
+                 "gemv_ldg_kernel<4,1,128,2>", "gemv_ldg_kernel<4,1,128,1>", "gemv_ldg_keep_kernel<2,1,256,4>"):
+        assert not any(x.startswith(("LDL", "STL")) for x in ops(sass[name])), name
+
+
+def test_every_vw4_gemv_uses_256_bit_loads(sass):
+    for name, body in sass.items():
+        m = re.match(r"gemv_ldg(_keep|_comm)?_kernel<(\d+),(\d+),(\d+),(\d+)>", name)
+        if not m:
+            continue
+        o = ops(body)
+        if m.group(5) == "4":
+            assert any(x.startswith("LDG.") and ".256" in x for x in o), name
+        if m.group(1) == "_keep":       # rows meant to survive in L2: evict-last beside evict-first
+            assert any(".ELL2." in x for x in o) and any(".EFL2." in x for x in o), name
+
+
+def test_bulk_variant_uses_the_tma_engine(sass):
+    bulk = {k: v for k, v in sass.items() if k.startswith("gemv_bulk_kernel<")}
+    assert len(bulk) >= 8
+    for name, body in bulk.items():
+        o = ops(body)
+        assert any(x.startswith("UBLKCP") for x in o), name                      # cp.async.bulk
+        assert any(x.startswith("SYNCS.ARRIVE.TRANS64") for x in o), name        # mbarrier expect_tx
+        assert any(x.startswith("SYNCS.PHASECHK.TRANS64.TRYWAIT") for x in o), name
+        assert any(x.startswith("LDS.128") or x.startswith("LDS.U.128") or x == "LDS.128" for x in o), name
+
+
+def test_iteration_kernels_carry_programmatic_dependent_launch(sass):
+    # everything cg_kernels.cu / cg_symv.cu launch through cgk_launch (the attribute is only legal on
+    # kernels that order themselves with griddepcontrol.wait)
+    for name in ("xr_update_kernel<false>", "p_update_kernel<false>", "cg2_step_one_kernel", "cg2_step_kernel<true>",
+                 "gemv_ldg_keep_kernel<4,1,128,4>", "gemv_ldg_comm_kernel<4,2,256,4>", "symv_tile_kernel<4>",
+                 "symv_finish_kernel", "symv_push_kernel"):
+        o = ops(sass[name])
+        assert "ACQBULK" in o, name        # griddepcontrol.wait
+        assert "PREEXIT" in o, name        # griddepcontrol.launch_dependents
+        assert o.index("ACQBULK") < o.index("PREEXIT"), name     # wait first: completion stays transitive (cg_device.cuh)
+    # the bandwidth-bound GEMV of large systems is launched the ordinary way and carries neither
+    o = ops(sass["gemv_ldg_kernel<8,2,512,4>"])
+    assert "ACQBULK" not in o and "PREEXIT" not in o
+
+
+def test_no_fp64_atomics_and_no_tensor_cores(sass):
+    for name, body in sass.items():
+        for x in ops(body):
+            assert not re.match(r"(ATOM|ATOMG|ATOMS|RED)\..*F64", x), (name, x)
+            assert not re.match(r"(HMMA|DMMA|IMMA|QMMA|UTCHMMA|UTCQMMA|UTCIMMA|HGMMA)", x), (name, x)
+
+
+def test_peer_exchange_uses_system_scope_accesses(sass):
+    # the kernels that push into peer windows fence at system scope, the consumers poll with sys loads
+    assert any(x == "MEMBAR.SC.SYS" for x in ops(sass["p_update_kernel<true>"]))
+    for name in ("xr_update_kernel<true>", "p_update_kernel<true>", "gemv_ldg_comm_kernel<4,2,256,4>"):
+        assert any(x.endswith("STRONG.SYS") and x.startswith("LDG") for x in ops(sass[name])), name
+    # ... and the one-rank forms pay no system-scope fence
+    for name in ("xr_update_kernel<false>", "p_update_kernel<false>", "gemv_ldg_kernel<8,2,512,4>", "cg2_step_one_kernel"):
+        assert "MEMBAR.SC.SYS" not in ops(sass[name]), name
