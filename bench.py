@@ -93,6 +93,12 @@ def ncu_traffic(n, world):
         return None, None
 
 
+def workload_name(n):
+    """BASELINE.json names four synthetic sizes; anything else is an off-list size asked for with --matrix-n."""
+    idx = {4096: 1, 16384: 2, 65536: 3, 131072: 4}.get(n)
+    return f"seeded synthetic SPD n={n} FP64, fixed-iteration CG ({'configs[%d]' % idx if idx else 'off-list size'})"
+
+
 def gemv_bytes(m, n):
     """Algorithmic bytes of one row-block GEMV launch: A once, p once, Ap once."""
     return 8.0 * (m * n + n + m)
@@ -181,6 +187,18 @@ def run_cpu_port(n, iters, threads, warmup=0):
     return st["iterations"] / st["loop_seconds"], st
 
 
+REFERENCE_BUDGET_S = 150.0
+
+
+def reference_iterations(n, threads, steps, gbs_per_thread=5.0):
+    """Iterations the CPU arm runs for --steps K: K itself unless streaming 8 n^2 bytes K times
+    through `threads` cores (a conservative 5 GB/s each; measured 6.9-7.3 on the bench box)
+    would exceed REFERENCE_BUDGET_S -- then the largest count that fits (at least 3)."""
+    per_iter = 8.0 * n * n / (threads * gbs_per_thread * 1e9)
+    cap = max(3, int(REFERENCE_BUDGET_S / max(per_iter, 1e-9)))
+    return min(steps, cap)
+
+
 def reference_arm(args):
     """--impl reference: the reference's CPU implementation of the path on this box's host
     cores, same metric/config.  Rank 0 only; other ranks exit 0 without work."""
@@ -188,19 +206,21 @@ def reference_arm(args):
         return 0
     n = args.n
     threads, cores = cpu_threads_for(n, args.cpu_threads)
-    # bounded: every step streams 8*n*n bytes per iteration through the host cores
-    iters = max(1, args.steps)
+    # bounded: every step streams 8*n*n bytes through the host cores (~0.3 s at n = 65536 on 16
+    # threads), so a very large --steps is cut to what fits REFERENCE_BUDGET_S and reported as such
     t0 = time.time()
+    iters, asked = reference_iterations(n, threads, max(1, args.steps)), max(1, args.steps)
     val, st = run_cpu_port(n, iters, threads, warmup=min(args.warmup, 1))
     m = n // threads
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": iters, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 / val, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"seeded synthetic SPD n={n} FP64, fixed-iteration CG (configs[3])", "n": n,
+        "config": {"workload": workload_name(n), "n": n,
                    "seed": SEED, "parallelism": f"{threads} host threads, row-block SPMD (parallel_cg.c)"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"full n={n} matrix ({8.0 * n * n / 1e9:.1f} GB), {iters} iterations, "
+                         "sample": f"full n={n} matrix ({8.0 * n * n / 1e9:.1f} GB), {iters} iterations"
+                                   + (f" (of the {asked} asked for: bounded to ~{REFERENCE_BUDGET_S:.0f} s of CPU work)" if iters < asked else "") + ", "
                                    f"{threads} of {cores} host cores; port because the reference's int "
                                    "indexing overflows above n=46340 (serialConjugate.c:78,117); the port is "
                                    "bit-identical to oracle/_ref at n<=2048 (tests/test_oracle.py)",
@@ -331,7 +351,7 @@ def b200_arm(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": loop_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"seeded synthetic SPD n={n} FP64, fixed-iteration CG (configs[3])", "n": n,
+        "config": {"workload": workload_name(n), "n": n,
                    "seed": SEED, "rows_per_gpu": m, "parallelism": f"row-block x{world}" if world > 1 else "single GPU",
                    "exchange": {0: "none (one rank)", 1: "nccl all-gather + 2 all-reduce per iteration",
                                 2: "fused peer-memory pushes over NVLink inside the solver kernels"}[st["comm"]],
