@@ -66,6 +66,23 @@ def main():
         ranks = [1, 2, 4, 8]
         gold["cases"][tag] = {"n": n, "seed": SEED, "flags": 0, "ranks": ranks,
                               "x": ref_all(A, b, x0, ranks)}
+    # --- long runs (SURVEY.md 8f-2 family, cond ~ 2^k): hundreds of iterations of the REAL reference pin the
+    #     recurrence itself (alpha, beta/rho, the stale-p exit), not just its first steps.
+    #     g5: FP64 stops after ~500 iterations, FP32 never meets the test and runs into the loop bound k < ROWS
+    #     (serialConjugate.c:211); g6: non-zero initial guess, so A*x0 matters (serialConjugate.c:209-210)
+    for tag, n, k, ranks, x0_seed in (("g5", 512, 12, [1, 2, 4, 8], None), ("g6", 2048, 7, [1, 8], SEED + 1)):
+        flags = O.GEN_KAPPA_LOG2(k)
+        A = O.gen_A(n, SEED, flags); b = O.gen_b(n, SEED, flags)
+        x0 = np.zeros(n) if x0_seed is None else O.gen_b(n, x0_seed)
+        c = {"n": n, "seed": SEED, "flags": flags, "ranks": ranks, "x": ref_all(A, b, x0, ranks)}
+        if x0_seed is not None:
+            c["x0_seed"] = x0_seed
+        gold["cases"][tag] = c
+    # --- no breakdown guard (parallel_cg.c:298,318): x0 already exact -> rho = 0 -> alpha = 0/0; the reference
+    #     carries NaNs to the loop bound.  NaN payload/sign is not portable through float.hex(): "nan" marks them.
+    A = np.array([[4.0, 1, 0, 0], [1, 4, 1, 0], [0, 1, 4, 1], [0, 0, 1, 4]]); x0 = np.array([1.0, 2, 3, 4]); b = A @ x0
+    gold["cases"]["g7"] = {"n": 4, "A": hexes(A.ravel()), "b": hexes(b), "x0": hexes(x0), "ranks": [1, 2, 4],
+                           "x": ref_all(A, b, x0, [1, 2, 4])}
     # --- generator known answers (pins the CPU twin; the GPU generator is
     #     compared with the twin bit for bit in the gpu tests)
     ks = [0, 1, 2, 3, 1000, 2**31, 2**40 + 12345]
