@@ -223,7 +223,7 @@ def reference_arm(args):
                                    + (f" (of the {asked} asked for: bounded to ~{REFERENCE_BUDGET_S:.0f} s of CPU work)" if iters < asked else "") + ", "
                                    f"{threads} of {cores} host cores; port because the reference's int "
                                    "indexing overflows above n=46340 (serialConjugate.c:78,117); the port is "
-                                   "bit-identical to oracle/_ref at n<=2048 (tests/test_oracle.py)",
+                                   "bit-identical to oracle/_ref at n<=16384 (tests/test_oracle.py)",
                          "gemv_gbs_per_rank": gemv_bytes(m, n) * val / 1e9,
                          "gen_seconds": st["gen_seconds"]},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

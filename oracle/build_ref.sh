@@ -16,12 +16,12 @@
 #   parallel_<p>_n<N>          the MPI program linked against oracle/mpi_shim
 #   libparallel_<p>_n<N>.so    its conjugrad(A,b,x,m,rank,np) + the shim
 # Flags: gcc -O2 (no -march: no FMA contraction, matching a stock x86-64 build).
-# Usage: oracle/build_ref.sh [n ...]      default: 2 4 512 2048
+# Usage: oracle/build_ref.sh [n ...]      default: 2 4 512 2048 16384
 set -euo pipefail
 here="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
 ref="${CG_REFERENCE_DIR:-/root/reference}"
 out="$here/_ref"
-sizes=("$@"); [ ${#sizes[@]} -eq 0 ] && sizes=(2 4 512 2048)
+sizes=("$@"); [ ${#sizes[@]} -eq 0 ] && sizes=(2 4 512 2048 16384)
 if [ ! -f "$ref/serialConjugate.c" ] || [ ! -f "$ref/parallel_cg.c" ]; then
   echo "build_ref: $ref not present; keeping prebuilt oracle/_ref as is" >&2
   exit 0

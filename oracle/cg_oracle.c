@@ -10,8 +10,11 @@
  *     initialguess.txt -> x = (2/3, 1/3); matrixA1.txt/vectorb1.txt/X0.txt ->
  *     x = (-1, 1, -1, 1)), committed under tests/golden/;
  *   - bit for bit against the real reference sources compiled into oracle/_ref
- *     (oracle/build_ref.sh) at n in {2, 4, 512, 2048}, FP32 as shipped and the
- *     mechanical float->double build, serial and MPI (through oracle/mpi_shim).
+ *     (oracle/build_ref.sh) at n in {2, 4, 512, 2048, 16384}, FP32 as shipped and the
+ *     mechanical float->double build, serial and MPI (through oracle/mpi_shim);
+ *   - against golden vectors the real reference produced on long runs (cond ~ 2^7
+ *     and 2^12: 149 and 506 iterations, FP32 leaving through the loop bound) and
+ *     on the rho = 0 breakdown (NaNs to the loop bound), tests/golden/golden.json.
  *
  * Build: see oracle/Makefile (gcc -O2 -ffp-contract=off, no -march).
  */
