@@ -20,9 +20,12 @@ matrices converge in ~5 iterations.
            init, K iterations, download of x -- wall clock, max over ranks.
   cpu_baseline / --impl reference
            the reference's row-block MPI algorithm (parallel_cg.c:248-345) on the
-           host cores: oracle/_ref (the real source over the MPI shim) when it
-           was built for this n, else the 64-bit-index port in oracle/ (the
-           reference's `int` indexing cannot address n > 46340).
+           host cores, as the 64-bit-index port in oracle/ (kind "port"): the real
+           source's `int` indexing cannot address n > 46340, and it can only run
+           to convergence (~4 iterations, A*x0 and its mallocs inside its timer),
+           not K fixed iterations.  The port is bit-identical to the real build
+           up to n = 16384 (tests/test_oracle.py); the real binaries of oracle/_ref
+           are timed beside it in tools/cpu_vs_gpu_table.py (profiles/r01_cpu_vs_gpu.md).
   graph_replay, symmetric_variant, fused_reductions_variant
            the same K iterations replayed from the captured CUDA graph (what a
            converging solve runs), and the two opt-in variants of SURVEY.md 8f-4
