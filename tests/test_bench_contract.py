@@ -89,3 +89,77 @@ def test_clock_sample_parser(tmp_path):
     lo = bench.ClockSampler._ts("2026/11/04 10:00:01.000")
     out = s.stop(lo, lo + 0.05)
     assert out == {"sm_mhz": 1965.0, "sm_max_mhz": 1965.0, "reasons": ["sw_power_cap"], "samples": 3}
+
+
+def test_numa_local_binds_and_restores(tmp_path):
+    assert bench.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert bench.parse_cpulist("") == set() and bench.parse_cpulist("a-b") == set()
+    before = os.sched_getaffinity(0)
+    dev = tmp_path / "0000:1b:00.0"
+    dev.mkdir()
+    first = min(before)
+    (dev / "local_cpulist").write_text(f"{first}\n")
+    with bench.NumaLocal(0, 0x1b, 0, sysfs=str(tmp_path)) as nl:
+        if len(before) > 1:
+            assert os.sched_getaffinity(0) == {first} and nl.bound == 1
+        else:
+            assert nl.bound == 0                                   # nothing narrower to bind to
+    assert os.sched_getaffinity(0) == before
+    # no sysfs entry, or a CPU list outside the container's cpuset: the process is left alone
+    with bench.NumaLocal(0, 0x99, 0, sysfs=str(tmp_path)) as nl:
+        assert nl.bound == 0 and os.sched_getaffinity(0) == before
+    (dev / "local_cpulist").write_text("100000-100003\n")
+    with bench.NumaLocal(0, 0x1b, 0, sysfs=str(tmp_path)) as nl:
+        assert nl.bound == 0 and os.sched_getaffinity(0) == before
+    assert os.sched_getaffinity(0) == before
+
+
+def test_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
+    """Executes every line of bench.e2e_leg on this GPU-less machine: the library is replaced by a stub
+    that records the calls (no arithmetic happens, nothing here is a parity claim) -- a typo in the leg
+    that produces the headline `e2e` object would otherwise only show on the GPU box."""
+    import ctypes as C
+    import types
+    import torch
+    from conjugate_gradient_b200 import _binding as B
+
+    calls = []
+
+    class StubLib:
+        def cgb_debug_read(self, h, what, off, count, dst):
+            calls.append(("read", what, count)); return 0
+
+        def cgb_conjugrad_rank(self, h, A, b, x, m, o, st):
+            opt = C.cast(o, C.POINTER(B.Options)).contents
+            s = C.cast(st, C.POINTER(B.Stats)).contents
+            s.iterations = opt.max_iter if opt.ignore_stop else 4
+            s.h2d_seconds, s.solve_seconds, s.h2d_bytes = 0.5, 0.1, 8 * (m * 64) // (2 if opt.symmetric == 2 else 1)
+            calls.append(("solve", int(opt.symmetric), int(opt.ignore_stop)))
+            return 0
+
+        def cgb_default_options(self, o):
+            return None
+
+    real_empty, real_zeros = torch.empty, torch.zeros
+    monkeypatch.setattr(torch, "empty", lambda *a, pin_memory=False, **k: real_empty(*a, **k))
+    monkeypatch.setattr(torch, "zeros", lambda *a, pin_memory=False, **k: real_zeros(*a, **k))
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
+    monkeypatch.setattr(torch.cuda, "get_device_properties",
+                        lambda i: types.SimpleNamespace(pci_domain_id=0, pci_bus_id=0x1b, pci_device_id=0))
+    monkeypatch.setattr(B, "lib", lambda: StubLib())
+    before = os.sched_getaffinity(0)
+    n = m = 64
+    K = 20
+    line = {"symmetric_variant": {}, "time_to_solution": {}}
+    env = (0, 1, 0, n, m, K, lambda: None, float, {}, None)
+    bench.e2e_leg(types.SimpleNamespace(_h=None), line, env)
+    e = line["e2e"]
+    assert e["unit"] == bench.UNIT and e["value"] > 0 and e["iterations"] == K
+    assert e["h2d_bytes_per_step"] == 8.0 * (m * n + m + n) / K and e["d2h_bytes_per_step"] == 8.0 * n / K
+    assert "host_buffers" in e and "api" in e
+    assert line["symmetric_variant"]["e2e"]["value"] > 0
+    assert line["time_to_solution"]["e2e_iterations"] == 4
+    # A and b read back once; two plain calls, two asserted-symmetric calls, one converging solve
+    assert [c for c in calls if c[0] == "read"] == [("read", 0, m * n), ("read", 1, m)]
+    assert [c[1:] for c in calls if c[0] == "solve"] == [(0, 1), (0, 1), (2, 1), (2, 1), (0, 0)]
+    assert os.sched_getaffinity(0) == before
