@@ -163,3 +163,59 @@ def test_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
     assert [c for c in calls if c[0] == "read"] == [("read", 0, m * n), ("read", 1, m)]
     assert [c[1:] for c in calls if c[0] == "solve"] == [(0, 1), (0, 1), (2, 1), (2, 1), (0, 0)]
     assert os.sched_getaffinity(0) == before
+
+
+def test_b200_arm_line_against_a_stub_context(monkeypatch):
+    """The same for the device-resident leg: bench.b200_arm assembled on a stub Context (fixed timings, no
+    arithmetic) must produce every key of the driver's contract with the stated meaning."""
+    import types
+    import torch
+    import conjugate_gradient_b200 as cg
+
+    class StubCtx:
+        def __init__(self, **kw):
+            self.solves = []
+
+        def device_info(self):
+            return {"name": "stub"}
+
+        def generate(self, n, seed):
+            self.n = n
+
+        def set_x0(self, x):
+            pass
+
+        def close(self):
+            pass
+
+        def solve(self, **kw):
+            self.solves.append(kw)
+            K = kw.get("max_iter", 4)
+            return {"loop_ms": 5.0 * K, "gemv_ms_avg": 4.5, "gemv_ms_min": 4.4, "gemv_timed": K, "kernel_launches": 3 * K + 4,
+                    "comm": 0, "pdl": 1, "graph_chunk": 2, "solve_seconds": 0.02, "iterations": K, "final_residual": 1e-8,
+                    "gemv_bytes": 1.0e9, "gemv_variant": 1, "gemv_rows": 8, "gemv_unroll": 2, "gemv_threads": 512, "gemv_vec": 4,
+                    "gemv_stages": 0, "gemv_tile_cols": 0, "gemv_grid": 8192}
+
+    monkeypatch.setattr(cg, "Context", StubCtx)
+    monkeypatch.setattr(cg, "device_count", lambda: 1)
+    monkeypatch.setattr(torch.cuda, "set_device", lambda i: None)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
+    monkeypatch.setattr(bench, "ClockSampler", lambda i: types.SimpleNamespace(
+        stop=lambda lo, hi: {"sm_mhz": 1965.0, "sm_max_mhz": 1965.0, "reasons": [], "samples": 5}))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    args = types.SimpleNamespace(gpus=1, steps=20, warmup=3, n=65536, gemv=0, comm="auto", rows=0, unroll=0, threads=0, l2_keep=0)
+    ctx, line, env = bench.b200_arm(args)
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+              "dtype", "data", "config", "roofline", "clocks", "gpu_launches"):
+        assert k in line, k
+    assert line["value"] == pytest.approx(20 / 0.1) and line["ms_per_step"] == pytest.approx(5.0)
+    assert line["steps"] == 20 and line["warmup"] == 3 and line["n_gpus"] == 1 and line["dtype"] == "f64"
+    assert "configs[3]" in line["config"]["workload"] and "model" not in line["config"]
+    r = line["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and r["bytes_per_launch"] == bench.gemv_bytes(65536, 65536)
+    assert r["achieved"] == pytest.approx(r["bytes_per_launch"] / 4.5e-3 / 1e9) and r["frac"] == pytest.approx(r["achieved"] / r["peak"])
+    assert line["gpu_launches"] == 3 * 20                     # the 4 set-up launches are outside the K iterations
+    assert ctx.solves[0]["max_iter"] == 3 and ctx.solves[1]["max_iter"] == 20 and ctx.solves[1]["time_gemv"] == 1
+    assert "symmetric_variant" in line and "fused_reductions_variant" in line
+    json.dumps(line)                                         # serialisable as ONE line
