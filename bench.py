@@ -412,6 +412,8 @@ class NumaLocal:
         self.bound = 0
 
     def __enter__(self):
+        if os.environ.get("CGB_BENCH_NUMA", "1") == "0":          # A/B switch: default placement
+            return self
         try:
             with open(self.path) as f:
                 local = parse_cpulist(f.read())
