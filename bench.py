@@ -517,7 +517,7 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu:
         # reported baseline, not the target: the reference's SPMD algorithm on the host cores
         threads, cores = cpu_threads_for(args.n, args.cpu_threads)
-        iters = 3
+        iters = min(10, reference_iterations(args.n, threads, 10))      # ~3 s of wall at n = 65536 on 16 threads
         val, st = run_cpu_port(args.n, iters, threads)
         line["cpu_baseline"] = {
             "value": val, "unit": UNIT, "cores": threads, "kind": "port",
