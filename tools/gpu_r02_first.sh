@@ -20,3 +20,14 @@ else
   done
   lscpu | grep -i "numa\|socket\|model name"; nvidia-smi topo -m | head -20
 fi
+# 4. G = 1 only: ncu capture of the per-GPU slice shape of the 8-GPU headline run (8192 x 65536)
+if [ "$G" -eq 1 ]; then
+  timeout 600 python tools/gemv_slice.py && \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemv_ldg -c 2 -f -o gpurun_out/r02_slice_8192x65536 python tools/gemv_slice.py > gpurun_out/r02_slice_ncu.log 2>&1
+  ncu -i gpurun_out/r02_slice_8192x65536.ncu-rep --page raw --csv 2>/dev/null | python -c "
+import csv,sys
+rows=list(csv.reader(sys.stdin)); h=rows[0]
+for k in ('gpu__time_duration.sum','dram__bytes_read.sum','dram__bytes_write.sum','gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'):
+    if k in h: print(k, [r[h.index(k)] for r in rows[2:]])
+" | tee gpurun_out/r02_slice_summary.txt
+fi
