@@ -108,9 +108,19 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         }
         else if (!strcmp(a, "--max-iter")) { long long k; if (parse_ll(a, v, 1, &k)) return -1; c->max_iter = k; ++i; }
         else if (!strcmp(a, "--gen")) { long long k; if (parse_ll(a, v, 1, &k)) return -1; c->gen_n = k; ++i; }
-        else if (!strcmp(a, "--seed")) { c->seed = strtoull(v, NULL, 10); ++i; }
+        else if (!strcmp(a, "--seed")) {
+            char *end = NULL;
+            c->seed = strtoull(v, &end, 10);
+            if (end == v || *end != '\0' || *v == '-') { fprintf(stderr, "option --seed takes an unsigned integer (got \"%s\")\n", v); return -1; }
+            ++i;
+        }
         else if (!strcmp(a, "--bench-iters")) { long long k; if (parse_ll(a, v, 1, &k)) return -1; c->bench_iters = k; ++i; }
-        else if (!strcmp(a, "--gemv")) { c->gemv = atoi(v); ++i; }
+        else if (!strcmp(a, "--gemv")) {
+            long long k = 0;
+            if (parse_ll(a, v, 0, &k)) return -1;
+            if (k > 2) { fprintf(stderr, "option --gemv takes 0 (default), 1 (streaming loads) or 2 (bulk-async copies)\n"); return -1; }
+            c->gemv = (int)k; ++i;
+        }
         else if (!strcmp(a, "--cg")) {
             if (!strcmp(v, "classic")) c->cg_variant = CGB_CG_CLASSIC;
             else if (!strcmp(v, "fused")) c->cg_variant = CGB_CG_FUSED_REDUCTIONS;
@@ -133,7 +143,10 @@ static int parse_cli(int argc, char **argv, cli_t *c)
         else { fprintf(stderr, "unknown option %s\n", a); return -1; }
     }
     c->fileA = pos[0]; c->fileB = pos[1]; c->fileX = pos[2];
-    if (c->gen_n > 0) return npos == 0 ? 0 : -1;
+    if (c->gen_n > 0) {
+        if (npos != 0) { fprintf(stderr, "--gen N solves a generated system: it takes no input files (got %d)\n", npos); return -1; }
+        return 0;
+    }
     return npos == 3 ? 0 : -2;
 }
 

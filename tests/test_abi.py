@@ -89,6 +89,11 @@ def test_cli_messages_without_gpu(golden_dir):
     (["--comm", "mpi"], "--comm takes nccl, peer or auto"),
     (["--no-such-flag", "1"], "unknown option"),
     (["--dims"], "needs a value"),
+    (["--seed", "12x"], "--seed takes an unsigned integer"),
+    (["--seed", "-5"], "--seed takes an unsigned integer"),
+    (["--gemv", "7"], "--gemv takes 0"),
+    (["--gemv", "bulk"], "--gemv takes an integer"),
+    (["--gen", "64"], "takes no input files"),                  # was a silent exit 2
 ])
 def test_cli_usage_errors(golden_dir, args, msg):
     files = [os.path.join(golden_dir, f) for f in ("g2_matrixA.txt", "g2_vectorb.txt", "g2_x0.txt")]
