@@ -81,6 +81,31 @@ def build(force=False):
 _lib = None
 
 
+def _share_nccl_with_torch():
+    """libcgb200.so links `libnccl.so.2`; PyTorch wheels bundle their own, usually newer, library under
+    the same soname (site-packages/nvidia/nccl/lib) and need its symbols.  A process can hold only one
+    `libnccl.so.2`, and the first one loaded serves everybody: with the system copy loaded first, a later
+    `import torch` fails on an undefined NCCL symbol.  So when no NCCL is mapped yet and the bundled copy
+    exists, load that one first -- it is the copy `bench.py` (which imports torch first) has always run on.
+    CGB_NCCL_PRELOAD=0 keeps the system library.  Returns the path loaded, or None."""
+    if os.environ.get("CGB_NCCL_PRELOAD", "1") == "0":
+        return None
+    try:
+        with open("/proc/self/maps") as f:
+            if "libnccl.so" in f.read():
+                return None
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+                return cand
+    except (OSError, ImportError, ValueError, AttributeError):
+        pass
+    return None
+
+
 def lib():
     global _lib
     if _lib is not None:
@@ -88,6 +113,7 @@ def lib():
     if not os.path.exists(LIB_PATH):
         raise ImportError(f"{LIB_PATH} is missing: run `make -C conjugate_gradient_b200/csrc` "
                           "(or __graft_entry__.build()); there is no fallback implementation")
+    _share_nccl_with_torch()
     L = C.CDLL(LIB_PATH)
     dp, i64, u64, vp = C.POINTER(C.c_double), C.c_int64, C.c_uint64, C.c_void_p
     op, sp = C.POINTER(Options), C.POINTER(Stats)

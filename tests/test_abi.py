@@ -162,3 +162,22 @@ def test_invalid_arguments_are_status_codes_not_crashes(golden_dir):
     assert L.cgb_write_values(b"/nonexistent_dir/x.txt", x.ctypes.data, 2, 4) == IO
     assert L.cgb_count_values(None) == -1
     assert L.cgb_shutdown() == 0 and L.cgb_release_rank() == 0
+
+
+def test_torch_imports_after_the_library_is_loaded():
+    # libcgb200.so and torch both want a `libnccl.so.2`; a process holds one.  Loading the library first must
+    # not break a later `import torch` (the binding maps torch's bundled copy when there is one), and the
+    # reverse order -- bench.py's -- must keep working; CGB_NCCL_PRELOAD=0 opts out.
+    import sys
+    code = ("import conjugate_gradient_b200 as cg; L = cg.lib(); import torch; "
+            "print('ok', L.cgb_version(), sum('libnccl' in l for l in open('/proc/self/maps')) > 0)")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=B.ROOT, timeout=600)
+    assert r.returncode == 0 and "ok 100 True" in r.stdout, r.stderr[-2000:]
+    code = ("import torch; import conjugate_gradient_b200 as cg; L = cg.lib(); "
+            "print('ok', L.cgb_version(), len({l.split()[-1] for l in open('/proc/self/maps') if 'libnccl' in l}))")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=B.ROOT, timeout=600)
+    assert r.returncode == 0 and "ok 100 1" in r.stdout, r.stderr[-2000:]          # ONE copy of NCCL mapped
+    code = "import conjugate_gradient_b200 as cg; cg.lib(); print([l.split()[-1] for l in open('/proc/self/maps') if 'libnccl' in l][0])"
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=B.ROOT, timeout=600,
+                       env=dict(os.environ, CGB_NCCL_PRELOAD="0"))
+    assert r.returncode == 0 and "site-packages" not in r.stdout, r.stdout + r.stderr[-1000:]

@@ -114,7 +114,22 @@ def test_numa_local_binds_and_restores(tmp_path):
     assert os.sched_getaffinity(0) == before
 
 
-def test_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
+# The two stub tests below patch torch and the binding; they run in a fresh interpreter so that nothing they
+# replace can leak into other test modules (and so that they do not depend on which NCCL copy earlier modules
+# of a full run have mapped -- see _binding._share_nccl_with_torch and tests/test_abi.py).
+IN_CHILD = os.environ.get("CGB_STUB_CHILD") == "1"
+
+
+def test_fresh_interpreter_runs_both_legs_on_stubs():
+    if IN_CHILD:
+        pytest.skip("already the child")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-p", "no:cacheprovider", os.path.abspath(__file__), "-k", "stub_"],
+                       capture_output=True, text=True, timeout=600, env=dict(os.environ, CGB_STUB_CHILD="1"), cwd=ROOT)
+    assert r.returncode == 0 and "2 passed" in r.stdout, r.stdout[-3000:] + r.stderr[-1000:]
+
+
+@pytest.mark.skipif(not IN_CHILD, reason="runs inside test_fresh_interpreter_runs_both_legs_on_stubs")
+def test_stub_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
     """Executes every line of bench.e2e_leg on this GPU-less machine: the library is replaced by a stub
     that records the calls (no arithmetic happens, nothing here is a parity claim) -- a typo in the leg
     that produces the headline `e2e` object would otherwise only show on the GPU box."""
@@ -165,7 +180,8 @@ def test_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
     assert os.sched_getaffinity(0) == before
 
 
-def test_b200_arm_line_against_a_stub_context(monkeypatch):
+@pytest.mark.skipif(not IN_CHILD, reason="runs inside test_fresh_interpreter_runs_both_legs_on_stubs")
+def test_stub_b200_arm_line_against_a_stub_context(monkeypatch):
     """The same for the device-resident leg: bench.b200_arm assembled on a stub Context (fixed timings, no
     arithmetic) must produce every key of the driver's contract with the stated meaning."""
     import types
