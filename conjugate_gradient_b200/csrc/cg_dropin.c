@@ -417,6 +417,12 @@ void conjugrad_mpi(double *local_matrixA, double *local_vectorB, double *local_v
         if (rc == CGB_OK) rc = cgb_create_rank(&tl_rank_ctx, dev, myrank, procsnum, id);
         if (rc != CGB_OK) { fprintf(stderr, "conjugrad_mpi: %s\n", cgb_last_error()); tl_rank_ctx = NULL; return; }
         tl_rank = myrank; tl_np = procsnum;
+        if (myrank == 0 && procsnum > 1) {
+            /* ncclCommInitRank is collective: once it has returned here every rank has read the id,
+             * so the rendezvous file can go -- a later run never meets a stale one */
+            const char *path = getenv("CGB_ID_FILE");
+            if (path && *path) (void)unlink(path);
+        }
     }
     int rc = cgb_conjugrad_rank(tl_rank_ctx, local_matrixA, local_vectorB, local_vectorX,
                                 local_row, NULL, &tl_stats);

@@ -1,0 +1,99 @@
+"""The drop-in boundary exactly as a maintainer of the reference would use it (INTEGRATION.md sections 1-2):
+C programs shaped like the reference's own mains (tests/csrc/serial_dropin.c, spmd_dropin.c) own the host
+buffers, read the three text files and make the reference's calls
+
+    conjugrad(matrixA, vectorB, vectorX)                                        serialConjugate.c:40,68
+    conjugrad(local_A, local_b, local_x, local_row, myrank, procsnum)           parallel_cg.c:46-48,118
+
+against libcgb200.so.  Results are compared with the golden vectors of the REAL reference.  The link step and
+the no-GPU behaviour are CPU tests; the solves need a B200."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import _oracle as O
+from conftest import unhex
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIBDIR = os.path.join(ROOT, "conjugate_gradient_b200", "lib")
+RTOL_X = 1.0e-10
+
+
+@pytest.fixture(scope="module")
+def callers(tmp_path_factory):
+    import shutil
+    cc = shutil.which("gcc") or shutil.which("cc") or ("/opt/gcc/bin/gcc" if os.path.exists("/opt/gcc/bin/gcc") else None)
+    if cc is None:
+        pytest.skip("no C compiler on this machine")
+    out = tmp_path_factory.mktemp("callers")
+    exes = {}
+    for name, extra in (("serial_dropin", []), ("spmd_dropin", ["-lpthread"])):
+        exe = str(out / name)
+        subprocess.run([cc, "-O2", "-Wall", "-Wextra", "-Werror", os.path.join(ROOT, "tests", "csrc", name + ".c"),
+                        "-I", os.path.join(ROOT, "include"), f"-L{LIBDIR}", "-lcgb200", f"-Wl,-rpath,{LIBDIR}", *extra, "-lm",
+                        "-o", exe], check=True)
+        exes[name] = exe
+    return exes
+
+
+def files_for(case, tmp_path, golden_dir, tag):
+    """the three text inputs of a golden case: the shipped fixtures as committed, generated systems written with
+    %.17g (an exact round trip through "%lf")"""
+    if "A" in case:
+        return [os.path.join(golden_dir, f"{tag}_{nm}.txt") for nm in ("matrixA", "vectorb", "x0")]
+    n = case["n"]
+    A, b = O.gen_A(n, case["seed"], case["flags"]), O.gen_b(n, case["seed"], case["flags"])
+    paths = [str(tmp_path / f"{tag}_{nm}.txt") for nm in ("A", "b", "x0")]
+    np.savetxt(paths[0], A.ravel(), fmt="%.17g"); np.savetxt(paths[1], b, fmt="%.17g"); np.savetxt(paths[2], np.zeros(n), fmt="%.1f")
+    return paths
+
+
+def parse_x(stdout):
+    return np.array([float.fromhex(l.split()[1]) for l in stdout.splitlines() if l.startswith("x ")])
+
+
+def relerr(x, ref):
+    return np.linalg.norm(x - ref) / np.linalg.norm(ref)
+
+
+def test_callers_link_and_fail_loudly_without_a_gpu(callers, golden_dir):
+    import conjugate_gradient_b200 as cg
+    if cg.device_count() > 0:
+        pytest.skip("a GPU is present: covered by the solves below")
+    f = [os.path.join(golden_dir, f"g2_{nm}.txt") for nm in ("matrixA", "vectorb", "x0")]
+    r = subprocess.run([callers["serial_dropin"], "4"] + f, capture_output=True, text=True)
+    assert r.returncode == 5 and "conjugrad:" in r.stderr and "x " not in r.stdout        # no CPU fallback
+    r = subprocess.run([callers["spmd_dropin"], "1", "4"] + f, capture_output=True, text=True)
+    assert r.returncode == 5 and "conjugrad_mpi: no CUDA device" in r.stderr
+    r = subprocess.run([callers["spmd_dropin"], "3", "4"] + f, capture_output=True, text=True)
+    assert r.returncode == 1 and "4 is not divisible by 3" in r.stdout                    # parallel_cg.c:86-90
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["g1", "g2", "g3"])
+def test_serial_caller_matches_the_real_reference(callers, golden, golden_dir, tmp_path, tag):
+    c = golden["cases"][tag]
+    r = subprocess.run([callers["serial_dropin"], str(c["n"])] + files_for(c, tmp_path, golden_dir, tag),
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "average clock execution time in seconds:" in r.stdout                         # serialConjugate.c:249-251
+    x = parse_x(r.stdout)
+    assert x.shape == (c["n"],) and relerr(x, unhex(c["x"]["serial_f64"])) <= RTOL_X
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,ranks", [("g2", 1), ("g3", 1), ("g2", 2), ("g3", 2), ("g2", 4), ("g3", 4), ("g3", 8)])
+def test_spmd_caller_matches_the_real_reference(callers, golden, golden_dir, tmp_path, tag, ranks):
+    import conjugate_gradient_b200 as cg
+    if cg.device_count() < ranks:
+        pytest.skip(f"needs {ranks} GPUs")
+    c = golden["cases"][tag]
+    env = {k: v for k, v in os.environ.items() if k not in ("LOCAL_RANK", "CGB_DEVICE", "CGB_ID_FILE")}
+    r = subprocess.run([callers["spmd_dropin"], str(ranks), str(c["n"])] + files_for(c, tmp_path, golden_dir, tag),
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.count("cg method execution time in seconds:") == 1                    # rank 0 only, parallel_cg.c:331-336
+    x = parse_x(r.stdout)
+    assert x.shape == (c["n"],) and relerr(x, unhex(c["x"][f"spmd{ranks}_f64"])) <= RTOL_X
