@@ -190,12 +190,25 @@ static int io_threads(size_t len)
     return (int)((size_t)nc < by_size ? (size_t)nc : by_size);
 }
 
+/* fn over jobs[0..T): job 0 on the calling thread, the others on their own threads; a thread that
+ * cannot be created (process limits) has its job run here instead, so the result never depends on it. */
+static void run_jobs(void *(*fn)(void *), void *jobs, size_t stride, int T)
+{
+    pthread_t th[IO_MAX_THREADS];
+    char started[IO_MAX_THREADS];
+    for (int t = 1; t < T; ++t) started[t] = pthread_create(&th[t], NULL, fn, (char *)jobs + (size_t)t * stride) == 0;
+    fn(jobs);
+    for (int t = 1; t < T; ++t) {
+        if (started[t]) pthread_join(th[t], NULL);
+        else fn((char *)jobs + (size_t)t * stride);
+    }
+}
+
 /* Returns the number of values, or -1 when the file needs the sequential path. */
 static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t cap)
 {
     const int T = io_threads(len);
     span_job job[IO_MAX_THREADS];
-    pthread_t th[IO_MAX_THREADS];
     const char *end = buf + len, *cut = buf;
     for (int t = 0; t < T; ++t) {
         const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
@@ -205,9 +218,7 @@ static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t 
         job[t].beg = cut; job[t].end = nxt;
         cut = nxt;
     }
-    for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, span_count, &job[t]);
-    span_count(&job[0]);
-    for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+    run_jobs(span_count, job, sizeof job[0], T);
     int64_t total = 0;
     for (int t = 0; t < T; ++t) {
         if (job[t].irregular) return -1;
@@ -216,9 +227,7 @@ static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t 
     }
     if (!dst) return total;
     for (int t = 0; t < T; ++t) { job[t].dst = dst; job[t].cap = cap; }
-    for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, span_parse, &job[t]);
-    span_parse(&job[0]);
-    for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+    run_jobs(span_parse, job, sizeof job[0], T);
     for (int t = 0; t < T; ++t)
         if (job[t].irregular) return -1;
     return total;
@@ -271,7 +280,6 @@ int64_t cgb_text_locate(const cgb_text *tx, int64_t first, int64_t count, size_t
     const size_t len = tx->len;
     const int T = io_threads(len);
     span_job job[IO_MAX_THREADS];
-    pthread_t th[IO_MAX_THREADS];
     const char *end = buf + len, *cut = buf;
     for (int t = 0; t < T; ++t) {
         const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
@@ -281,9 +289,7 @@ int64_t cgb_text_locate(const cgb_text *tx, int64_t first, int64_t count, size_t
         job[t].beg = cut; job[t].end = nxt;
         cut = nxt;
     }
-    for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, span_count, &job[t]);
-    span_count(&job[0]);
-    for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+    run_jobs(span_count, job, sizeof job[0], T);
     int64_t total = 0;
     for (int t = 0; t < T; ++t) {
         if (job[t].irregular) return -1;
@@ -404,15 +410,12 @@ int cgb_write_values_mode(const char *path, const double *v, int64_t count, int 
         const int64_t cnt = count - base < slab ? count - base : slab;
         int T = io_threads((size_t)cnt * 16);
         fmt_job job[IO_MAX_THREADS];
-        pthread_t th[IO_MAX_THREADS];
         for (int t = 0; t < T; ++t) {
             const int64_t lo = cnt * t / T, hi = cnt * (t + 1) / T;
             memset(&job[t], 0, sizeof job[t]);
             job[t].v = v + base + lo; job[t].count = hi - lo; job[t].decimals = fmt_decimals;
         }
-        for (int t = 1; t < T; ++t) pthread_create(&th[t], NULL, fmt_main, &job[t]);
-        fmt_main(&job[0]);
-        for (int t = 1; t < T; ++t) pthread_join(th[t], NULL);
+        run_jobs(fmt_main, job, sizeof job[0], T);
         for (int t = 0; t < T; ++t) {
             if (job[t].fail || (job[t].len && fwrite(job[t].buf, 1, job[t].len, f) != job[t].len)) rc = CGB_ERR_IO;
             free(job[t].buf);

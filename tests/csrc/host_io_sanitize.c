@@ -15,6 +15,18 @@
 #include "../../include/cgb200.h"
 #include "../../conjugate_gradient_b200/csrc/cg_io.h"
 
+#ifdef CGB_TEST_THREADS_FAIL
+/* built with -Dpthread_create=cgb_test_failing_create: every thread creation in cg_io.c is refused, the
+ * jobs must then run on the calling thread with the same results */
+#include <errno.h>
+#include <pthread.h>
+int cgb_test_failing_create(pthread_t *t, const pthread_attr_t *a, void *(*fn)(void *), void *arg)
+{
+    (void)t; (void)a; (void)fn; (void)arg;
+    return EAGAIN;
+}
+#endif
+
 static uint64_t rng_state = 0x9E3779B97F4A7C15ull;
 static uint64_t rnd(void)
 {

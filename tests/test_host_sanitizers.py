@@ -39,6 +39,15 @@ def test_host_text_path_under_asan_ubsan(tmp_path):
     assert "ERROR: AddressSanitizer" not in r.stderr and "runtime error" not in r.stderr and "LeakSanitizer" not in r.stderr
 
 
+def test_host_text_path_when_no_thread_can_be_created(tmp_path):
+    # pthread_create renamed to a stub that always answers EAGAIN: every span / formatter job runs inline
+    exe = build(tmp_path, "io_nothreads", ["-fsanitize=address,undefined", "-fno-sanitize-recover=undefined",
+                                           "-Dpthread_create=cgb_test_failing_create", "-DCGB_TEST_THREADS_FAIL"])
+    r = run(exe, tmp_path, {"ASAN_OPTIONS": "detect_leaks=1"})
+    assert r.returncode == 0 and "host_io_sanitize: ok" in r.stdout, r.stderr[-3000:]
+    assert "AddressSanitizer" not in r.stderr and "runtime error" not in r.stderr
+
+
 def test_host_text_path_under_tsan(tmp_path):
     exe = build(tmp_path, "io_tsan", ["-fsanitize=thread"])
     r = run(exe, tmp_path, {"TSAN_OPTIONS": "halt_on_error=0:exitcode=66"})
