@@ -15,6 +15,7 @@
 #   libserial_<p>_n<N>.so      its conjugrad(A,b,x)      (main renamed away)
 #   parallel_<p>_n<N>          the MPI program linked against oracle/mpi_shim
 #   libparallel_<p>_n<N>.so    its conjugrad(A,b,x,m,rank,np) + the shim
+#   libp2p_<p>_n<N>.so         the same from point-to-point_cg.c (MPI_Send / MPI_Recv through rank 0)
 # Flags: gcc -O2 (no -march: no FMA contraction, matching a stock x86-64 build).
 # Usage: oracle/build_ref.sh [n ...]      default: 2 4 512 2048 16384
 set -euo pipefail
@@ -51,6 +52,12 @@ for n in "${sizes[@]}"; do
     xform "$n" "$p" "$ref/parallel_cg.c" \
       | $CC $CFLAGS -fPIC -shared -Wl,-Bsymbolic -Dmain=ref_main -I"$here/mpi_shim" "$out/mpi_shim.o" -x c - \
           -o "$out/libparallel_${p}_n${n}.so" -lm -lpthread
+    # the point-to-point twin (same conjugrad signature, collectives emulated through rank 0 with MPI_Send / MPI_Recv)
+    if [ -f "$ref/point-to-point_cg.c" ]; then
+      xform "$n" "$p" "$ref/point-to-point_cg.c" \
+        | $CC $CFLAGS -fPIC -shared -Wl,-Bsymbolic -Dmain=ref_main -I"$here/mpi_shim" "$out/mpi_shim.o" -x c - \
+            -o "$out/libp2p_${p}_n${n}.so" -lm -lpthread
+    fi
   done
 done
 echo "build_ref: built reference binaries for n = ${sizes[*]} into $out"

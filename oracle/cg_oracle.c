@@ -11,7 +11,8 @@
  *     x = (-1, 1, -1, 1)), committed under tests/golden/;
  *   - bit for bit against the real reference sources compiled into oracle/_ref
  *     (oracle/build_ref.sh) at n in {2, 4, 512, 2048, 16384}, FP32 as shipped and the
- *     mechanical float->double build, serial and MPI (through oracle/mpi_shim);
+ *     mechanical float->double build, serial and both MPI programs (parallel_cg.c
+ *     and point-to-point_cg.c, through oracle/mpi_shim);
  *   - against golden vectors the real reference produced on long runs (cond ~ 2^7
  *     and 2^12: 149 and 506 iterations, FP32 leaving through the loop bound) and
  *     on the rho = 0 breakdown (NaNs to the loop bound), tests/golden/golden.json.

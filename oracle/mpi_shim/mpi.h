@@ -2,7 +2,8 @@
  *
  * A minimal single-node stand-in for the 11 MPI-1 entry points that the
  * reference's collective CG program uses (parallel_cg.c:76-82,109-117,278-291,
- * 294,313,328-329), so that the UNMODIFIED reference source can be compiled and
+ * 294,313,328-329) and the two more its point-to-point twin needs (MPI_Send,
+ * MPI_Recv), so that the UNMODIFIED reference source can be compiled and
  * run in an image without any MPI implementation (no mpicc / mpi.h / libmpi
  * here or on the GPU box).  Ranks are forked processes, messages go through one
  * anonymous shared mapping, MPI_Allreduce sums in rank order 0..P-1.
@@ -36,6 +37,11 @@ int    MPI_Allreduce(const void *sendbuf, void *recvbuf, int count, MPI_Datatype
                      MPI_Op op, MPI_Comm comm);
 int    MPI_Allgather(const void *sendbuf, int sendcount, MPI_Datatype sdt,
                      void *recvbuf, int recvcount, MPI_Datatype rdt, MPI_Comm comm);
+
+/* point-to-point_cg.c replaces the four collectives above by blocking sends and receives through rank 0
+ * (:183-256, :339-394) */
+int    MPI_Send(const void *buf, int count, MPI_Datatype dt, int dest, int tag, MPI_Comm comm);
+int    MPI_Recv(void *buf, int count, MPI_Datatype dt, int source, int tag, MPI_Comm comm, MPI_Status *status);
 
 /* Test driver hook (not MPI): run `fn(local_A, local_b, local_x, m, rank, np)`
  * -- the reference's SPMD conjugrad signature, parallel_cg.c:46-48 -- on np

@@ -17,11 +17,24 @@
 #include <unistd.h>
 
 #define SHIM_BUF_BYTES ((size_t)64 << 20)
+#define SHIM_MAX_NP 16
+#define SHIM_CHAN_BYTES ((size_t)256 << 10)
+
+/* One channel per ordered (source, destination) pair for MPI_Send / MPI_Recv: a single slot that
+ * the sender fills and the receiver drains, so messages of a pair arrive in the order sent
+ * (MPI's non-overtaking rule); longer messages travel as a sequence of slot-sized pieces. */
+typedef struct {
+    volatile int full;
+    int tag;
+    size_t len;
+    char data[SHIM_CHAN_BYTES];
+} shim_chan;
 
 typedef struct {
     pthread_barrier_t bar;
     int np;
     char pad[64];
+    shim_chan chan[SHIM_MAX_NP][SHIM_MAX_NP];     /* [source][destination]; untouched pages cost nothing */
     char buf[];
 } shim_region;
 
@@ -32,6 +45,7 @@ static pid_t *g_kids = NULL;
 static void shim_setup(int np)
 {
     g_np = np < 1 ? 1 : np;
+    if (g_np > SHIM_MAX_NP) { fprintf(stderr, "mpi_shim: at most %d ranks\n", SHIM_MAX_NP); exit(1); }
     g_shm = mmap(NULL, sizeof(shim_region) + SHIM_BUF_BYTES, PROT_READ | PROT_WRITE,
                  MAP_SHARED | MAP_ANONYMOUS, -1, 0);
     if (g_shm == MAP_FAILED) { perror("mpi_shim mmap"); exit(1); }
@@ -186,6 +200,57 @@ int MPI_Allgather(const void *sendbuf, int sendcount, MPI_Datatype sdt, void *re
             memcpy((char *)recvbuf + (size_t)r * per + off, g_shm->buf + (size_t)r * cap, len);
         bar();
     }
+    return MPI_SUCCESS;
+}
+
+/* Blocking point-to-point, as point-to-point_cg.c uses it (:183-256 distribution, :339-394 the
+ * emulated reduce / gather): the receiver names its source and tag, counts match exactly. */
+#include <sched.h>
+static void shim_wait(volatile int *flag, int until)
+{
+    for (unsigned spins = 0; __atomic_load_n(flag, __ATOMIC_ACQUIRE) != until; ++spins) {
+        if (spins < 2000) continue;
+        if (spins < 4000) { sched_yield(); continue; }
+        struct timespec ts = {0, 20000};
+        nanosleep(&ts, NULL);
+    }
+}
+
+int MPI_Send(const void *buf, int count, MPI_Datatype dt, int dest, int tag, MPI_Comm c)
+{
+    (void)c;
+    if (dest < 0 || dest >= g_np || dest == g_rank) { fprintf(stderr, "mpi_shim: bad destination %d\n", dest); MPI_Abort(0, 1); }
+    shim_chan *ch = &g_shm->chan[g_rank][dest];
+    size_t total = (size_t)count * (size_t)dt, off = 0;
+    do {
+        const size_t len = total - off < SHIM_CHAN_BYTES ? total - off : SHIM_CHAN_BYTES;
+        shim_wait(&ch->full, 0);
+        memcpy(ch->data, (const char *)buf + off, len);
+        ch->tag = tag; ch->len = len;
+        __atomic_store_n(&ch->full, 1, __ATOMIC_RELEASE);
+        off += len;
+    } while (off < total);
+    return MPI_SUCCESS;
+}
+
+int MPI_Recv(void *buf, int count, MPI_Datatype dt, int source, int tag, MPI_Comm c, MPI_Status *status)
+{
+    (void)c;
+    if (source < 0 || source >= g_np || source == g_rank) { fprintf(stderr, "mpi_shim: bad source %d\n", source); MPI_Abort(0, 1); }
+    shim_chan *ch = &g_shm->chan[source][g_rank];
+    size_t total = (size_t)count * (size_t)dt, off = 0;
+    do {
+        shim_wait(&ch->full, 1);
+        if (ch->tag != tag || ch->len > total - off) {
+            fprintf(stderr, "mpi_shim: rank %d expected tag %d (%zu bytes left) from %d, got tag %d (%zu bytes)\n",
+                    g_rank, tag, total - off, source, ch->tag, ch->len);
+            MPI_Abort(0, 1);
+        }
+        memcpy((char *)buf + off, ch->data, ch->len);
+        off += ch->len;
+        __atomic_store_n(&ch->full, 0, __ATOMIC_RELEASE);
+    } while (off < total);
+    if (status) { status->MPI_SOURCE = source; status->MPI_TAG = tag; status->MPI_ERROR = MPI_SUCCESS; }
     return MPI_SUCCESS;
 }
 

@@ -157,9 +157,11 @@ def ref_available(kind, prec, n):
     return os.path.exists(os.path.join(REF_DIR, f"lib{kind}_{prec}_n{n}.so"))
 
 
-def ref_conjugrad(A, b, x0, ranks=None):
+def ref_conjugrad(A, b, x0, ranks=None, program="parallel"):
     """Run the REAL reference's conjugrad() (compiled by oracle/build_ref.sh) on
-    in-memory arrays.  Precision follows A.dtype; n must have been built."""
+    in-memory arrays.  Precision follows A.dtype; n must have been built.
+    ranks=None: serialConjugate.c; ranks=P: parallel_cg.c, or with program="p2p"
+    point-to-point_cg.c (same signature, collectives emulated with sends and receives)."""
     A = np.ascontiguousarray(A); b = np.ascontiguousarray(b)
     n = A.shape[0]
     prec = "f64" if A.dtype == np.float64 else "f32"
@@ -170,7 +172,7 @@ def ref_conjugrad(A, b, x0, ranks=None):
         L.conjugrad.argtypes = [vp, vp, vp]; L.conjugrad.restype = None
         L.conjugrad(A.ctypes.data, b.ctypes.data, x.ctypes.data)
     else:
-        L = C.CDLL(os.path.join(REF_DIR, f"libparallel_{prec}_n{n}.so"))
+        L = C.CDLL(os.path.join(REF_DIR, f"lib{program}_{prec}_n{n}.so"))
         L.cgshim_run_conjugrad.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int]
         L.cgshim_run_conjugrad.restype = C.c_int
         fn = C.cast(L.conjugrad, vp)

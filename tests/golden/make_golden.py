@@ -41,7 +41,11 @@ def ref_all(A, b, x0, ranks_list):
         Ad, bd, xd = A.astype(dt), b.astype(dt), x0.astype(dt)
         out[f"serial_{prec}"] = hexes(O.ref_conjugrad(Ad, bd, xd))
         for P in ranks_list:
-            out[f"spmd{P}_{prec}"] = hexes(O.ref_conjugrad(Ad, bd, xd, ranks=P))
+            xs = O.ref_conjugrad(Ad, bd, xd, ranks=P)
+            out[f"spmd{P}_{prec}"] = hexes(xs)
+            if O.ref_available("p2p", prec, A.shape[0]):      # point-to-point_cg.c: the same bits, not stored twice
+                xp = O.ref_conjugrad(Ad, bd, xd, ranks=P, program="p2p")
+                assert np.array_equal(xs, xp, equal_nan=True), (prec, P)
     return out
 
 

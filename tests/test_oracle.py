@@ -111,6 +111,31 @@ def test_oracle_vs_live_reference(n, ranks, prec):
     assert xs.tobytes() == O.ref_conjugrad(A, b, x0, ranks=ranks).tobytes()
 
 
+@pytest.mark.parametrize("n,ranks,k", [(4, 2, 0), (4, 4, 0), (512, 8, 0), (512, 4, 12), (2048, 8, 7)])
+@pytest.mark.parametrize("prec", ["f64", "f32"])
+def test_point_to_point_program_is_the_same_arithmetic(n, ranks, k, prec):
+    # point-to-point_cg.c:397-504 (SURVEY.md 8a-1's "p2p twin"): the real program over the shim's MPI_Send /
+    # MPI_Recv gives the bits of the collective program and of the oracle -- its emulated reduce adds the
+    # partials in rank order at rank 0 (:339-359) -- up to runs of 512 iterations.  So the SPMD golden vectors
+    # and `conjugrad_mpi` stand for it as well.
+    if not (O.ref_available("p2p", prec, n) and O.ref_available("parallel", prec, n)):
+        pytest.skip("oracle/_ref not built (needs /root/reference; run make -C oracle)")
+    dt = np.float64 if prec == "f64" else np.float32
+    if n == 4:
+        rng = np.random.default_rng(3)
+        R = rng.random((n, n)); A = (0.5 * (R + R.T) + n * np.eye(n)).astype(dt)
+        b = rng.random(n).astype(dt); x0 = rng.random(n).astype(dt)
+    else:
+        f = O.GEN_KAPPA_LOG2(k)
+        A = O.gen_A(n, 5, f).astype(dt); b = O.gen_b(n, 5, f).astype(dt); x0 = np.zeros(n, dt)
+    xp = O.ref_conjugrad(A, b, x0, ranks=ranks, program="p2p")
+    assert xp.tobytes() == O.ref_conjugrad(A, b, x0, ranks=ranks).tobytes()
+    xo, so = O.conjugrad(A, b, x0, ranks=ranks)
+    assert xp.tobytes() == xo.tobytes()
+    if k == 12:
+        assert so["iterations"] > 400
+
+
 def test_threaded_team_equals_sequential_spmd():
     n, seed = 512, 99
     A, b = O.gen_A(n, seed), O.gen_b(n, seed)
