@@ -97,3 +97,44 @@ def test_spmd_caller_matches_the_real_reference(callers, golden, golden_dir, tmp
     assert r.stdout.count("cg method execution time in seconds:") == 1                    # rank 0 only, parallel_cg.c:331-336
     x = parse_x(r.stdout)
     assert x.shape == (c["n"],) and relerr(x, unhex(c["x"][f"spmd{ranks}_f64"])) <= RTOL_X
+
+
+def _masked(stdout):
+    import re
+    return [re.sub(r"\d+\.\d+", "#", l).rstrip() for l in stdout.splitlines()]
+
+
+REF_BIN = os.path.join(ROOT, "oracle", "_ref")
+
+
+def test_real_programs_print_the_lines_the_cli_is_held_to(golden_dir):
+    """CPU side of the stdout contract: what the REAL programs print on the shipped 4 x 4 fixture."""
+    if not os.path.exists(os.path.join(REF_BIN, "serial_f64_n4")):
+        pytest.skip("oracle/_ref not built")
+    f = [os.path.join(golden_dir, f"g2_{nm}.txt") for nm in ("matrixA", "vectorb", "x0")]
+    r = subprocess.run([os.path.join(REF_BIN, "serial_f64_n4")] + f, capture_output=True, text=True, timeout=60)
+    assert _masked(r.stdout) == ["Computing cg of matrix size : 16", "average clock execution time in seconds: #"]
+    r = subprocess.run([os.path.join(REF_BIN, "parallel_f64_n4")] + f, capture_output=True, text=True, timeout=60,
+                       env=dict(os.environ, CGSHIM_NP="2"))
+    assert _masked(r.stdout) == ["Computing cg of matrix size : 16", "cg method execution time in seconds: #",
+                                 "collective data distribution time in seconds: #", "clock execution time in seconds: #"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gpus", [1, 2])
+def test_cli_stdout_equals_the_real_programs_stdout(golden_dir, gpus):
+    """`prog A.txt b.txt x0.txt`: the CLI's stdout is the real program's stdout, line for line, digits of the
+    timings aside -- serialConjugate.c on one GPU, parallel_cg.c (2 ranks over the shim) on two."""
+    import conjugate_gradient_b200 as cg
+    from conjugate_gradient_b200 import _binding as B
+    if cg.device_count() < gpus:
+        pytest.skip(f"needs {gpus} GPUs")
+    ref = os.path.join(REF_BIN, "serial_f64_n4" if gpus == 1 else "parallel_f64_n4")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref did not travel")
+    f = [os.path.join(golden_dir, f"g2_{nm}.txt") for nm in ("matrixA", "vectorb", "x0")]
+    want = subprocess.run([ref] + f, capture_output=True, text=True, timeout=60, env=dict(os.environ, CGSHIM_NP=str(gpus)))
+    got = subprocess.run([B.CLI_PATH] + f + ["--dims", os.path.join(golden_dir, "g2_dimensions.txt"), "--gpus", str(gpus)],
+                         capture_output=True, text=True, timeout=300)
+    assert got.returncode == 0, got.stderr[-2000:]
+    assert _masked(got.stdout) == _masked(want.stdout)
