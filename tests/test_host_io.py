@@ -218,3 +218,53 @@ def test_appending_writer_builds_a_matrix_file_block_by_block(tmp_path):
         blk = np.ascontiguousarray(blk)
         assert L.cgb_write_values_mode(os.fsencode(f), blk.ctypes.data, blk.size, 4, 1 if k else 0) == 0
     assert open(f).read() == "".join("%.4f\n" % a for a in A.ravel())
+
+
+@pytest.mark.parametrize("sep", ["\n", "\r\n", " ", ",", "\t", " \n", ";"])
+@pytest.mark.parametrize("fmt", ["%.4f", "%.1f", "%.17g", "%e"])
+def test_parser_agrees_with_the_real_initialize(tmp_path, sep, fmt):
+    """The REAL reader -- initialize() of serialConjugate.c:85-105 in the float->double build of oracle/_ref
+    (fscanf "%lf%*c", ROWS = 4) -- and cgb_read_values give the same doubles on every separator the reference's
+    "one arbitrary character after each number" rule tolerates."""
+    import ctypes as C
+    import _oracle as O
+    if not O.ref_available("serial", "f64", 4):
+        pytest.skip("oracle/_ref not built")
+    L = C.CDLL(os.path.join(O.REF_DIR, "libserial_f64_n4.so"))
+    L.initialize.argtypes = [C.c_void_p, C.c_char_p, C.c_int]; L.initialize.restype = None
+    rng = np.random.default_rng(len(sep) * 31 + len(fmt))
+    for cols in (1, 4):                                        # a vector and the 4 x 4 matrix
+        vals = (rng.random(4 * cols) - 0.3) * 10.0 ** rng.integers(-3, 6, 4 * cols)
+        path = tmp_path / f"v{cols}.txt"
+        path.write_text(sep.join(fmt % v for v in vals) + sep)
+        ref = np.full(4 * cols, np.nan)
+        L.initialize(ref.ctypes.data, os.fsencode(str(path)), cols)
+        got = cg.read_values(str(path), 4 * cols)
+        assert got.tobytes() == ref.tobytes()
+        assert got.tobytes() == np.array([float(fmt % v) for v in vals]).tobytes()
+
+
+def test_print_format_is_the_real_printers(tmp_path):
+    """printer() of serialConjugate.c:260-276 (disabled at its call site, :252) run from the real build: the CLI's
+    --print-x lines (cgb_print_vector, asserted in tests/test_gpu_parity.py::test_cli_on_shipped_fixture) are its bytes."""
+    import subprocess
+    import sys
+    import _oracle as O
+    if not O.ref_available("serial", "f64", 4):
+        pytest.skip("oracle/_ref not built")
+    code = ("import ctypes as C, numpy as np\n"
+            f"L = C.CDLL({os.path.join(O.REF_DIR, 'libserial_f64_n4.so')!r})\n"
+            "L.printer.argtypes = [C.c_void_p, C.c_int, C.c_int]; L.printer.restype = None\n"
+            "v = np.array([2 / 3, 1 / 3, -1.0, 12345.678901]); L.printer(v.ctypes.data, 4, 1); L.printer(v.ctypes.data, 2, 2)\n"
+            "C.CDLL(None).fflush(None)\n")
+    real = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, check=True).stdout
+    assert real.splitlines()[:2] == ["0.666667  ", "0.333333  "]
+    # the product's formatter on the same data, through a tiny C probe (cg_io.c is plain C)
+    src = tmp_path / "probe.c"
+    src.write_text('#include "cg_io.h"\nint main(void){double v[4]={2.0/3,1.0/3,-1.0,12345.678901};'
+                   'cgb_print_vector(stdout,v,4,1);cgb_print_vector(stdout,v,2,2);return 0;}\n')
+    exe = tmp_path / "probe"
+    csrc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "conjugate_gradient_b200", "csrc")
+    subprocess.run(["gcc", str(src), os.path.join(csrc, "cg_io.c"), "-I", csrc, "-o", str(exe), "-lpthread", "-lm"], check=True)
+    ours = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout
+    assert ours == real
