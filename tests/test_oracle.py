@@ -222,3 +222,30 @@ def test_fused_reductions_oracle_agrees_with_the_pinned_classic_oracle(golden):
     xk, sk = O.cg_fused(A, b, x0, max_iter=2, eps=1e-300)
     xc, _ = O.conjugrad(A, b, x0, max_iter=2, eps=1e-300)
     np.testing.assert_allclose(xk, xc, rtol=1e-12)
+
+
+@pytest.mark.parametrize("n", [4, 512, 2048])
+@pytest.mark.parametrize("prec", ["f64", "f32"])
+def test_building_blocks_against_the_real_functions(n, prec):
+    """matVec / vecVec of the REAL build (serialConjugate.c:109-120,145-155, exported by oracle/_ref's library form)
+    against the oracle's restatements, bit for bit: these two carry all of the path's rounding (strict
+    left-to-right accumulation, the product rounded before each add)."""
+    import ctypes as C
+    import os
+    if not O.ref_available("serial", prec, n):
+        pytest.skip("oracle/_ref not built")
+    dt, ct = (np.float64, C.c_double) if prec == "f64" else (np.float32, C.c_float)
+    L = C.CDLL(os.path.join(O.REF_DIR, f"libserial_{prec}_n{n}.so"))
+    vp = C.c_void_p
+    L.matVec.argtypes = [vp, vp, vp]; L.matVec.restype = None
+    L.vecVec.argtypes = [vp, vp]; L.vecVec.restype = ct
+    rng = np.random.default_rng(n)
+    A = (rng.standard_normal((n, n)) * 10.0 ** rng.integers(-2, 3, (n, n))).astype(dt)
+    v = rng.standard_normal(n).astype(dt); w = rng.standard_normal(n).astype(dt)
+    y = np.full(n, np.nan, dtype=dt)
+    L.matVec(y.ctypes.data, A.ctypes.data, v.ctypes.data)
+    assert y.tobytes() == O.matvec(A, v).tobytes()
+    assert dt(L.vecVec(v.ctypes.data, w.ctypes.data)).tobytes() == dt(O.vecvec(v, w)).tobytes()
+    # ... and these bits are NOT what a fused or pairwise evaluation gives (the test has teeth)
+    if n >= 512:
+        assert y.tobytes() != (A @ v).astype(dt).tobytes()
