@@ -29,6 +29,10 @@ def run(exe, tmp_path, env_extra):
     r = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=600, env=env)
     if r.returncode != 0 and "unexpected memory mapping" in r.stderr:
         pytest.skip("ThreadSanitizer cannot map its shadow memory under this kernel's ASLR settings")
+    if r.returncode != 0 and "LeakSanitizer has encountered a fatal error" in r.stderr:
+        # leak checking needs ptrace, which some sandboxes refuse: keep the address / UB checks
+        env["ASAN_OPTIONS"] = "detect_leaks=0"
+        r = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True, timeout=600, env=env)
     return r
 
 
