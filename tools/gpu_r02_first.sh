@@ -1,6 +1,6 @@
 # usage: bash tools/gpu_r02_first.sh G   (G = 1, or the rank count of a multi-GPU box)
 # First GPU call of the next round: confirms what was added after round 1's last GPU session.
-#   1. full GPU suite (one new case: tests/test_gpu_parity.py::test_long_run_matches_reference_golden)
+#   1. full GPU suite (new since the last GPU session: tests/test_gpu_reference_callers.py -- C callers, stdout contract, long-run golden)
 #   2. default bench, both arms
 #   3. G > 1: e2e upload rate with and without the NUMA-local placement of the pinned host buffers
 #      (bench.py NumaLocal; CGB_BENCH_NUMA=0 is the A/B switch) -- look at e2e.h2d_gbs_per_gpu
