@@ -141,7 +141,7 @@ int cgb_load_text(cgb_ctx *c, int64_t n, const char *fileA, const char *fileB, c
             const size_t len = cend - pos;
             const size_t padded = (len + 15) / 16 * 16;
             if (used[s]) CU(cudaEventSynchronize(ev[s]));         /* its previous upload has left the pinned buffer */
-            memcpy(pin[s], tx.p + pos, len);
+            cgb_parallel_copy(pin[s], tx.p + pos, len);          /* mapped file -> pinned staging buffer */
             memset(pin[s] + len, '\n', padded - len + 64);
             CU(cudaMemcpyAsync(dtxt[s], pin[s], padded + 64, cudaMemcpyHostToDevice, st));
             CU(cudaEventRecord(ev[s], st));

@@ -204,6 +204,30 @@ static void run_jobs(void *(*fn)(void *), void *jobs, size_t stride, int T)
     }
 }
 
+/* memcpy by several threads: one thread moves ~2.5 GB/s out of a freshly mapped file (page faults
+ * included), which was the limit of the GPU text ingest's staging copy (cg_ingest.c). */
+typedef struct { char *dst; const char *src; size_t len; } copy_job;
+static void *copy_main(void *arg)
+{
+    copy_job *j = arg;
+    memcpy(j->dst, j->src, j->len);
+    return NULL;
+}
+void cgb_parallel_copy(void *dst, const void *src, size_t len)
+{
+    int T = io_threads(len);
+    if (T > 8) T = 8;
+    if (T <= 1) { memcpy(dst, src, len); return; }
+    copy_job job[8];
+    const size_t per = (len / (size_t)T + 4095) & ~(size_t)4095;            /* page-sized pieces */
+    int used = 0;
+    for (size_t off = 0; off < len && used < 8; off += per, ++used) {
+        job[used].dst = (char *)dst + off; job[used].src = (const char *)src + off;
+        job[used].len = len - off < per ? len - off : per;
+    }
+    run_jobs(copy_main, job, sizeof job[0], used);
+}
+
 /* Returns the number of values, or -1 when the file needs the sequential path. */
 static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t cap)
 {

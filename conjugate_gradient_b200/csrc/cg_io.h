@@ -25,6 +25,9 @@ int  cgb_token_to_double(const char *p, const char *e, double *out);
  * bytes the fast tokeniser does not handle (a BOM): use cgb_read_values() then. */
 int64_t cgb_text_locate(const cgb_text *t, int64_t first, int64_t count, size_t *beg, size_t *end);
 
+/* memcpy split between up to 8 threads (CGB_IO_THREADS caps it; below 2 MiB a plain memcpy). */
+void cgb_parallel_copy(void *dst, const void *src, size_t len);
+
 /* cgb_write_values() with the choice to append (row blocks of a matrix written in turn). */
 int cgb_write_values_mode(const char *path, const double *v, int64_t count, int fmt_decimals, int append);
 #ifdef __cplusplus

@@ -180,6 +180,23 @@ int main(int argc, char **argv)
     write_file(path, "2\n2\n", 4);
     CHECK(cgb_read_dimensions(path, dims) != CGB_OK, "short dimensions");
 
+    /* the ingest's staging copy: every byte, every split, exact-size buffers */
+    {
+        const size_t sizes[] = {0, 1, 4095, 4096, 4097, (size_t)1 << 20, ((size_t)3 << 20) + 17, ((size_t)32 << 20) + 2053};
+        for (unsigned t = 0; t < sizeof threads / sizeof *threads; ++t) {
+            setenv("CGB_IO_THREADS", threads[t], 1);
+            for (unsigned k = 0; k < sizeof sizes / sizeof *sizes; ++k) {
+                const size_t len = sizes[k];
+                unsigned char *src = malloc(len + 1), *dst = malloc(len + 1);
+                for (size_t i = 0; i < len; ++i) src[i] = (unsigned char)(i * 2654435761u >> 13);
+                memset(dst, 0xEE, len + 1);
+                cgb_parallel_copy(dst, src, len);
+                CHECK(memcmp(dst, src, len) == 0 && dst[len] == 0xEE, "parallel copy of %zu bytes (threads %s)", len, threads[t]);
+                free(src); free(dst);
+            }
+        }
+    }
+
     FILE *nul = fopen("/dev/null", "w");
     const double m[6] = {1, 2, 3, 4, 5, 6};
     cgb_print_vector(nul, m, 2, 3);
