@@ -97,3 +97,31 @@ def test_cli_argument_handling_under_asan_ubsan(tmp_path, golden_dir):
         out = r.stdout + r.stderr
         assert "AddressSanitizer" not in out and "runtime error" not in out, (args[:2], out[-2000:])
         assert r.returncode == code and msg in out, (args, r.returncode, out[-500:])
+
+
+def test_cli_random_argument_vectors_under_asan(tmp_path, golden_dir):
+    """300 seeded random argument vectors from the CLI's own vocabulary (plus junk) against the sanitizer build:
+    whatever the combination, the process ends with status 0, 1 or 2 and no sanitizer report."""
+    import random
+    import conjugate_gradient_b200 as cg
+    libdir = os.path.dirname(cg.LIB_PATH)
+    exe = str(tmp_path / "cg_b200_asan")
+    r = subprocess.run([CC, "-O1", "-g", "-std=gnu11", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined",
+                        os.path.join(ROOT, "conjugate_gradient_b200", "csrc", "cg_main.c"), "-o", exe,
+                        f"-L{libdir}", "-lcgb200", f"-Wl,-rpath,{libdir}", "-lpthread", "-lm"], capture_output=True, text=True)
+    if r.returncode != 0 and "cannot find -lasan" in r.stderr:
+        pytest.skip("no libasan")
+    assert r.returncode == 0, r.stderr
+    g = lambda f: os.path.join(golden_dir, f)
+    flags = ["--print-x", "--stats", "--round4", "--guard", "--symmetric", "--dims", "--write-x", "--run-record", "--emit-files",
+             "--gpus", "--eps", "--max-iter", "--gen", "--seed", "--bench-iters", "--gemv", "--cg", "--kappa-log2", "--comm", "--bogus"]
+    values = ["0", "1", "2", "3", "16", "-1", "1e-6", "x", "", "classic", "fused", "peer", "nccl", "auto", "99999999999999999999",
+              g("g2_dimensions.txt"), g("g2_matrixA.txt"), g("g2_vectorb.txt"), g("g2_x0.txt"), str(tmp_path / "out.txt"), "/nonexistent/f"]
+    rnd = random.Random(20170209)
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0")
+    for _ in range(300):
+        argv = [rnd.choice(flags + values) for _ in range(rnd.randint(0, 9))]
+        r = subprocess.run([exe] + argv, capture_output=True, text=True, env=env, timeout=120, cwd=str(tmp_path))
+        out = r.stdout + r.stderr
+        assert "AddressSanitizer" not in out and "runtime error" not in out, (argv, out[-1500:])
+        assert r.returncode in (0, 1, 2), (argv, r.returncode, out[-500:])
