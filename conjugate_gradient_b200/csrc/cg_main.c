@@ -40,6 +40,7 @@
  *                     reason, timings, GB/s) -- the reference reports only a time
  */
 #define _GNU_SOURCE
+#include <errno.h>
 #include <math.h>
 #include <pthread.h>
 #include <stdio.h>
@@ -65,8 +66,9 @@ typedef struct {
 static int parse_ll(const char *opt, const char *v, long long lo, long long *out)
 {
     char *end = NULL;
+    errno = 0;
     const long long x = strtoll(v, &end, 10);
-    if (end == v || *end != '\0' || x < lo) {
+    if (end == v || *end != '\0' || x < lo || errno == ERANGE) {
         fprintf(stderr, "option %s takes an integer >= %lld (got \"%s\")\n", opt, lo, v);
         return -1;
     }
@@ -281,8 +283,11 @@ int main(int argc, char **argv)
 #define SOLVER_STDOUT_OFF() do { fflush(stdout); saved_stdout = dup(1); if (saved_stdout >= 0) dup2(2, 1); } while (0)
 #define SOLVER_STDOUT_ON()  do { fflush(stdout); if (saved_stdout >= 0) { dup2(saved_stdout, 1); close(saved_stdout); saved_stdout = -1; } } while (0)
 
+    /* n * n is printed and sized below: keep it inside 63 bits (no GPU set holds such a matrix anyway) */
+#define MAX_ORDER 2147483647LL
     if (cli.gen_n > 0) {
         n = cli.gen_n;
+        if (n > MAX_ORDER) { fprintf(stderr, "cg_b200: matrix order %lld is out of range\n", (long long)n); return 1; }
         if (n % cli.gpus != 0) {                     /* parallel_cg.c:86-90 */
             printf("%lld is not divisible by %d\n", (long long)n, cli.gpus);
             return 1;
@@ -312,6 +317,7 @@ int main(int argc, char **argv)
             return 1;
         }
         n = dims[0];
+        if (n > MAX_ORDER) { fprintf(stderr, "cg_b200: matrix order %lld is out of range\n", (long long)n); return 1; }
         if (dims[2] != n || dims[3] != 1) {
             fprintf(stderr, "cg_b200: dimensions of b (%lld x %lld) do not match A\n", (long long)dims[2], (long long)dims[3]);
             return 1;

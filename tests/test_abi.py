@@ -94,11 +94,19 @@ def test_cli_messages_without_gpu(golden_dir):
     (["--gemv", "7"], "--gemv takes 0"),
     (["--gemv", "bulk"], "--gemv takes an integer"),
     (["--gen", "64"], "takes no input files"),                  # was a silent exit 2
+    (["--max-iter", "99999999999999999999"], "--max-iter takes an integer"),   # strtoll saturates: not a number we were given
 ])
 def test_cli_usage_errors(golden_dir, args, msg):
     files = [os.path.join(golden_dir, f) for f in ("g2_matrixA.txt", "g2_vectorb.txt", "g2_x0.txt")]
     r = subprocess.run([B.CLI_PATH] + files + args, capture_output=True, text=True)
     assert r.returncode == 2 and msg in r.stderr, (r.returncode, r.stderr)
+
+
+def test_cli_refuses_orders_whose_square_overflows():
+    r = subprocess.run([B.CLI_PATH, "--gen", "4000000000"], capture_output=True, text=True)
+    assert r.returncode == 1 and "out of range" in r.stderr and "Computing cg" not in r.stdout   # printed n*n = -2446744073709551616
+    r = subprocess.run([B.CLI_PATH, "--gen", "99999999999999999999"], capture_output=True, text=True)
+    assert r.returncode == 2 and "--gen takes an integer" in r.stderr
 
 
 def test_compute_fails_loudly_without_gpu():
