@@ -118,7 +118,7 @@ int cgb_shutdown(void)
 int cgb_conjugrad_host_opt(const double *A, const double *b, double *x, int64_t n, int gpus,
                            const cgb_options *opt, cgb_stats *stats)
 {
-    if (!A || !b || !x || n < 1) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_host: bad argument", "", __LINE__); return CGB_ERR_ARG; }
+    if (!A || !b || !x || n < 1 || n > CGB_MAX_ORDER) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_host: bad argument (null pointer or matrix order out of range)", "", __LINE__); return CGB_ERR_ARG; }
     if (gpus < 1) gpus = 1;
     if (gpus > MAX_GPUS) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_host: too many GPUs", "", __LINE__); return CGB_ERR_ARG; }
     if (n % gpus != 0) {
@@ -188,7 +188,7 @@ static void *team_generated_main(void *arg)
 int cgb_solve_generated(int64_t n, uint64_t seed, unsigned flags, int gpus,
                         const cgb_options *opt, double *x, cgb_stats *stats)
 {
-    if (n < 1) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_solve_generated: bad order", "", __LINE__); return CGB_ERR_ARG; }
+    if (n < 1 || n > CGB_MAX_ORDER) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_solve_generated: matrix order out of range", "", __LINE__); return CGB_ERR_ARG; }
     if (gpus < 1) gpus = 1;
     if (gpus > MAX_GPUS) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_solve_generated: too many GPUs", "", __LINE__); return CGB_ERR_ARG; }
     if (n % gpus != 0) {
@@ -256,7 +256,7 @@ static void *team_files_solve_main(void *arg)
 int cgb_conjugrad_files(const char *fileA, const char *fileB, const char *fileX, int64_t n, int gpus,
                         const cgb_options *opt, double *x, cgb_stats *stats)
 {
-    if (!fileA || !fileB || !fileX || n < 1) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_files: bad argument", "", __LINE__); return CGB_ERR_ARG; }
+    if (!fileA || !fileB || !fileX || n < 1 || n > CGB_MAX_ORDER) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_files: bad argument (null pointer or matrix order out of range)", "", __LINE__); return CGB_ERR_ARG; }
     if (gpus < 1) gpus = 1;
     if (gpus > MAX_GPUS) { cgb_set_error("%s%s (cg_dropin.c:%d)", "cgb_conjugrad_files: too many GPUs", "", __LINE__); return CGB_ERR_ARG; }
     if (n % gpus != 0) {

@@ -18,6 +18,10 @@ struct cgb_graph_key {
     int n_dot, defer_rr, pdl;
 };
 
+/* Largest matrix order the entry points accept: n * n * 8 must stay far inside size_t / int64_t
+ * (2^24 squared is 2.2 PB of FP64 -- beyond any GPU set this library runs on). */
+#define CGB_MAX_ORDER ((int64_t)1 << 24)
+
 #define CGB_MAX_GUARDS 24
 #define CGB_GUARD_BYTES 256
 #define CGB_GUARD_BYTE 0xA5

@@ -415,6 +415,7 @@ int cgb_device_info(cgb_ctx *c, int *device, int *sm_count, int64_t *free_bytes,
 int cgb_ensure_problem(cgb_ctx *c, int64_t n)
 {
     if (n < 1) FAIL(CGB_ERR_ARG, "matrix order must be >= 1");
+    if (n > CGB_MAX_ORDER) FAIL(CGB_ERR_ARG, "matrix order out of range (n * n * 8 bytes must be addressable)");
     if (n % c->ranks != 0) {
         /* parallel_cg.c:86-90: "%d is not divisible by %d" */
         snprintf(tl_err, sizeof tl_err, "%lld is not divisible by %d", (long long)n, c->ranks);
@@ -1048,7 +1049,7 @@ int cgb_conjugrad_rank(cgb_ctx *c, const double *local_A, const double *local_b,
                        double *local_x, int64_t local_row, const cgb_options *opt,
                        cgb_stats *stats)
 {
-    if (!c || !local_A || !local_b || !local_x || local_row < 1)
+    if (!c || !local_A || !local_b || !local_x || local_row < 1 || local_row > CGB_MAX_ORDER)
         FAIL(CGB_ERR_ARG, "cgb_conjugrad_rank: bad argument");
     const int64_t n = local_row * c->ranks;
     int rc = CGB_OK;
@@ -1130,7 +1131,7 @@ static int dev_dup(cgb_ctx *c, double **d, const double *h, int64_t count, cudaS
 int cgb_op_matvec(cgb_ctx *c, const double *A, const double *v, const double *w, double *y,
                   double *dot, int64_t m, int64_t n, const cgb_options *opt)
 {
-    if (!c || !A || !v || !y || m < 1 || n < 1) FAIL(CGB_ERR_ARG, "cgb_op_matvec: bad argument");
+    if (!c || !A || !v || !y || m < 1 || n < 1 || m > CGB_MAX_ORDER || n > CGB_MAX_ORDER) FAIL(CGB_ERR_ARG, "cgb_op_matvec: bad argument");
     cgb_options o;
     if (opt) o = *opt; else cgb_default_options(&o);
     CU(cudaSetDevice(c->device));
@@ -1251,7 +1252,7 @@ out:
 int cgb_op_generate(cgb_ctx *c, int64_t n, int64_t row0, int64_t m, uint64_t seed, unsigned flags,
                     double *A_rows, double *b_rows)
 {
-    if (!c || n < 1 || m < 1 || row0 < 0 || row0 + m > n) FAIL(CGB_ERR_ARG, "cgb_op_generate: bad argument");
+    if (!c || n < 1 || n > CGB_MAX_ORDER || m < 1 || row0 < 0 || row0 + m > n) FAIL(CGB_ERR_ARG, "cgb_op_generate: bad argument");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = c->stream;
     double *dA = NULL, *db = NULL;

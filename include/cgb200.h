@@ -28,7 +28,7 @@ extern "C" {
 /* status codes (the reference returns nothing and exit(0)s / MPI_Aborts on
  * failure, serialConjugate.c:48-57,78-82, parallel_cg.c:76-95; a library must not) */
 #define CGB_OK                 0
-#define CGB_ERR_ARG           -1   /* bad argument / null pointer / n < 1            */
+#define CGB_ERR_ARG           -1   /* bad argument / null pointer / n < 1 or > 2^24  */
 #define CGB_ERR_CUDA          -2   /* CUDA runtime error or no device                 */
 #define CGB_ERR_NCCL          -3   /* NCCL error                                      */
 #define CGB_ERR_NOT_DIVISIBLE -4   /* n % ranks != 0   (parallel_cg.c:86-90)          */

@@ -131,6 +131,11 @@ def test_invalid_arguments_are_status_codes_not_crashes(golden_dir):
         for gpus in (-1, 0, 1, 3, 100000):
             assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, n, gpus, C.byref(o), C.byref(st)) == ARG
     assert host(None, b.ctypes.data, x.ctypes.data, 2, 1, C.byref(o), C.byref(st)) == ARG
+    # orders whose n * n * 8 bytes would wrap size_t are refused before anything is sized from them
+    for n in (2 ** 24 + 1, 2 ** 31, 2 ** 40, 2 ** 62):
+        assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, n, 1, C.byref(o), C.byref(st)) == ARG
+        assert L.cgb_solve_generated(n, 1, 0, 1, C.byref(o), None, C.byref(st)) == ARG
+        assert L.cgb_conjugrad_files(b"a", b"b", b"c", n, 1, C.byref(o), None, C.byref(st)) == ARG
     assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, 2, 3, C.byref(o), C.byref(st)) == NOTDIV   # parallel_cg.c:86-90
     assert b"2 is not divisible by 3" in L.cgb_last_error()
     assert host(A.ctypes.data, b.ctypes.data, x.ctypes.data, 2, 17, C.byref(o), C.byref(st)) == ARG
