@@ -51,7 +51,7 @@ class Stats(C.Structure):
                 ("gemv_threads", C.c_int), ("gemv_vec", C.c_int), ("gemv_stages", C.c_int),
                 ("gemv_tile_cols", C.c_int), ("gemv_grid", C.c_int), ("graph_chunk", C.c_int),
                 ("comm", C.c_int), ("exit_reason", C.c_int), ("cg_variant", C.c_int),
-                ("gemv_keep_rows", C.c_int64), ("h2d_bytes", C.c_int64), ("pdl", C.c_int), ("reserved_", C.c_int)]
+                ("gemv_keep_rows", C.c_int64), ("h2d_bytes", C.c_int64), ("pdl", C.c_int), ("h2d_path", C.c_int)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

@@ -195,6 +195,7 @@ done:
         c->sym_state = 0;
         c->tiles_only = 0;
         c->h2d_bytes = 0;
+        c->h2d_path = CGB_H2D_NONE;
     }
 out:
     if (have_text) cgb_text_close(&tx);

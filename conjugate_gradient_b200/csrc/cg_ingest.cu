@@ -52,7 +52,7 @@ __device__ __forceinline__ unsigned int ing_start_mask(const unsigned char *txt,
 }
 
 __global__ void __launch_bounds__(ING_NT)
-ingest_count_kernel(const unsigned char *__restrict__ txt, long long n16, unsigned int *__restrict__ block_counts)
+cgb_ingest_count_kernel(const unsigned char *__restrict__ txt, long long n16, unsigned int *__restrict__ block_counts)
 {
     const long long t = (long long)blockIdx.x * ING_NT + threadIdx.x;
     unsigned int c = (t < n16) ? __popc(ing_start_mask(txt, t)) : 0u;
@@ -71,7 +71,7 @@ ingest_count_kernel(const unsigned char *__restrict__ txt, long long n16, unsign
 
 /* One CTA: block_offsets[b] = state->base + sum_{q<b} block_counts[q]; state->base += total. */
 __global__ void __launch_bounds__(1024)
-ingest_scan_kernel(const unsigned int *__restrict__ block_counts, long long *__restrict__ block_offsets,
+cgb_ingest_scan_kernel(const unsigned int *__restrict__ block_counts, long long *__restrict__ block_offsets,
                    int nblocks, cgk_ingest_state *state)
 {
     __shared__ long long s_part[1024];
@@ -139,7 +139,7 @@ __device__ __forceinline__ bool ing_parse(const unsigned char *p, double *out)
 }
 
 __global__ void __launch_bounds__(ING_NT)
-ingest_parse_kernel(const unsigned char *__restrict__ txt, long long n16, long long abs_pos,
+cgb_ingest_parse_kernel(const unsigned char *__restrict__ txt, long long n16, long long abs_pos,
                     const long long *__restrict__ block_offsets, double *__restrict__ dst,
                     long long cap, cgk_ingest_state *state, unsigned long long *__restrict__ exc_pos,
                     long long *__restrict__ exc_idx, unsigned int exc_cap)
@@ -177,7 +177,7 @@ ingest_parse_kernel(const unsigned char *__restrict__ txt, long long n16, long l
     }
 }
 
-__global__ void scatter_kernel(double *__restrict__ dst, const long long *__restrict__ idx,
+__global__ void cgb_place_values_kernel(double *__restrict__ dst, const long long *__restrict__ idx,
                                const double *__restrict__ val, long long count)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -199,9 +199,9 @@ extern "C" int cgk_ingest_chunk(const unsigned char *txt, int64_t padded_len, in
     const long long n16 = padded_len / ING_BYTES_PER_THREAD;
     const int nb = (int)cgk_ingest_blocks(padded_len);
     if (nb < 1) return 0;
-    ingest_count_kernel<<<nb, ING_NT, 0, st>>>(txt, n16, block_counts);
-    ingest_scan_kernel<<<1, 1024, 0, st>>>(block_counts, block_offsets, nb, state);
-    ingest_parse_kernel<<<nb, ING_NT, 0, st>>>(txt, n16, (long long)abs_pos, block_offsets, dst, (long long)cap,
+    cgb_ingest_count_kernel<<<nb, ING_NT, 0, st>>>(txt, n16, block_counts);
+    cgb_ingest_scan_kernel<<<1, 1024, 0, st>>>(block_counts, block_offsets, nb, state);
+    cgb_ingest_parse_kernel<<<nb, ING_NT, 0, st>>>(txt, n16, (long long)abs_pos, block_offsets, dst, (long long)cap,
                                               state, exc_pos, exc_idx, exc_cap);
     return (int)cudaGetLastError();
 }
@@ -209,6 +209,6 @@ extern "C" int cgk_ingest_chunk(const unsigned char *txt, int64_t padded_len, in
 extern "C" int cgk_scatter(double *dst, const long long *idx, const double *val, int64_t count, void *stream)
 {
     if (count < 1) return 0;
-    scatter_kernel<<<(unsigned int)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dst, idx, val, (long long)count);
+    cgb_place_values_kernel<<<(unsigned int)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dst, idx, val, (long long)count);
     return (int)cudaGetLastError();
 }

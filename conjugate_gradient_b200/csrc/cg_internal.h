@@ -23,6 +23,13 @@ struct cgb_graph_key {
 #define CGB_MAX_ORDER ((int64_t)1 << 24)
 
 #define CGB_MAX_GUARDS 24
+
+/* pageable host memory -> HBM (cg_stage.c) */
+#define CGB_STAGE_MAX_THREADS 32
+typedef struct cgb_stage_run {      /* rows of `width` bytes: host rows `spitch` apart, device rows `dpitch` apart */
+    void *dst; const void *src;
+    size_t width, rows, dpitch, spitch;
+} cgb_stage_run;
 #define CGB_GUARD_BYTES 256
 #define CGB_GUARD_BYTE 0xA5
 
@@ -77,6 +84,13 @@ struct cgb_ctx {
     void *sy_tiles;
     int64_t sy_ntiles;
     cgk_symplan sy_plan;              /* ranks > 1: which half of the row block this rank reads */
+    /* staging ring of cg_stage.c: T threads x 2 pinned slots, one copy stream per thread */
+    void *stage_pin;
+    size_t stage_pin_bytes;
+    cudaStream_t stage_stream[CGB_STAGE_MAX_THREADS];
+    cudaEvent_t stage_ev[CGB_STAGE_MAX_THREADS][2];
+    int stage_threads_used;
+    int h2d_path;                     /* CGB_H2D_* of the last upload */
     /* guard bands (CGB_DEBUG_GUARDS=1 at cgb_create): 256 B of a fixed byte before and after every
      * solver array, verified by cgb_debug_check_guards -- the out-of-bounds-write check of the tests */
     int guards_on, n_guards;
@@ -86,5 +100,10 @@ struct cgb_ctx {
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);
 /* (Re)allocates the device arrays (and, with ranks > 1, the peer window: collective) for order n. */
 int cgb_ensure_problem(cgb_ctx *c, int64_t n);
+/* cg_stage.c */
+int  cgb_host_is_pageable(const void *p);
+int  cgb_stage_mode(void);
+int  cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int pageable, int *path_out);
+void cgb_stage_release(cgb_ctx *c);
 
 #endif

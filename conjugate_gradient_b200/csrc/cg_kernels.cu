@@ -87,7 +87,7 @@ __device__ __forceinline__ void gemv_accumulate(double (&acc)[R], const double *
 
 template <int R, int U, int NT, int VW>
 __global__ void __launch_bounds__(NT)
-gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
+cgb_rowblock_matvec_ldg(const double *__restrict__ A, const double *__restrict__ v,
                 const double *__restrict__ w, double *__restrict__ y,
                 double *__restrict__ partials, double *__restrict__ dot_out,
                 cgk_scalars *__restrict__ sc, long long m, long long n)
@@ -146,7 +146,7 @@ gemv_ldg_kernel(const double *__restrict__ A, const double *__restrict__ v,
  * of 1024 CTAs then fits the 148 SMs in ONE wave (6 per SM would leave a second wave of 136) */
 template <int R, int U, int NT, int VW>
 __global__ void __launch_bounds__(NT, (NT == 128 && R * U * VW <= 16) ? 7 : 0)
-gemv_ldg_keep_kernel(const double *__restrict__ A, const double *__restrict__ v,
+cgb_rowblock_matvec_keep(const double *__restrict__ A, const double *__restrict__ v,
                      const double *__restrict__ w, double *__restrict__ y,
                      double *__restrict__ partials, double *__restrict__ dot_out,
                      cgk_scalars *__restrict__ sc, long long m, long long n, long long keep_rows)
@@ -239,7 +239,7 @@ gemv_ldg_keep_kernel(const double *__restrict__ A, const double *__restrict__ v,
  * the rank's p.Ap partial into every rank's mailbox and advances the epoch. */
 template <int R, int U, int NT, int VW>
 __global__ void __launch_bounds__(NT)
-gemv_ldg_comm_kernel(const double *__restrict__ A, const double *v,
+cgb_rowblock_matvec_comm(const double *__restrict__ A, const double *v,
                      const double *w, double *__restrict__ y,
                      double *__restrict__ partials, double *__restrict__ dot_out,
                      cgk_scalars *sc, long long m, long long n, const cgk_peers peers)
@@ -386,7 +386,7 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 
 template <int R, int C, int STAGES, int NT>
 __global__ void __launch_bounds__(NT + 32)
-gemv_bulk_kernel(const double *__restrict__ A, const double *__restrict__ v,
+cgb_rowblock_matvec_bulk(const double *__restrict__ A, const double *__restrict__ v,
                  const double *__restrict__ w, double *__restrict__ y,
                  double *__restrict__ partials, double *__restrict__ dot_out,
                  cgk_scalars *__restrict__ sc, long long m, long long n)
@@ -559,7 +559,7 @@ __device__ __forceinline__ void post_p_flags(const cgk_peers &peers, unsigned in
  * parallel_cg.c:290) and the r.r partial to every mailbox (the all-reduce of :287). */
 template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
-init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax,
+cgb_init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax,
                      double *__restrict__ r, double *p_loc,
                      double *__restrict__ partials, double *__restrict__ rr_out,
                      cgk_scalars *sc, long long m, const cgk_peers peers)
@@ -600,7 +600,7 @@ init_residual_kernel(const double *__restrict__ b, const double *__restrict__ Ax
  * mailbox (MPI_Allreduce :294); the r.r partial is pushed to every mailbox (:313). */
 template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
-xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
+cgb_xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
                  const double *p_loc, const double *__restrict__ Ap,
                  double *__restrict__ partials, double *__restrict__ rr_out,
                  cgk_scalars *sc, int cur, int guard, long long m, const cgk_peers peers,
@@ -654,7 +654,7 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
     const double mine = vec_cta_sum(s);
     if constexpr (COMM) {
         double total = 0.0;
-        /* x and r are local: device-scope fences (see gemv_ldg_comm_kernel) */
+        /* x and r are local: device-scope fences (see cgb_rowblock_matvec_comm) */
         if (cta_partials_finish_sys<VEC_NT, false>(mine, partials, rr_out, &sc->ticket_vec, &total) && threadIdx.x == 0) {
             const unsigned int e = ep + 1u;                       /* r.r events: 0 = init, k+1 = iteration k */
             for (int g = 0; g < peers.ranks; ++g)
@@ -677,7 +677,7 @@ xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
  * as it is computed and the last CTA posts the tag the peers' next GEMV waits for. */
 template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
-p_update_kernel(double *p_loc, const double *__restrict__ r,
+cgb_p_update_kernel(double *p_loc, const double *__restrict__ r,
                 cgk_scalars *sc, int cur, double eps, int ignore_stop,
                 long long max_iter, long long m, const cgk_peers peers,
                 const double *__restrict__ rr_partials, int n_rr)
@@ -746,7 +746,7 @@ p_update_kernel(double *p_loc, const double *__restrict__ r,
  * derives the same decisions from the same scalars, none from a flag written in this launch. */
 template <bool COMM>
 __global__ void __launch_bounds__(VEC_NT)
-cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec, double *__restrict__ svec,
+cgb_cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec, double *__restrict__ svec,
                 const double *__restrict__ w, double *__restrict__ partials, cgk_scalars *sc, double eps,
                 int ignore_stop, int guard, long long max_iter, long long m, const cgk_peers peers)
 {
@@ -823,7 +823,7 @@ cg2_step_kernel(double *__restrict__ x, double *r_loc, double *__restrict__ pvec
  * added up by every CTA from the partials the previous step / the product left; the step's
  * own state moves between the two parity slots of cgk_scalars. */
 __global__ void __launch_bounds__(VEC_NT)
-cg2_step_one_kernel(double *__restrict__ x, double *__restrict__ r_loc, double *__restrict__ pvec,
+cgb_cg2_step_one_kernel(double *__restrict__ x, double *__restrict__ r_loc, double *__restrict__ pvec,
                     double *__restrict__ svec, const double *__restrict__ w, double *partials,
                     cgk_scalars *sc, int cur, double eps, int ignore_stop, int guard, long long max_iter,
                     long long m, const double *__restrict__ dot_partials, int n_dot)
@@ -885,7 +885,7 @@ cg2_step_one_kernel(double *__restrict__ x, double *__restrict__ r_loc, double *
     if (threadIdx.x == 0) partials[(size_t)(cur ^ 1) * CGK_MAX_VEC_CTAS + blockIdx.x] = mine;
 }
 
-__global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
+__global__ void cgb_reset_kernel(cgk_scalars *sc, unsigned int gen)
 {
     sc->rr[0] = sc->rr[1] = 0.0;
     sc->pAp = sc->pAp_local = sc->rr_local = 0.0;
@@ -903,7 +903,7 @@ __global__ void reset_kernel(cgk_scalars *sc, unsigned int gen)
 }
 
 template <bool COMM>
-__global__ void after_init_kernel(cgk_scalars *sc, int guard, const cgk_peers peers)
+__global__ void cgb_after_init_kernel(cgk_scalars *sc, int guard, const cgk_peers peers)
 {
     if constexpr (COMM) {
         const unsigned int gen = *(volatile unsigned int *)&sc->gen;
@@ -942,7 +942,7 @@ __device__ __forceinline__ double gen_elem(uint64_t key, uint64_t n, uint64_t i,
 }
 
 __global__ void __launch_bounds__(256)
-generate_A_kernel(double *__restrict__ A, long long n, long long row0, long long m,
+cgb_generate_A_kernel(double *__restrict__ A, long long n, long long row0, long long m,
                   uint64_t key, unsigned flags)
 {
     const long long total = m * n;
@@ -954,7 +954,7 @@ generate_A_kernel(double *__restrict__ A, long long n, long long row0, long long
 }
 
 __global__ void __launch_bounds__(256)
-generate_b_kernel(double *__restrict__ b, long long n, long long row0, long long m,
+cgb_generate_b_kernel(double *__restrict__ b, long long n, long long row0, long long m,
                   uint64_t key, unsigned flags)
 {
     for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < m;
@@ -965,7 +965,7 @@ generate_b_kernel(double *__restrict__ b, long long n, long long row0, long long
     }
 }
 
-__global__ void __launch_bounds__(256) l2_flush_kernel(double2 *buf, long long n2)
+__global__ void __launch_bounds__(256) cgb_l2_flush_kernel(double2 *buf, long long n2)
 {
     for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n2;
          e += (long long)gridDim.x * 256) {
@@ -997,8 +997,8 @@ static gemv_fn pick_ldg_vec(int vec)
 {
     if (R * U * vec > 64) return nullptr;                    /* would spill: not instantiated */
     switch (vec) {
-    case 4: if constexpr (R * U * 4 <= 64) return gemv_ldg_kernel<R, U, NT, 4>; else return nullptr;
-    case 2: if constexpr (R * U * 2 <= 64) return gemv_ldg_kernel<R, U, NT, 2>; else return nullptr;
+    case 4: if constexpr (R * U * 4 <= 64) return cgb_rowblock_matvec_ldg<R, U, NT, 4>; else return nullptr;
+    case 2: if constexpr (R * U * 2 <= 64) return cgb_rowblock_matvec_ldg<R, U, NT, 2>; else return nullptr;
     default: return nullptr;
     }
 }
@@ -1024,7 +1024,7 @@ static gemv_fn pick_ldg_u(int u, int nt, int vec)
 }
 static gemv_fn pick_ldg(int r, int u, int nt, int vec)
 {
-    if (vec == 1) return gemv_ldg_kernel<4, 1, 128, 1>;      /* odd n / unaligned: scalar loads */
+    if (vec == 1) return cgb_rowblock_matvec_ldg<4, 1, 128, 1>;      /* odd n / unaligned: scalar loads */
     switch (r) {
     case 1: return pick_ldg_u<1>(u, nt, vec);
     case 2: return pick_ldg_u<2>(u, nt, vec);
@@ -1039,11 +1039,11 @@ typedef void (*gemv_keep_fn)(const double *, const double *, const double *, dou
                              double *, cgk_scalars *, long long, long long, long long);
 struct keep_cfg { int r, u, nt, vec; gemv_keep_fn fn; };
 static const keep_cfg k_keep[] = {
-    {4, 1, 128, 4, gemv_ldg_keep_kernel<4, 1, 128, 4>},
-    {4, 2, 128, 4, gemv_ldg_keep_kernel<4, 2, 128, 4>},
-    {8, 1, 128, 4, gemv_ldg_keep_kernel<8, 1, 128, 4>},
-    {2, 1, 256, 4, gemv_ldg_keep_kernel<2, 1, 256, 4>},
-    {4, 2, 256, 4, gemv_ldg_keep_kernel<4, 2, 256, 4>},
+    {4, 1, 128, 4, cgb_rowblock_matvec_keep<4, 1, 128, 4>},
+    {4, 2, 128, 4, cgb_rowblock_matvec_keep<4, 2, 128, 4>},
+    {8, 1, 128, 4, cgb_rowblock_matvec_keep<8, 1, 128, 4>},
+    {2, 1, 256, 4, cgb_rowblock_matvec_keep<2, 1, 256, 4>},
+    {4, 2, 256, 4, cgb_rowblock_matvec_keep<4, 2, 256, 4>},
 };
 static const keep_cfg *find_keep(int r, int u, int nt, int vec)
 {
@@ -1055,16 +1055,16 @@ static const keep_cfg *find_keep(int r, int u, int nt, int vec)
 /* bulk variants: (R, C, STAGES, NT) */
 struct bulk_cfg { int r, c, stages, nt; gemv_fn fn; };
 static const bulk_cfg k_bulk[] = {
-    {4, 512, 4, 128, gemv_bulk_kernel<4, 512, 4, 128>},
-    {4, 512, 8, 128, gemv_bulk_kernel<4, 512, 8, 128>},
-    {8, 512, 4, 128, gemv_bulk_kernel<8, 512, 4, 128>},
-    {8, 512, 5, 128, gemv_bulk_kernel<8, 512, 5, 128>},
-    {8, 256, 8, 128, gemv_bulk_kernel<8, 256, 8, 128>},
-    {4, 1024, 4, 256, gemv_bulk_kernel<4, 1024, 4, 256>},
-    {8, 1024, 2, 256, gemv_bulk_kernel<8, 1024, 2, 256>},
-    {8, 1024, 3, 256, gemv_bulk_kernel<8, 1024, 3, 256>},
-    {16, 256, 5, 128, gemv_bulk_kernel<16, 256, 5, 128>},
-    {16, 512, 3, 128, gemv_bulk_kernel<16, 512, 3, 128>},
+    {4, 512, 4, 128, cgb_rowblock_matvec_bulk<4, 512, 4, 128>},
+    {4, 512, 8, 128, cgb_rowblock_matvec_bulk<4, 512, 8, 128>},
+    {8, 512, 4, 128, cgb_rowblock_matvec_bulk<8, 512, 4, 128>},
+    {8, 512, 5, 128, cgb_rowblock_matvec_bulk<8, 512, 5, 128>},
+    {8, 256, 8, 128, cgb_rowblock_matvec_bulk<8, 256, 8, 128>},
+    {4, 1024, 4, 256, cgb_rowblock_matvec_bulk<4, 1024, 4, 256>},
+    {8, 1024, 2, 256, cgb_rowblock_matvec_bulk<8, 1024, 2, 256>},
+    {8, 1024, 3, 256, cgb_rowblock_matvec_bulk<8, 1024, 3, 256>},
+    {16, 256, 5, 128, cgb_rowblock_matvec_bulk<16, 256, 5, 128>},
+    {16, 512, 3, 128, cgb_rowblock_matvec_bulk<16, 512, 3, 128>},
 };
 static const bulk_cfg *find_bulk(int r, int c, int stages, int nt)
 {
@@ -1188,12 +1188,12 @@ typedef void (*gemv_comm_fn)(const double *, const double *, const double *, dou
                              double *, cgk_scalars *, long long, long long, const cgk_peers);
 struct comm_cfg { int r, u, nt, vec; gemv_comm_fn fn; };
 static const comm_cfg k_comm[] = {
-    {4, 2, 256, 4, gemv_ldg_comm_kernel<4, 2, 256, 4>},
-    {2, 1, 256, 4, gemv_ldg_comm_kernel<2, 1, 256, 4>},
-    {2, 2, 256, 4, gemv_ldg_comm_kernel<2, 2, 256, 4>},
-    {4, 1, 128, 4, gemv_ldg_comm_kernel<4, 1, 128, 4>},
-    {4, 2, 128, 2, gemv_ldg_comm_kernel<4, 2, 128, 2>},
-    {4, 1, 128, 1, gemv_ldg_comm_kernel<4, 1, 128, 1>},
+    {4, 2, 256, 4, cgb_rowblock_matvec_comm<4, 2, 256, 4>},
+    {2, 1, 256, 4, cgb_rowblock_matvec_comm<2, 1, 256, 4>},
+    {2, 2, 256, 4, cgb_rowblock_matvec_comm<2, 2, 256, 4>},
+    {4, 1, 128, 4, cgb_rowblock_matvec_comm<4, 1, 128, 4>},
+    {4, 2, 128, 2, cgb_rowblock_matvec_comm<4, 2, 128, 2>},
+    {4, 1, 128, 1, cgb_rowblock_matvec_comm<4, 1, 128, 1>},
 };
 static const comm_cfg *find_comm(int r, int u, int nt, int vec)
 {
@@ -1249,10 +1249,10 @@ extern "C" int cgk_init_residual(const double *b, const double *Ax, double *r, d
                                  const cgk_peers *peers, void *stream)
 {
     if (peers)
-        init_residual_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
+        cgb_init_residual_kernel<true><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
                                                                                     rr_out, sc, (long long)m, *peers);
     else
-        init_residual_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
+        cgb_init_residual_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(b, Ax, r, p_loc, partials,
                                                                                      rr_out, sc, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
@@ -1263,10 +1263,10 @@ extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const do
                              void *stream)
 {
     if (peers)
-        cgk_launch(xr_update_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
+        cgk_launch(cgb_xr_update_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
                    rr_out, sc, cur, guard, (long long)m, *peers, (const double *)nullptr, 0);
     else
-        cgk_launch(xr_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
+        cgk_launch(cgb_xr_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
                    rr_out, sc, cur, guard, (long long)m, k_no_peers, dot_partials, n_dot);
     return (int)cudaGetLastError();
 }
@@ -1278,10 +1278,10 @@ extern "C" int cgk_p_update(double *p_loc, const double *r, cgk_scalars *sc, int
                             const double *rr_partials, int n_rr, void *stream)
 {
     if (peers)
-        cgk_launch(p_update_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
+        cgk_launch(cgb_p_update_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
                    ignore_stop, (long long)max_iter, (long long)m, *peers, (const double *)nullptr, 0);
     else
-        cgk_launch(p_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
+        cgk_launch(cgb_p_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, p_loc, r, sc, cur, eps,
                    ignore_stop, (long long)max_iter, (long long)m, k_no_peers, rr_partials, n_rr);
     return (int)cudaGetLastError();
 }
@@ -1291,10 +1291,10 @@ extern "C" int cgk_cg2_step(double *x, double *r_loc, double *pvec, double *svec
                             int64_t max_iter, int64_t m, const cgk_peers *peers, void *stream)
 {
     if (peers)
-        cgk_launch(cg2_step_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r_loc, pvec, svec, w,
+        cgk_launch(cgb_cg2_step_kernel<true>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r_loc, pvec, svec, w,
                    partials, sc, eps, ignore_stop, guard, (long long)max_iter, (long long)m, *peers);
     else
-        cg2_step_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
+        cgb_cg2_step_kernel<false><<<vec_grid(m), VEC_NT, 0, (cudaStream_t)stream>>>(x, r_loc, pvec, svec, w, partials, sc, eps,
                                                                                 ignore_stop, guard, (long long)max_iter, (long long)m, k_no_peers);
     return (int)cudaGetLastError();
 }
@@ -1303,21 +1303,21 @@ extern "C" int cgk_cg2_step_one(double *x, double *r_loc, double *pvec, double *
                                 cgk_scalars *sc, int cur, double eps, int ignore_stop, int guard, int64_t max_iter,
                                 int64_t m, const double *dot_partials, int n_dot, void *stream)
 {
-    cgk_launch(cg2_step_one_kernel, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r_loc, pvec, svec, w, partials,
+    cgk_launch(cgb_cg2_step_one_kernel, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r_loc, pvec, svec, w, partials,
                sc, cur, eps, ignore_stop, guard, (long long)max_iter, (long long)m, dot_partials, n_dot);
     return (int)cudaGetLastError();
 }
 
 extern "C" int cgk_reset(cgk_scalars *sc, unsigned int gen, void *stream)
 {
-    reset_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc, gen);
+    cgb_reset_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sc, gen);
     return (int)cudaGetLastError();
 }
 
 extern "C" int cgk_after_init(cgk_scalars *sc, int guard, const cgk_peers *peers, void *stream)
 {
-    if (peers) after_init_kernel<true><<<1, 32, 0, (cudaStream_t)stream>>>(sc, guard, *peers);
-    else after_init_kernel<false><<<1, 32, 0, (cudaStream_t)stream>>>(sc, guard, k_no_peers);
+    if (peers) cgb_after_init_kernel<true><<<1, 32, 0, (cudaStream_t)stream>>>(sc, guard, *peers);
+    else cgb_after_init_kernel<false><<<1, 32, 0, (cudaStream_t)stream>>>(sc, guard, k_no_peers);
     return (int)cudaGetLastError();
 }
 
@@ -1327,7 +1327,7 @@ extern "C" int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uin
     int64_t g = ceil_div(m * n, 256 * 8);
     if (g < 1) g = 1;
     if (g > 148 * 32) g = 148 * 32;
-    generate_A_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)row0,
+    cgb_generate_A_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)row0,
                                                                (long long)m, cgb_gen_key(seed), flags);
     return (int)cudaGetLastError();
 }
@@ -1338,14 +1338,14 @@ extern "C" int cgk_generate_b(double *b, int64_t n, int64_t row0, int64_t m, uin
     int64_t g = ceil_div(m, 256);
     if (g < 1) g = 1;
     if (g > 592) g = 592;
-    generate_b_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(b, (long long)n, (long long)row0,
+    cgb_generate_b_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(b, (long long)n, (long long)row0,
                                                                (long long)m, cgb_gen_key(seed), flags);
     return (int)cudaGetLastError();
 }
 
 extern "C" int cgk_l2_flush(void *buf, int64_t bytes, void *stream)
 {
-    l2_flush_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>((double2 *)buf, (long long)(bytes / 16));
+    cgb_l2_flush_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>((double2 *)buf, (long long)(bytes / 16));
     return (int)cudaGetLastError();
 }
 

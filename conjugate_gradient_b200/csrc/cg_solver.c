@@ -384,6 +384,7 @@ int cgb_destroy(cgb_ctx *c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_problem(c);
+    cgb_stage_release(c);
     if (c->has_comm) ncclCommDestroy(c->comm);
     for (int i = 0; i < 3; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < c->n_gemv_ev; ++i) cudaEventDestroy(c->gemv_ev[i]);
@@ -471,11 +472,15 @@ int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_r
     double t0 = now_s();
     CU(cudaMemcpyAsync(c->x_full, x0_full, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(c->b, b_rows, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    /* A in slabs so that pageable sources pipeline through the driver's staging */
-    const size_t total = (size_t)m * (size_t)n * sizeof(double), slab = (size_t)256 << 20;
-    for (size_t off = 0; off < total; off += slab) {
-        size_t len = total - off < slab ? total - off : slab;
-        CU(cudaMemcpyAsync((char *)c->A + off, (const char *)A_rows + off, len, cudaMemcpyHostToDevice, c->stream));
+    /* A: a pinned source is read in place by the DMA engine; a malloc'ed one (the reference's
+     * memAllocate(), serialConjugate.c:62-64) goes through the staging ring of cg_stage.c */
+    const size_t total = (size_t)m * (size_t)n * sizeof(double);
+    {
+        cgb_stage_run runs[1];                               /* the contiguous block: one row of `total` bytes */
+        const int nr = 1;
+        runs[0].dst = c->A; runs[0].src = A_rows; runs[0].width = total; runs[0].rows = 1; runs[0].dpitch = runs[0].spitch = total;
+        rc = cgb_stage_upload(c, runs, nr, cgb_host_is_pageable(A_rows), &c->h2d_path);
+        if (rc != CGB_OK) return rc;
     }
     CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = now_s() - t0;
@@ -521,24 +526,34 @@ int cgb_load_host_symmetric(cgb_ctx *c, int64_t n, const double *A_rows, const d
     double t0 = now_s();
     cudaError_t ce = cudaMemcpyAsync(c->x_full, x0_full, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream);
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(c->b, b_rows, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, c->stream);
-    int64_t sent = 0;
-    for (int64_t k = 0; k < cnt && ce == cudaSuccess; ) {
+    /* one 2-D run per stretch of adjacent tiles in a tile row (cut at 4 MiB of row width) */
+    cgb_stage_run *runs = malloc((size_t)(cnt > 0 ? cnt : 1) * sizeof *runs);
+    if (!runs) { free(tl); FAIL(CGB_ERR_NOMEM, "out of host memory for the tile runs"); }
+    int64_t sent = 0, nr = 0;
+    const int64_t max_tiles = ((int64_t)4 << 20) / (T * (int64_t)sizeof(double)) > 0 ? ((int64_t)4 << 20) / (T * (int64_t)sizeof(double)) : 1;
+    for (int64_t k = 0; k < cnt; ) {
         const int64_t I = tl[2 * k] & 0xffffff, J0 = tl[2 * k + 1];
         int64_t q = k + 1;
-        while (q < cnt && (tl[2 * q] & 0xffffff) == I && tl[2 * q + 1] == J0 + (q - k)) ++q;
+        while (q < cnt && q - k < max_tiles && (tl[2 * q] & 0xffffff) == I && tl[2 * q + 1] == J0 + (q - k)) ++q;
         const size_t off = (size_t)(I * T) * (size_t)n + (size_t)(J0 * T);
-        ce = cudaMemcpy2DAsync(c->A + off, (size_t)n * sizeof(double), A_rows + off, (size_t)n * sizeof(double),
-                               (size_t)((q - k) * T) * sizeof(double), (size_t)T, cudaMemcpyHostToDevice, c->stream);
+        runs[nr].dst = c->A + off; runs[nr].src = A_rows + off;
+        runs[nr].width = (size_t)((q - k) * T) * sizeof(double); runs[nr].rows = (size_t)T;
+        runs[nr].dpitch = runs[nr].spitch = (size_t)n * sizeof(double);
+        ++nr;
         sent += (q - k) * T * T;
         k = q;
     }
     free(tl);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);
     if (ce != cudaSuccess) {
         (void)cudaGetLastError();
+        free(runs);
         snprintf(tl_err, sizeof tl_err, "cgb_load_host_symmetric: %s", cudaGetErrorString(ce));
         return CGB_ERR_CUDA;
     }
+    rc = cgb_stage_upload(c, runs, nr, cgb_host_is_pageable(A_rows), &c->h2d_path);
+    free(runs);
+    if (rc != CGB_OK) return rc;
+    CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = now_s() - t0;
     c->h2d_bytes = (sent + n + m) * (int64_t)sizeof(double);
     c->loaded = 1;
@@ -559,6 +574,7 @@ int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
     CU(cudaStreamSynchronize(c->stream));
     c->h2d_seconds = 0.0;
     c->h2d_bytes = 0;
+    c->h2d_path = CGB_H2D_NONE;
     c->loaded = 1;
     c->tiles_only = 0;
     c->sym_state = 1;          /* 0.5 (u_ij + u_ji): IEEE addition commutes, exactly symmetric */
@@ -1029,6 +1045,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         stats->exit_reason = c->h_sc->stop_req;
         stats->cg_variant = o.cg_variant;
         stats->pdl = c->pdl;
+        stats->h2d_path = c->h2d_path;
         if (gemv_pairs_used > 0) {
             double sum = 0.0, mn = 1e300;
             for (int i = 0; i < gemv_pairs_used; ++i) {

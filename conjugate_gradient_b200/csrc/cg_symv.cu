@@ -26,7 +26,7 @@
 
 template <int RU>
 __global__ void __launch_bounds__(SY_NT)
-symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
+cgb_halfmat_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
                  const int2 *__restrict__ tiles, double *__restrict__ rowpart,
                  double *__restrict__ colpart, cgk_scalars *__restrict__ sc, long long n, int split)
 {
@@ -111,7 +111,7 @@ symv_tile_kernel(const double *__restrict__ A, const double *__restrict__ p,
  * thread per i (9.1 -> measured below at n = 4096); the 8 sums are added in warp order. */
 #define SY_FR 32
 __global__ void __launch_bounds__(SY_NT)
-symv_finish_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
+cgb_halfmat_finish_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
                    const double *__restrict__ w, double *__restrict__ y,
                    double *__restrict__ partials, double *__restrict__ dot_out,
                    cgk_scalars *__restrict__ sc, long long n, int split)
@@ -148,7 +148,7 @@ symv_finish_kernel(const double *__restrict__ rowpart, const double *__restrict_
  * row-wise (256-byte segments) and compared through a shared-memory transpose.  Any a_ij that
  * is not bit-identical to a_ji (NaNs included) raises *flag. */
 __global__ void __launch_bounds__(256)
-symmetry_check_kernel(const double *__restrict__ A, long long n, long long nb, int *flag)
+cgb_symmetry_check_kernel(const double *__restrict__ A, long long n, long long nb, int *flag)
 {
     /* blockIdx.x enumerates (bi, bj), bi <= bj, row-major over the upper block triangle */
     long long t = blockIdx.x, bi = 0, rowlen = nb;
@@ -210,11 +210,11 @@ extern "C" int cgk_symv(const double *A, const double *v, const double *w, doubl
     if (n % SY_T != 0 || ntiles < 1 || (split != 1 && split != 2 && split != 4)) return (int)cudaErrorInvalidValue;
     const int2 *tl = (const int2 *)tiles;
     switch (rows_in_flight) {
-    case 1: cgk_launch(symv_tile_kernel<1>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
-    case 2: cgk_launch(symv_tile_kernel<2>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
-    default: cgk_launch(symv_tile_kernel<4>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    case 1: cgk_launch(cgb_halfmat_tile_kernel<1>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    case 2: cgk_launch(cgb_halfmat_tile_kernel<2>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
+    default: cgk_launch(cgb_halfmat_tile_kernel<4>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)n, split); break;
     }
-    cgk_launch(symv_finish_kernel, dim3((unsigned)(n / SY_FR)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc, (long long)n, split);
+    cgk_launch(cgb_halfmat_finish_kernel, dim3((unsigned)(n / SY_FR)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc, (long long)n, split);
     return (int)cudaGetLastError();
 }
 
@@ -226,7 +226,7 @@ extern "C" int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void 
     const long long blocks = nb * (nb + 1) / 2;
     if (blocks > 2147483647LL) return (int)cudaErrorInvalidValue;
     cudaMemsetAsync(d_flag, 0, sizeof(int), (cudaStream_t)stream);
-    symmetry_check_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, nb, d_flag);
+    cgb_symmetry_check_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, nb, d_flag);
     return (int)cudaGetLastError();
 }
 
@@ -241,10 +241,10 @@ extern "C" int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void 
  *                    fixed order, stored into the owner's crecv[rank][...]; last CTA posts c_flag
  *   symv_finish_comm waits for the c_flags of the ranks that read blocks of MY columns, adds
  *                    row partials, own-block column partials and the received sums in a fixed
- *                    order; p.Ap partial pushed to every mailbox as in gemv_ldg_comm_kernel */
+ *                    order; p.Ap partial pushed to every mailbox as in cgb_rowblock_matvec_comm */
 template <int RU>
 __global__ void __launch_bounds__(SY_NT)
-symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 *__restrict__ tiles,
+cgb_halfmat_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 *__restrict__ tiles,
                       double *__restrict__ rowpart, double *__restrict__ colpart, cgk_scalars *sc,
                       long long m, long long n, int split, const cgk_peers peers)
 {
@@ -338,7 +338,7 @@ symv_tile_comm_kernel(const double *__restrict__ A, const double *p, const int2 
 /* grid: (m / SY_NT, nblk).  Column j of foreign block b: sum over the contributing local tile
  * rows, pushed into the owner's receive area.  The last CTA posts c_flag to every owner. */
 __global__ void __launch_bounds__(SY_NT)
-symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long m, long long n, int split,
+cgb_halfmat_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long m, long long n, int split,
                  const cgk_symplan sp, const cgk_peers peers)
 {
     pdl_wait();
@@ -371,7 +371,7 @@ symv_push_kernel(const double *__restrict__ colpart, cgk_scalars *sc, long long 
 }
 
 __global__ void __launch_bounds__(SY_NT)
-symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
+cgb_halfmat_finish_comm_kernel(const double *__restrict__ rowpart, const double *__restrict__ colpart,
                         const double *w, double *__restrict__ y, double *__restrict__ partials,
                         double *__restrict__ dot_out, cgk_scalars *sc, long long m, long long n, int split,
                         const cgk_symplan sp, const cgk_peers peers)
@@ -382,7 +382,7 @@ symv_finish_comm_kernel(const double *__restrict__ rowpart, const double *__rest
     const unsigned int ep = *(volatile unsigned int *)&sc->ep_gemv;
     const unsigned int gen = *(volatile unsigned int *)&sc->gen;
     /* 32 local rows per CTA; the 8 warps take every 8th term of the row's list of partials
-     * (as symv_finish_kernel: 8 x the CTAs, an 8 x shorter chain of loads per thread) */
+     * (as cgb_halfmat_finish_kernel: 8 x the CTAs, an 8 x shorter chain of loads per thread) */
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const long long mt = m / SY_T;
     const long long i = (long long)blockIdx.x * SY_FR + lane;                /* local row, < m */
@@ -497,13 +497,13 @@ extern "C" int cgk_symv_comm(const double *A, const double *v, const double *w, 
     if (split != 1 && split != 2 && split != 4) return (int)cudaErrorInvalidValue;
     const int2 *tl = (const int2 *)tiles;
     switch (rows_in_flight) {
-    case 1: cgk_launch(symv_tile_comm_kernel<1>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
-    case 2: cgk_launch(symv_tile_comm_kernel<2>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
-    default: cgk_launch(symv_tile_comm_kernel<4>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    case 1: cgk_launch(cgb_halfmat_tile_comm_kernel<1>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    case 2: cgk_launch(cgb_halfmat_tile_comm_kernel<2>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
+    default: cgk_launch(cgb_halfmat_tile_comm_kernel<4>, dim3((unsigned)ntiles), dim3(SY_NT), 0, st, A, v, tl, rowpart, colpart, sc, (long long)m, (long long)n, split, *peers); break;
     }
     if (sp->nblk > 0)
-        cgk_launch(symv_push_kernel, dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), dim3(SY_NT), 0, st, colpart, sc, (long long)m, (long long)n, split, *sp, *peers);
-    cgk_launch(symv_finish_comm_kernel, dim3((unsigned)(m / SY_FR)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc,
+        cgk_launch(cgb_halfmat_push_kernel, dim3((unsigned)(m / SY_NT), (unsigned)sp->nblk), dim3(SY_NT), 0, st, colpart, sc, (long long)m, (long long)n, split, *sp, *peers);
+    cgk_launch(cgb_halfmat_finish_comm_kernel, dim3((unsigned)(m / SY_FR)), dim3(SY_NT), 0, st, rowpart, colpart, w, y, partials, dot_out, sc,
                (long long)m, (long long)n, split, *sp, *peers);
     return (int)cudaGetLastError();
 }

@@ -140,8 +140,17 @@ typedef struct cgb_stats {
     int64_t h2d_bytes;         /* bytes the last cgb_load_host / cgb_load_host_symmetric copied    */
     int     pdl;               /* 1: the iteration kernels overlapped their launches (programmatic */
                                /* dependent launch; one rank, CGB_PDL=0 in the environment: off)   */
-    int     reserved_;
+    int     h2d_path;          /* CGB_H2D_*: how the last upload of A reached the GPU              */
 } cgb_stats;
+
+/* cgb_stats.h2d_path: the caller's A may be pinned (cudaHostAlloc / cudaHostRegister) or plain
+ * malloc memory as in the reference's main() (memAllocate(), serialConjugate.c:62-64,76-84) */
+#define CGB_H2D_NONE       0       /* nothing uploaded (generated on the device, or text ingest)  */
+#define CGB_H2D_DIRECT     1       /* pinned source: DMA straight out of the caller's buffer      */
+#define CGB_H2D_STAGED     2       /* pageable source: host threads pack it into a ring of pinned */
+                                   /* slots, one async copy per slot (cg_stage.c)                 */
+#define CGB_H2D_DRIVER     3       /* pageable source left to the driver (small, or CGB_STAGE=0)  */
+#define CGB_H2D_REGISTERED 4       /* pageable source pinned in place piece by piece (CGB_STAGE=register) */
 
 /* ---- debugging -------------------------------------------------------------- */
 /* With CGB_DEBUG_GUARDS=1 in the environment at cgb_create*(), every device array of the
@@ -174,7 +183,9 @@ int cgb_destroy(cgb_ctx *ctx);
 /* What MPI_Bcast(x0) + MPI_Scatter(A) + MPI_Scatter(b) deliver to a rank
  * (parallel_cg.c:111-115): the rank's m = n/ranks rows of A (row-major, m x n),
  * its m entries of b, and the FULL initial guess x0 (n).  Host buffers,
- * caller-owned, copied to the GPU (pinned buffers copy at PCIe rate). */
+ * caller-owned, copied to the GPU.  Pinned buffers are read in place by the DMA engine; plain
+ * malloc memory (what the reference's main() passes) goes through a multi-threaded ring of
+ * pinned staging slots so that it, too, moves at PCIe rate (cgb_stats.h2d_path says which). */
 int cgb_load_host(cgb_ctx *ctx, int64_t n, const double *A_rows, const double *b_rows,
                   const double *x0_full);
 /* cgb_load_host for a matrix the caller asserts to be symmetric (a_ij == a_ji bit for bit, as

@@ -47,17 +47,17 @@ def test_only_sm_100a_code():
 
 def test_every_kernel_family_is_present(sass):
     fam = {re.sub(r"<.*", "", k) for k in sass}
-    want = {"gemv_ldg_kernel", "gemv_ldg_keep_kernel", "gemv_ldg_comm_kernel", "gemv_bulk_kernel",
-            "xr_update_kernel", "p_update_kernel", "init_residual_kernel", "after_init_kernel", "reset_kernel",
-            "cg2_step_kernel", "cg2_step_one_kernel", "generate_A_kernel", "generate_b_kernel",
-            "symv_tile_kernel", "symv_tile_comm_kernel", "symv_finish_kernel", "symv_finish_comm_kernel",
-            "symv_push_kernel", "symmetry_check_kernel", "ingest_scan_kernel", "ingest_count_kernel",
-            "ingest_parse_kernel", "scatter_kernel", "l2_flush_kernel"}
+    want = {"cgb_rowblock_matvec_ldg", "cgb_rowblock_matvec_keep", "cgb_rowblock_matvec_comm", "cgb_rowblock_matvec_bulk",
+            "cgb_xr_update_kernel", "cgb_p_update_kernel", "cgb_init_residual_kernel", "cgb_after_init_kernel", "cgb_reset_kernel",
+            "cgb_cg2_step_kernel", "cgb_cg2_step_one_kernel", "cgb_generate_A_kernel", "cgb_generate_b_kernel",
+            "cgb_halfmat_tile_kernel", "cgb_halfmat_tile_comm_kernel", "cgb_halfmat_finish_kernel", "cgb_halfmat_finish_comm_kernel",
+            "cgb_halfmat_push_kernel", "cgb_symmetry_check_kernel", "cgb_ingest_scan_kernel", "cgb_ingest_count_kernel",
+            "cgb_ingest_parse_kernel", "cgb_place_values_kernel", "cgb_l2_flush_kernel"}
     assert want <= fam, want - fam
 
 
 def test_headline_gemv_streams_with_256_bit_evict_first_loads(sass):
-    body = sass["gemv_ldg_kernel<8,2,512,4>"]          # the n = 65536 default (profiles/r01_summary.md §2)
+    body = sass["cgb_rowblock_matvec_ldg<8,2,512,4>"]          # the n = 65536 default (profiles/r01_summary.md §2)
     o = ops(body)
     wide = [x for x in o if x.startswith("LDG.") and ".256" in x]
     # R * U = 16 independent 32-byte loads of A in flight per thread, all no-allocate + evict-first
@@ -70,8 +70,8 @@ def test_headline_gemv_streams_with_256_bit_evict_first_loads(sass):
 def test_default_gemv_shapes_do_not_spill(sass):
     # the shapes cgk_gemv_make_plan picks by itself (tests/test_plans.py); the register-capped keep
     # kernel and a few selectable 512-thread shapes carry 8-24 bytes of stack (profiles/r01_kernel_resources.txt)
-    for name in ("gemv_ldg_kernel<8,2,512,4>", "gemv_ldg_kernel<2,1,256,4>", "gemv_ldg_kernel<4,1,128,4>",
-                 "gemv_ldg_kernel<4,1,128,2>", "gemv_ldg_kernel<4,1,128,1>", "gemv_ldg_keep_kernel<2,1,256,4>"):
+    for name in ("cgb_rowblock_matvec_ldg<8,2,512,4>", "cgb_rowblock_matvec_ldg<2,1,256,4>", "cgb_rowblock_matvec_ldg<4,1,128,4>",
+                 "cgb_rowblock_matvec_ldg<4,1,128,2>", "cgb_rowblock_matvec_ldg<4,1,128,1>", "cgb_rowblock_matvec_keep<2,1,256,4>"):
         assert not any(x.startswith(("LDL", "STL")) for x in ops(sass[name])), name
 
 
@@ -88,7 +88,7 @@ def test_every_vw4_gemv_uses_256_bit_loads(sass):
 
 
 def test_bulk_variant_uses_the_tma_engine(sass):
-    bulk = {k: v for k, v in sass.items() if k.startswith("gemv_bulk_kernel<")}
+    bulk = {k: v for k, v in sass.items() if k.startswith("cgb_rowblock_matvec_bulk<")}
     assert len(bulk) >= 8
     for name, body in bulk.items():
         o = ops(body)
@@ -101,15 +101,15 @@ def test_bulk_variant_uses_the_tma_engine(sass):
 def test_iteration_kernels_carry_programmatic_dependent_launch(sass):
     # everything cg_kernels.cu / cg_symv.cu launch through cgk_launch (the attribute is only legal on
     # kernels that order themselves with griddepcontrol.wait)
-    for name in ("xr_update_kernel<false>", "p_update_kernel<false>", "cg2_step_one_kernel", "cg2_step_kernel<true>",
-                 "gemv_ldg_keep_kernel<4,1,128,4>", "gemv_ldg_comm_kernel<4,2,256,4>", "symv_tile_kernel<4>",
-                 "symv_finish_kernel", "symv_push_kernel"):
+    for name in ("cgb_xr_update_kernel<false>", "cgb_p_update_kernel<false>", "cgb_cg2_step_one_kernel", "cgb_cg2_step_kernel<true>",
+                 "cgb_rowblock_matvec_keep<4,1,128,4>", "cgb_rowblock_matvec_comm<4,2,256,4>", "cgb_halfmat_tile_kernel<4>",
+                 "cgb_halfmat_finish_kernel", "cgb_halfmat_push_kernel"):
         o = ops(sass[name])
         assert "ACQBULK" in o, name        # griddepcontrol.wait
         assert "PREEXIT" in o, name        # griddepcontrol.launch_dependents
         assert o.index("ACQBULK") < o.index("PREEXIT"), name     # wait first: completion stays transitive (cg_device.cuh)
     # the bandwidth-bound GEMV of large systems is launched the ordinary way and carries neither
-    o = ops(sass["gemv_ldg_kernel<8,2,512,4>"])
+    o = ops(sass["cgb_rowblock_matvec_ldg<8,2,512,4>"])
     assert "ACQBULK" not in o and "PREEXIT" not in o
 
 
@@ -122,9 +122,9 @@ def test_no_fp64_atomics_and_no_tensor_cores(sass):
 
 def test_peer_exchange_uses_system_scope_accesses(sass):
     # the kernels that push into peer windows fence at system scope, the consumers poll with sys loads
-    assert any(x == "MEMBAR.SC.SYS" for x in ops(sass["p_update_kernel<true>"]))
-    for name in ("xr_update_kernel<true>", "p_update_kernel<true>", "gemv_ldg_comm_kernel<4,2,256,4>"):
+    assert any(x == "MEMBAR.SC.SYS" for x in ops(sass["cgb_p_update_kernel<true>"]))
+    for name in ("cgb_xr_update_kernel<true>", "cgb_p_update_kernel<true>", "cgb_rowblock_matvec_comm<4,2,256,4>"):
         assert any(x.endswith("STRONG.SYS") and x.startswith("LDG") for x in ops(sass[name])), name
     # ... and the one-rank forms pay no system-scope fence
-    for name in ("xr_update_kernel<false>", "p_update_kernel<false>", "gemv_ldg_kernel<8,2,512,4>", "cg2_step_one_kernel"):
+    for name in ("cgb_xr_update_kernel<false>", "cgb_p_update_kernel<false>", "cgb_rowblock_matvec_ldg<8,2,512,4>", "cgb_cg2_step_one_kernel"):
         assert "MEMBAR.SC.SYS" not in ops(sass[name]), name

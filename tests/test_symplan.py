@@ -115,7 +115,7 @@ def test_numpy_emulation_of_the_three_kernels_gives_A_times_p(ranks, mt):
 @pytest.mark.parametrize("mt", [1, 2, 4, 16])
 @pytest.mark.parametrize("split", [1, 2, 4])
 def test_finish_kernels_split_the_partial_list_exactly_once(ranks, mt, split):
-    """symv_finish_comm_kernel (cg_symv.cu) walks the flat list [own block's row partials | each foreign
+    """cgb_halfmat_finish_comm_kernel (cg_symv.cu) walks the flat list [own block's row partials | each foreign
     block's | own column partials] with 8 warps at stride 8, carrying the offset from one segment into
     the next (k -= cnt).  Restated here: every term is visited by exactly one warp, whatever the
     segment lengths."""

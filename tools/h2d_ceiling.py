@@ -1,0 +1,126 @@
+#!/usr/bin/env python
+"""tools/h2d_ceiling.py -- what can this box move from host memory to HBM?
+
+One rank:   python tools/h2d_ceiling.py [--n 32768] [--sweep]
+            pinned source (the DMA ceiling), pageable source left to the driver (CGB_STAGE=0),
+            pageable source through the staging ring of cg_stage.c (threads x chunk sweep) and
+            pinned in place piece by piece (CGB_STAGE=register) -- all through cgb_load_host.
+N ranks:    python -m torch.distributed.run --nproc-per-node N ... tools/h2d_ceiling.py --n 32768
+            every subset the round-1 verdict asked for: all ranks at once, then the pairs (0,1), (0,2),
+            (0,4) alone (a shared PCIe uplink shows as a pair that halves), pinned and staged.
+Prints one JSON object (rank 0); nothing here is a bench value.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=32768)
+    ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--reps", type=int, default=2)
+    args = ap.parse_args()
+    import numpy as np
+    import torch
+    import conjugate_gradient_b200 as cg
+    from conjugate_gradient_b200 import _binding as B
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group(backend="gloo", rank=rank, world_size=world)
+    L = B.lib()
+    n = args.n
+    ctx = cg.Context(device=local)                 # every rank an independent one-rank context: only the copies matter
+    ctx.generate(n, 1)
+    hA_pin = torch.empty(n * n, dtype=torch.float64, pin_memory=True)
+    B._check(L.cgb_debug_read(ctx._h, 0, 0, n * n, hA_pin.data_ptr()))
+    hA = np.empty(n * n, dtype=np.float64)         # malloc / mmap'ed, pageable
+    hA[:] = hA_pin.numpy()
+    hb = np.zeros(n)
+    hx = np.zeros(n)
+    nbytes = 8.0 * n * n
+    dp = C.POINTER(C.c_double)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def upload(src_ptr, active=True, **env):
+        old = {k: os.environ.get(k) for k in env}
+        for k, v in env.items():
+            os.environ[k] = str(v)
+        best = 1e30
+        for _ in range(args.reps):
+            barrier()
+            if active:
+                t0 = time.perf_counter()
+                B._check(L.cgb_load_host(ctx._h, n, C.cast(src_ptr, dp), hb.ctypes.data_as(dp), hx.ctypes.data_as(dp)))
+                best = min(best, time.perf_counter() - t0)
+            barrier()
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+        return nbytes / best / 1e9 if active else 0.0
+
+    def gather(v):
+        if dist is None:
+            return [v]
+        out = [None] * world
+        dist.all_gather_object(out, v)
+        return out
+
+    res = {"n": n, "gb": nbytes / 1e9, "world": world, "cpus": len(os.sched_getaffinity(0))}
+    pin_ptr, pg_ptr = hA_pin.data_ptr(), hA.ctypes.data
+    if world == 1:
+        res["pinned"] = upload(pin_ptr)
+        res["pageable_driver"] = upload(pg_ptr, CGB_STAGE=0)
+        res["pageable_staged_default"] = upload(pg_ptr)
+        res["pageable_register"] = upload(pg_ptr, CGB_STAGE="register", CGB_STAGE_CHUNK_MB=64)
+        if args.sweep:
+            sw = {}
+            for t in (2, 4, 6, 8, 12, 16, 24, 32):
+                for mb in (2, 4, 8, 16, 32):
+                    sw[f"t{t}_c{mb}"] = round(upload(pg_ptr, CGB_STAGE_THREADS=t, CGB_STAGE_CHUNK_MB=mb), 2)
+            res["staged_sweep_gbs"] = sw
+            res["register_sweep_gbs"] = {f"t{t}_c{mb}": round(upload(pg_ptr, CGB_STAGE="register", CGB_STAGE_THREADS=t, CGB_STAGE_CHUNK_MB=mb), 2)
+                                         for t in (2, 4, 8) for mb in (32, 128)}
+    else:
+        res["all_pinned_gbs_per_gpu"] = gather(round(upload(pin_ptr), 2))
+        res["all_staged_gbs_per_gpu"] = gather(round(upload(pg_ptr), 2))
+        for t in (2, 4, 8):
+            res[f"all_staged_t{t}_gbs_per_gpu"] = gather(round(upload(pg_ptr, CGB_STAGE_THREADS=t), 2))
+        for pair in ((0, 1), (0, 2), (0, 4), (0, 7)):
+            if pair[1] < world:
+                res[f"pair{pair[0]}{pair[1]}_pinned"] = [v for v in gather(round(upload(pin_ptr, active=rank in pair), 2)) if v]
+        res["solo_pinned"] = [v for v in gather(round(upload(pin_ptr, active=rank == 0), 2)) if v]
+    if rank == 0:
+        try:
+            import subprocess
+            res["lscpu"] = [l.strip() for l in subprocess.run(["lscpu"], capture_output=True, text=True).stdout.splitlines()
+                            if any(k in l for k in ("Model name", "Socket", "NUMA", "Core(s)", "Thread(s)", "CPU(s):"))]
+            res["mem_gb"] = os.sysconf("SC_PAGE_SIZE") * os.sysconf("SC_PHYS_PAGES") / 1e9
+        except Exception:
+            pass
+        print(json.dumps(res), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

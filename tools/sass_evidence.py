@@ -29,9 +29,9 @@ for nm, body in zip(names, parts[2::2]):
     nm = nm[:nm.index("(")] if "(" in nm else nm
     ops = re.findall(r"^\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", body, flags=re.M)
     rows.append((nm, [sum(1 for o in ops if re.match(rx, o)) for _, rx in COLS]))
-keep = lambda nm: not nm.startswith("gemv_ldg_kernel<") or nm.replace(" ", "") in (
-    "gemv_ldg_kernel<8,2,512,4>", "gemv_ldg_kernel<2,1,256,4>", "gemv_ldg_kernel<4,1,128,4>", "gemv_ldg_kernel<4,1,128,2>", "gemv_ldg_kernel<4,1,128,1>")
+keep = lambda nm: not nm.startswith("cgb_rowblock_matvec_ldg<") or nm.replace(" ", "") in (
+    "cgb_rowblock_matvec_ldg<8,2,512,4>", "cgb_rowblock_matvec_ldg<2,1,256,4>", "cgb_rowblock_matvec_ldg<4,1,128,4>", "cgb_rowblock_matvec_ldg<4,1,128,2>", "cgb_rowblock_matvec_ldg<4,1,128,1>")
 for nm, counts in sorted(rows):
     if keep(nm):
         print(nm + " | " + " | ".join(str(c) for c in counts))
-print(f"# ({sum(1 for nm, _ in rows if not keep(nm))} further selectable gemv_ldg_kernel<R,U,NT,VW> shapes omitted; the five listed are the ones the plan picks by itself)")
+print(f"# ({sum(1 for nm, _ in rows if not keep(nm))} further selectable cgb_rowblock_matvec_ldg<R,U,NT,VW> shapes omitted; the five listed are the ones the plan picks by itself)")
