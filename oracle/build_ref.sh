@@ -17,12 +17,12 @@
 #   libparallel_<p>_n<N>.so    its conjugrad(A,b,x,m,rank,np) + the shim
 #   libp2p_<p>_n<N>.so         the same from point-to-point_cg.c (MPI_Send / MPI_Recv through rank 0)
 # Flags: gcc -O2 (no -march: no FMA contraction, matching a stock x86-64 build).
-# Usage: oracle/build_ref.sh [n ...]      default: 2 4 512 2048 16384
+# Usage: oracle/build_ref.sh [n ...]      default: 2 4 512 2048 8192 16384
 set -euo pipefail
 here="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
 ref="${CG_REFERENCE_DIR:-/root/reference}"
 out="$here/_ref"
-sizes=("$@"); [ ${#sizes[@]} -eq 0 ] && sizes=(2 4 512 2048 16384)
+sizes=("$@"); [ ${#sizes[@]} -eq 0 ] && sizes=(2 4 512 2048 8192 16384)
 if [ ! -f "$ref/serialConjugate.c" ] || [ ! -f "$ref/parallel_cg.c" ]; then
   echo "build_ref: $ref not present; keeping prebuilt oracle/_ref as is" >&2
   exit 0

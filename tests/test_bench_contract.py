@@ -67,6 +67,25 @@ def test_reference_arm_line_has_the_contract_keys():
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["value"] == d["value"] and cb["cores"] >= 1 and "1024" in cb["sample"]
     assert "workload" in d["config"] and "model" not in d["config"]
+    assert d["config"] == bench.workload_config(1024, 1)              # the same dict the B200 arm emits
+    assert d["warmup"] == 1 and d["implementation"]["steps_run"] == 4
+
+
+def test_reference_timer_line_is_parsed():
+    assert bench.reference_timer_seconds("Computing\naverage clock execution time in seconds: 0.562000\n") == pytest.approx(0.562)
+    assert bench.reference_timer_seconds("cg method execution time in seconds: 0.234\nclock execution time in seconds: 16.0\n") == pytest.approx(0.234)
+    assert bench.reference_timer_seconds("nothing") is None
+
+
+def test_cpu_rows_child_uses_the_real_reference_timers():
+    import _oracle as O
+    if not O.ref_available("serial", "f64", 8192):
+        pytest.skip("oracle/_ref has no n = 8192 build here")
+    rows = bench.cpu_reference_rows()
+    names = [r["name"] for r in rows]
+    assert names[:2] == ["serial_f32_1core", "serial_f64_1core"] and "spmd_np2" in names
+    for r in rows:
+        assert r["kind"] == "reference" and r["n"] == 8192 and r["value"] > 0 and "own" in r["timer"]
 
 
 def test_clock_sample_parser(tmp_path):
@@ -89,29 +108,6 @@ def test_clock_sample_parser(tmp_path):
     lo = bench.ClockSampler._ts("2026/11/04 10:00:01.000")
     out = s.stop(lo, lo + 0.05)
     assert out == {"sm_mhz": 1965.0, "sm_max_mhz": 1965.0, "reasons": ["sw_power_cap"], "samples": 3}
-
-
-def test_numa_local_binds_and_restores(tmp_path):
-    assert bench.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
-    assert bench.parse_cpulist("") == set() and bench.parse_cpulist("a-b") == set()
-    before = os.sched_getaffinity(0)
-    dev = tmp_path / "0000:1b:00.0"
-    dev.mkdir()
-    first = min(before)
-    (dev / "local_cpulist").write_text(f"{first}\n")
-    with bench.NumaLocal(0, 0x1b, 0, sysfs=str(tmp_path)) as nl:
-        if len(before) > 1:
-            assert os.sched_getaffinity(0) == {first} and nl.bound == 1
-        else:
-            assert nl.bound == 0                                   # nothing narrower to bind to
-    assert os.sched_getaffinity(0) == before
-    # no sysfs entry, or a CPU list outside the container's cpuset: the process is left alone
-    with bench.NumaLocal(0, 0x99, 0, sysfs=str(tmp_path)) as nl:
-        assert nl.bound == 0 and os.sched_getaffinity(0) == before
-    (dev / "local_cpulist").write_text("100000-100003\n")
-    with bench.NumaLocal(0, 0x1b, 0, sysfs=str(tmp_path)) as nl:
-        assert nl.bound == 0 and os.sched_getaffinity(0) == before
-    assert os.sched_getaffinity(0) == before
 
 
 # The two stub tests below patch torch and the binding; they run in a fresh interpreter so that nothing they
@@ -148,21 +144,28 @@ def test_stub_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
             opt = C.cast(o, C.POINTER(B.Options)).contents
             s = C.cast(st, C.POINTER(B.Stats)).contents
             s.iterations = opt.max_iter if opt.ignore_stop else 4
-            s.h2d_seconds, s.solve_seconds, s.h2d_bytes = 0.5, 0.1, 8 * (m * 64) // (2 if opt.symmetric == 2 else 1)
-            calls.append(("solve", int(opt.symmetric), int(opt.ignore_stop)))
+            s.h2d_seconds, s.solve_seconds = 0.5, 0.1
+            s.h2d_bytes = 8 * (m * 64 + m + 64) // (2 if opt.symmetric == 2 else 1)
+            s.h2d_path = 1 if A in pinned_ptrs else 2
+            calls.append(("solve", int(opt.symmetric), int(opt.ignore_stop), int(s.h2d_path)))
             return 0
 
         def cgb_default_options(self, o):
             return None
 
-    real_empty, real_zeros = torch.empty, torch.zeros
-    monkeypatch.setattr(torch, "empty", lambda *a, pin_memory=False, **k: real_empty(*a, **k))
-    monkeypatch.setattr(torch, "zeros", lambda *a, pin_memory=False, **k: real_zeros(*a, **k))
+    real_empty = torch.empty
+    pinned_ptrs = set()
+
+    def fake_empty(*a, pin_memory=False, **k):
+        t = real_empty(*a, **k)
+        if pin_memory:
+            pinned_ptrs.add(t.data_ptr())
+            keep.append(t)
+        return t
+    keep = []
+    monkeypatch.setattr(torch, "empty", fake_empty)
     monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
-    monkeypatch.setattr(torch.cuda, "get_device_properties",
-                        lambda i: types.SimpleNamespace(pci_domain_id=0, pci_bus_id=0x1b, pci_device_id=0))
     monkeypatch.setattr(B, "lib", lambda: StubLib())
-    before = os.sched_getaffinity(0)
     n = m = 64
     K = 20
     line = {"symmetric_variant": {}, "time_to_solution": {}}
@@ -171,13 +174,14 @@ def test_stub_e2e_leg_runs_end_to_end_against_a_stub_library(monkeypatch):
     e = line["e2e"]
     assert e["unit"] == bench.UNIT and e["value"] > 0 and e["iterations"] == K
     assert e["h2d_bytes_per_step"] == 8.0 * (m * n + m + n) / K and e["d2h_bytes_per_step"] == 8.0 * n / K
-    assert "host_buffers" in e and "api" in e
+    assert "malloc" in e["api"] and e["h2d_path"].startswith("staged") and e["h2d_frac_of_pinned"] == pytest.approx(1.0)
+    assert line["e2e_pinned"]["h2d_path"].startswith("direct") and line["e2e_pinned"]["value"] > 0
     assert line["symmetric_variant"]["e2e"]["value"] > 0
     assert line["time_to_solution"]["e2e_iterations"] == 4
-    # A and b read back once; two plain calls, two asserted-symmetric calls, one converging solve
+    # A and b read back once; two calls on malloc'ed buffers (the headline), two on pinned ones, two
+    # asserted-symmetric calls and one converging solve on malloc'ed buffers again
     assert [c for c in calls if c[0] == "read"] == [("read", 0, m * n), ("read", 1, m)]
-    assert [c[1:] for c in calls if c[0] == "solve"] == [(0, 1), (0, 1), (2, 1), (2, 1), (0, 0)]
-    assert os.sched_getaffinity(0) == before
+    assert [c[1:] for c in calls if c[0] == "solve"] == [(0, 1, 2), (0, 1, 2), (0, 1, 1), (0, 1, 1), (2, 1, 2), (2, 1, 2), (0, 0, 2)]
 
 
 @pytest.mark.skipif(not IN_CHILD, reason="runs inside test_fresh_interpreter_runs_both_legs_on_stubs")
@@ -201,6 +205,10 @@ def test_stub_b200_arm_line_against_a_stub_context(monkeypatch):
         def set_x0(self, x):
             pass
 
+        def read_x(self):
+            import numpy as np
+            return np.zeros(self.n)
+
         def close(self):
             pass
 
@@ -221,7 +229,9 @@ def test_stub_b200_arm_line_against_a_stub_context(monkeypatch):
     for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
         monkeypatch.delenv(k, raising=False)
     args = types.SimpleNamespace(gpus=1, steps=20, warmup=3, n=65536, gemv=0, comm="auto", rows=0, unroll=0, threads=0, l2_keep=0)
-    ctx, line, env = bench.b200_arm(args)
+    ctx, line, env, conv = bench.b200_arm(args)
+    assert conv[0]["iterations"] == 4 and conv[1].shape == (65536,)
+    assert line["config"] == bench.workload_config(65536, 1) and "gemv_kernel" in line["implementation"]
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
               "dtype", "data", "config", "roofline", "clocks", "gpu_launches"):
         assert k in line, k
@@ -235,3 +245,42 @@ def test_stub_b200_arm_line_against_a_stub_context(monkeypatch):
     assert ctx.solves[0]["max_iter"] == 3 and ctx.solves[1]["max_iter"] == 20 and ctx.solves[1]["time_gemv"] == 1
     assert "symmetric_variant" in line and "fused_reductions_variant" in line
     json.dumps(line)                                         # serialisable as ONE line
+
+
+def test_parity_leg_accepts_the_oracle_and_rejects_a_wrong_answer():
+    """bench.parity_leg on a stand-in context that answers with the oracle's own x (serial order: differs from the
+    threaded SPMD order in the last bits only) must report ok; the same x with one entry off by 1e-6 must not."""
+    import types
+    import numpy as np
+    import _oracle as O
+    n, K = 512, 20
+    A, b = O.gen_A(n, bench.SEED), O.gen_b(n, bench.SEED)
+    x_fix, s_fix = O.conjugrad(A, b, np.zeros(n), ignore_stop=True, max_iter=10)
+    x_conv, s_conv = O.conjugrad(A, b, np.zeros(n))
+
+    class Ctx:
+        def __init__(self, bump):
+            self.bump = bump
+
+        def set_x0(self, x):
+            pass
+
+        def solve(self, **kw):
+            return {"first_hit_k": s_fix["first_hit_k"], "iterations": 10}
+
+        def read_x(self):
+            x = x_fix.copy()
+            x[7] += self.bump
+            return x
+
+    args = types.SimpleNamespace(cpu_threads=2, no_cpu=False)
+    env = (0, 1, 0, n, n, K, lambda: None, float, {}, None)
+    conv = ({"iterations": s_conv["iterations"], "final_residual": float(np.sqrt(s_conv["final_beta"]))}, x_conv)
+    line = {}
+    assert bench.parity_leg(Ctx(0.0), line, env, conv, args) is True
+    p = line["parity"]
+    assert p["ok"] and p["fixed_run"]["iterations"] == 10 and p["fixed_run"]["rel_err_x"] <= 1e-12
+    assert p["converging_solve"]["iterations"]["gpu"] == p["converging_solve"]["iterations"]["oracle"]
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] == 2
+    line = {}
+    assert bench.parity_leg(Ctx(1e-6), line, env, conv, args) is False and line["parity"]["ok"] is False

@@ -411,12 +411,55 @@ def test_full_size_gemv_properties(ctx):
     assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
 
 
-@pytest.mark.parametrize("n", [65536, 131072])
-def test_baseline_sizes_through_size_independent_properties(ctx, n):
-    """BASELINE.json configs[3] and [4] (34 GB / 137 GB): no oracle pass at these sizes (a CPU matVec
-    streams the whole matrix), so: the solve converges in the iteration count the family always needs;
-    b - A x is small on sampled rows recomputed on the CPU from the generator twin; the symmetric
-    product gives the same solution; a fixed-iteration run reproduces itself bit for bit."""
+def test_baseline_size_vs_oracle_65536(ctx):
+    """BASELINE.json configs[3] (n = 65536, 34 GB), the size the metric is quoted on, against the CPU oracle itself:
+    the threaded row-block form of the port (parallel_cg.c:283-323, bit-identical to the real reference wherever the
+    real reference can run) regenerates the same matrix from the seed and streams it ~0.3 s per iteration on 16
+    cores.  Converged solve: relative error of x <= 1e-10, iteration count within +-1, residual below eps; and x
+    after 10 fixed iterations (the bench's mode), where the GEMV's summation order over 65536 columns has had ten
+    products to show.  The symmetric product and bitwise reproducibility are checked on the same resident matrix."""
+    n, seed = 65536, 20170209
+    info = ctx.device_info()
+    if info["total_bytes"] < 8 * n * n + (4 << 30):
+        pytest.skip("GPU memory too small for this size")
+    import os
+    threads = 1
+    while threads * 2 <= (os.cpu_count() or 1) and threads < 64:
+        threads *= 2
+    ctx.generate(n, seed)
+    st = ctx.solve()
+    x = ctx.read_x()
+    xo, so = O.team_solve_generated(n, seed, threads)
+    assert st["final_residual"] < EPS and st["exit_reason"] == 1
+    assert abs(st["iterations"] - so["iterations"]) <= 1
+    if st["iterations"] == so["iterations"]:
+        assert relerr(x, xo) <= RTOL_X, relerr(x, xo)
+        assert np.sqrt(so["final_beta"]) < EPS
+    ctx.set_x0(np.zeros(n))
+    st10 = ctx.solve(ignore_stop=1, max_iter=10)
+    x10 = ctx.read_x()
+    xo10, so10 = O.team_solve_generated(n, seed, threads, ignore_stop=True, max_iter=10)
+    assert relerr(x10, xo10) <= RTOL_X, relerr(x10, xo10)
+    assert st10["first_hit_k"] == so10["first_hit_k"]
+    # the symmetric product on the same matrix: same solution
+    ctx.set_x0(np.zeros(n))
+    sts = ctx.solve(symmetric=1)
+    assert sts["gemv_variant"] == 3 and abs(sts["iterations"] - so["iterations"]) <= 1
+    assert relerr(ctx.read_x(), xo) <= RTOL_X
+    # run-to-run bitwise reproducibility of the fixed-iteration mode
+    ctx.set_x0(np.zeros(n))
+    ctx.solve(ignore_stop=1, max_iter=10)
+    np.testing.assert_array_equal(ctx.read_x(), x10)
+    ctx.generate(512, 1)                      # release the big block for the tests that follow
+
+
+def test_baseline_size_131072_through_size_independent_properties(ctx):
+    """BASELINE.json configs[4] (137 GB): the oracle would need 137 GB of host memory and ~6 s per product on the
+    bench box's 16 cores (196 GB of RAM there, but not on every box), so this size -- and only this one -- is held
+    to size-independent properties: the solve converges in the iteration count the family always needs; b - A x is
+    small on sampled rows recomputed on the CPU from the generator twin; the symmetric product gives the same
+    solution; a fixed-iteration run reproduces itself bit for bit.  n = 65536 has the oracle pass above."""
+    n = 131072
     info = ctx.device_info()
     if info["total_bytes"] < 8 * n * n + (4 << 30):
         pytest.skip("GPU memory too small for this size")
