@@ -127,6 +127,7 @@ def lib():
         "cgb_load_host_symmetric": ([vp, i64, vp, vp, vp], C.c_int),
         "cgb_debug_check_guards": ([vp], C.c_int),
         "cgb_debug_poke": ([vp, C.c_int, i64, C.c_double], C.c_int),
+        "cgb_debug_probe_read": ([vp, vp, i64], i64),
         "cgb_load_text": ([vp, i64, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
         "cgb_conjugrad_files": ([C.c_char_p, C.c_char_p, C.c_char_p, i64, C.c_int, op, vp, sp], C.c_int),
         "cgb_generate": ([vp, i64, u64, C.c_uint], C.c_int), "cgb_set_x0": ([vp, vp], C.c_int),
@@ -334,6 +335,15 @@ class Context:
 
     def debug_poke(self, what, offset, value):
         _check(lib().cgb_debug_poke(self._h, what, offset, value))
+
+    def probe_read(self):
+        """CGB_PROBE=1: the exchange kernels' per-CTA time stamps of their last launch, as an (N, 8) uint64 array."""
+        words = 8 * (16384 + 2 * 592)
+        out = np.zeros(words, dtype=np.uint64)
+        got = lib().cgb_debug_probe_read(self._h, out.ctypes.data, words)
+        if got < 0:
+            _check(int(got))
+        return out[:got].reshape(-1, 8)
 
     def debug_read(self, what, offset, count):
         out = np.empty(count, dtype=np.float64)

@@ -23,6 +23,9 @@ template <> struct Ld<1> {
     static __device__ __forceinline__ void coherent(const double *p, double (&o)[1]) {
         asm volatile("ld.global.f64 %0, [%1];" : "=d"(o[0]) : "l"(p) : "memory");
     }
+    static __device__ __forceinline__ void plain(const double *p, double (&o)[1]) {
+        asm("ld.global.f64 %0, [%1];" : "=d"(o[0]) : "l"(p));
+    }
 };
 template <> struct Ld<2> {
     static __device__ __forceinline__ void stream(const double *p, double (&o)[2]) {
@@ -36,6 +39,9 @@ template <> struct Ld<2> {
     }
     static __device__ __forceinline__ void coherent(const double *p, double (&o)[2]) {
         asm volatile("ld.global.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p) : "memory");
+    }
+    static __device__ __forceinline__ void plain(const double *p, double (&o)[2]) {
+        asm("ld.global.v2.f64 {%0,%1}, [%2];" : "=d"(o[0]), "=d"(o[1]) : "l"(p));
     }
 };
 template <> struct Ld<4> {      /* 256-bit LDG: new on sm_100 */
@@ -70,7 +76,23 @@ template <> struct Ld<4> {      /* 256-bit LDG: new on sm_100 */
         o[0] = __longlong_as_double(a); o[1] = __longlong_as_double(b);
         o[2] = __longlong_as_double(c); o[3] = __longlong_as_double(d);
     }
+    /* the same ordinary (not .nc) load without the compiler barrier: free to be scheduled among
+     * the loads of A.  Ordering against a preceding flag acquire is kept by address dependency:
+     * the caller launders the base pointer through an `asm volatile` placed after the acquire
+     * (order_after_acquire below), so no such load can be hoisted above it. */
+    static __device__ __forceinline__ void plain(const double *p, double (&o)[4]) {
+        unsigned long long a, b, c, d;
+        asm("ld.global.v4.b64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+        o[0] = __longlong_as_double(a); o[1] = __longlong_as_double(b);
+        o[2] = __longlong_as_double(c); o[3] = __longlong_as_double(d);
+    }
 };
+__device__ __forceinline__ const double *order_after_acquire(const double *p)
+{
+    asm volatile("" : "+l"(p) : : "memory");
+    return p;
+}
 
 /* Programmatic dependent launch (one rank; cgk_set_pdl): a kernel launched with the attribute
  * may start while its predecessor in the stream is still running.  Rule kept by every kernel
@@ -221,6 +243,12 @@ __device__ __forceinline__ unsigned long long global_ns(void)
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
+__device__ __forceinline__ unsigned int sm_id(void)
+{
+    unsigned int v;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(v));
+    return v;
+}
 /* tag of exchange event e of solve generation gen (never 0 for gen & 0x3ff != 0) */
 __device__ __forceinline__ unsigned int cgk_tag(unsigned int gen, unsigned int e)
 {
@@ -305,6 +333,41 @@ __device__ __forceinline__ void warp_wait_p_flags(const cgk_peers &peers, unsign
         (void)ld_acquire_sys(f);
     }
     __syncwarp();
+}
+/* The same wait for a CTA that asked for the flags long ago.  `early` is what lane g's relaxed load of
+ * p_flag[g] returned when it was issued at kernel entry (lanes >= G and the own rank: the tag itself);
+ * by now -- the own column block is done -- the value is in a register, so the test costs no memory
+ * round trip.  Only a warp that still sees an old tag polls (the first wave).  Returns 0 in every lane,
+ * computed FROM the observed flag words: the caller adds it to the base address of its loads of p, so
+ * those loads cannot issue before the flag values have arrived (a true address dependency -- the
+ * hardware's ordering, with no fence and no second load), and the peer's fence.sys put its slice in
+ * this GPU's memory before the flag. */
+__device__ __forceinline__ unsigned int warp_flags_ready(const cgk_peers &peers, unsigned int tag, unsigned long long early,
+                                                         cgk_scalars *sc)
+{
+    const int g = threadIdx.x & 31;
+    const bool mine = g < peers.ranks && g != peers.rank;
+    unsigned long long seen = mine ? early : (unsigned long long)tag;
+    if (__any_sync(0xffffffffu, seen != (unsigned long long)tag)) {
+        if (mine && seen != (unsigned long long)tag) {
+            const unsigned long long *f = &peers.mbox[peers.rank]->p_flag[g];
+            unsigned long long t0 = 0ull;
+            unsigned int polls = 0;
+            while ((seen = ld_relaxed_sys(f)) != (unsigned long long)tag)
+                if ((++polls & 1023u) == 0u && spin_give_up(&t0, sc)) { seen = (unsigned long long)tag; break; }
+            (void)ld_acquire_sys(f);
+        }
+        __syncwarp();
+    }
+    const unsigned long long d = seen ^ (unsigned long long)tag;              /* 0 */
+    return __reduce_or_sync(0xffffffffu, (unsigned int)d | (unsigned int)(d >> 32));
+}
+/* lane g's early request for p_flag[g] (see warp_flags_ready) */
+__device__ __forceinline__ unsigned long long flags_request(const cgk_peers &peers, unsigned int tag)
+{
+    const int g = threadIdx.x & 31;
+    if (g < peers.ranks && g != peers.rank) return ld_relaxed_sys(&peers.mbox[peers.rank]->p_flag[g]);
+    return (unsigned long long)tag;
 }
 /* cta_partials_finish for kernels that stored into peer memory: thread 0's fence is
  * system-scope and cumulative over the CTA's stores (all before the preceding barrier), so

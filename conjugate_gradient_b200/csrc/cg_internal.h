@@ -15,7 +15,7 @@ struct cgb_graph_key {
     const void *win;        /* peer window the captured kernels point into */
     int comm, guard;
     int symv, symv_ru, symv_split, cg_variant;
-    int n_dot, defer_rr, pdl;
+    int n_dot, defer_rr, pdl, xrp;
 };
 
 /* Largest matrix order the entry points accept: n * n * 8 must stay far inside size_t / int64_t
@@ -26,6 +26,7 @@ struct cgb_graph_key {
 
 /* pageable host memory -> HBM (cg_stage.c) */
 #define CGB_STAGE_MAX_THREADS 32
+#define CGB_STAGE_REGISTER_FROM_RANKS 4
 typedef struct cgb_stage_run {      /* rows of `width` bytes: host rows `spitch` apart, device rows `dpitch` apart */
     void *dst; const void *src;
     size_t width, rows, dpitch, spitch;
@@ -65,6 +66,7 @@ struct cgb_ctx {
     int64_t graph_launches;           /* kernels per replay of the captured graph */
     int n_dot, defer_rr;              /* deferred reductions of the current solve (cg_kernels.h) */
     int pdl;                          /* iteration kernels launched with programmatic dependent launch */
+    int use_xrp;                      /* peer exchange: xr_update and p_update as one launch (cgk_xrp_update) */
     /* peer-memory exchange (ranks > 1): this rank's window [cgk_mailbox | p_full], the peers'
      * windows as mapped here (same-process peer access or CUDA IPC), and the table the kernels get */
     void *win;
@@ -73,6 +75,7 @@ struct cgb_ctx {
     int peer_ipc[CGK_MAX_RANKS];      /* 1: opened with cudaIpcOpenMemHandle (close it)  */
     int peer_ok;                      /* every rank mapped every window                  */
     cgk_peers peers;
+    unsigned long long *probe;        /* CGB_PROBE=1: per-CTA time stamps of the exchange kernels (CGK_PROBE_WORDS) */
     unsigned int gen;                 /* solve generation, in lockstep on all ranks      */
     int comm_mode;                    /* CGB_COMM_* in use by the current / last solve   */
     char peer_why[160];               /* why peer_ok == 0                                */
@@ -103,6 +106,7 @@ int cgb_ensure_problem(cgb_ctx *c, int64_t n);
 /* cg_stage.c */
 int  cgb_host_is_pageable(const void *p);
 int  cgb_stage_mode(void);
+int  cgb_stage_mode_for(int ranks);
 int  cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int pageable, int *path_out);
 void cgb_stage_release(cgb_ctx *c);
 

@@ -230,6 +230,28 @@ cgb_rowblock_matvec_keep(const double *__restrict__ A, const double *__restrict_
     cta_partials_finish<NT>(contrib, partials, dot_out, &sc->ticket_gemv);
 }
 
+/* One full tile of the exchange-fused kernel: columns c + u*STEP (u < U) of the CTA's R rows,
+ * p first, then A, as in gemv_accumulate; p with ordinary loads (peers write other parts of it). */
+template <int R, int U, int NT, int VW>
+__device__ __forceinline__ void comm_tile(double (&acc)[R], const double *const (&a)[R], const double *v, long long c)
+{
+    constexpr long long STEP = (long long)NT * VW;
+    double pv[U][VW];
+    double av[R][U][VW];
+#pragma unroll
+    for (int u = 0; u < U; ++u) Ld<VW>::plain(v + c + u * STEP, pv[u]);
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int u = 0; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int e = 0; e < VW; ++e)
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u][e], pv[u][e], acc[r]);
+}
+
 /* The same product with the p exchange fused in (row-sharded A, ranks > 1; replaces
  * MPI_Allgather + matVec + vecVec + MPI_Allreduce, parallel_cg.c:290-294).  Order of work in
  * a CTA: (1) the rank's own column block, whose slice of p this GPU's p-update kernel wrote
@@ -273,32 +295,64 @@ cgb_rowblock_matvec_comm(const double *__restrict__ A, const double *v,
     const unsigned int tag = cgk_tag(gen, ep);
     constexpr long long STEP = (long long)NT * VW;
     constexpr long long TILE = STEP * U;
+    /* CGB_PROBE=1 only: thread 0 leaves time stamps (layout in cg_kernels.h); NULL otherwise */
+    unsigned long long *pb = (peers.probe && tid == 0 && blockIdx.x < CGK_PROBE_MAX_PRODUCT_CTAS) ? peers.probe + 8ull * blockIdx.x : nullptr;
+    if (pb) { pb[0] = global_ns(); pb[5] = sm_id(); pb[6] = ep; pb[7] = 1ull; }
     if (m % TILE == 0) {
-        /* One uninterrupted loop over the columns in wrapped order lo, lo+TILE, ..., n-TILE,
-         * 0, ..., lo-TILE: tiles never straddle a block boundary.  The flag check sits AFTER
-         * the tile's loads of A are issued (A is local and never waits) and before its loads
-         * of p, so it costs nothing once the flags are there (every CTA but the first wave)
-         * and the first wave polls with its loads in flight.  Warp-level: lanes g < G poll,
-         * __syncwarp orders the other lanes behind the acquire. */
+        /* The columns in wrapped order lo, lo+TILE, ..., n-TILE, 0, ..., lo-TILE (tiles never
+         * straddle a block boundary), as three pieces: the own block -- the plain kernel's loop;
+         * ONE tile at which the peers' flags are tested, with its first loads of A already issued
+         * (A is local and never waits); the remaining remote tiles -- the plain loop again.
+         * The flags were REQUESTED at kernel entry (one relaxed load per lane g < G, nobody waits
+         * for it), so for every CTA but the first wave the test is a register compare: round 2's
+         * probes (tools/probe_exchange.py) showed the former poll + acquire at this point costing
+         * ~1.4 us in every one of the 8192 CTAs, flags long set -- 1 % of the kernel.  The loads
+         * of p that follow take their address from the flag words (warp_flags_ready). */
+        const unsigned long long early = flags_request(peers, tag);
         const long long tiles = n / TILE;
         const long long local_tiles = m / TILE;
         long long c = lo + (long long)tid * VW;
-        for (long long k = 0; k < tiles; ++k) {
-            double pv[U][VW];
-            double av[R][U][VW];
+        for (long long k = 0; k < local_tiles; ++k) {
+            comm_tile<R, U, NT, VW>(acc, a, v, c);
+            c += TILE;
+        }
+        if (c >= n) c -= n;
+        const double *vq = v;
+        if (local_tiles < tiles) {
+            double pv0[VW];
+            double av0[R][VW];
 #pragma unroll
-            for (int r = 0; r < R; ++r)
+            for (int r = 0; r < R; ++r) Ld<VW>::stream(a[r] + c, av0[r]);
+            long long w0 = 0;
+            if (pb) { pb[1] = global_ns(); w0 = clock64(); }
+            vq = order_after_acquire(vq + warp_flags_ready(peers, tag, early, sc));
+            if (pb) { pb[4] = (unsigned long long)(clock64() - w0); pb[2] = global_ns(); }
+            Ld<VW>::plain(vq + c, pv0);
 #pragma unroll
-                for (int u = 0; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u]);
-            if (k == local_tiles) warp_wait_p_flags(peers, tag, sc);
+            for (int e = 0; e < VW; ++e)
 #pragma unroll
-            for (int u = 0; u < U; ++u) Ld<VW>::coherent(v + c + u * STEP, pv[u]);
+                for (int r = 0; r < R; ++r) acc[r] = fma(av0[r][e], pv0[e], acc[r]);
+            if constexpr (U > 1) {
+                double pv[U - 1][VW];
+                double av[R][U - 1][VW];
 #pragma unroll
-            for (int u = 0; u < U; ++u)
+                for (int u = 1; u < U; ++u) Ld<VW>::plain(vq + c + u * STEP, pv[u - 1]);
 #pragma unroll
-                for (int e = 0; e < VW; ++e)
+                for (int r = 0; r < R; ++r)
 #pragma unroll
-                    for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u][e], pv[u][e], acc[r]);
+                    for (int u = 1; u < U; ++u) Ld<VW>::stream(a[r] + c + u * STEP, av[r][u - 1]);
+#pragma unroll
+                for (int u = 1; u < U; ++u)
+#pragma unroll
+                    for (int e = 0; e < VW; ++e)
+#pragma unroll
+                        for (int r = 0; r < R; ++r) acc[r] = fma(av[r][u - 1][e], pv[u - 1][e], acc[r]);
+            }
+            c += TILE;
+            if (c >= n) c -= n;
+        }
+        for (long long k = local_tiles + 1; k < tiles; ++k) {
+            comm_tile<R, U, NT, VW>(acc, a, vq, c);
             c += TILE;
             if (c >= n) c -= n;
         }
@@ -310,6 +364,7 @@ cgb_rowblock_matvec_comm(const double *__restrict__ A, const double *v,
         gemv_accumulate<R, U, NT, VW, true>(acc, a, v, hi, n, tid);
     }
 
+    if (pb) pb[3] = global_ns();
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         acc[r] = warp_sum(acc[r]);
@@ -619,10 +674,15 @@ cgb_xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
     if (*(volatile int *)&sc->stop_req) return;
     unsigned int ep = 0u, gen = 0u;
     double pAp;
+    unsigned long long *pb = nullptr;
     if constexpr (COMM) {
         ep = *(volatile unsigned int *)&sc->ep_xr;
         gen = *(volatile unsigned int *)&sc->gen;
+        if (peers.probe && threadIdx.x == 0 && blockIdx.x < CGK_PROBE_VEC_CTAS) pb = peers.probe + 8ull * (CGK_PROBE_MAX_PRODUCT_CTAS + blockIdx.x);
+        long long w0 = 0;
+        if (pb) { pb[0] = global_ns(); pb[5] = sm_id(); pb[6] = ep; pb[7] = 1ull; w0 = clock64(); }
         pAp = ll_gather_sum(&peers.mbox[peers.rank]->dot[0][ep & 1u][0][0], peers.ranks, cgk_tag(gen, ep), sc);
+        if (pb) { pb[4] = (unsigned long long)(clock64() - w0); pb[1] = global_ns(); }
     } else if (n_dot > 0) {
         /* deferred p.Ap: the GEMV left one partial per CTA (fixed order, same bits in every CTA) */
         pAp = cta_sum_partials<VEC_NT>(dot_partials, n_dot);
@@ -662,6 +722,7 @@ cgb_xr_update_kernel(double *__restrict__ x, double *__restrict__ r,
             sc->pAp = pAp;
             sc->ep_xr = e;
         }
+        if (pb) pb[2] = global_ns();
     } else {
         cta_partials_finish<VEC_NT>(mine, partials, rr_out, &sc->ticket_vec);
     }
@@ -693,11 +754,17 @@ cgb_p_update_kernel(double *p_loc, const double *__restrict__ r,
     if (*(volatile int *)&sc->stopped || *(volatile int *)&sc->breakdown) return;
     unsigned int ep = 0u, gen = 0u;
     double beta;
+    unsigned long long *pb = nullptr;
     if constexpr (COMM) {
         ep = *(volatile unsigned int *)&sc->ep_p;
         gen = *(volatile unsigned int *)&sc->gen;
         const unsigned int e = ep + 1u;
+        if (peers.probe && threadIdx.x == 0 && blockIdx.x < CGK_PROBE_VEC_CTAS)
+            pb = peers.probe + 8ull * (CGK_PROBE_MAX_PRODUCT_CTAS + CGK_PROBE_VEC_CTAS + blockIdx.x);
+        long long w0 = 0;
+        if (pb) { pb[0] = global_ns(); pb[5] = sm_id(); pb[6] = ep; pb[7] = 1ull; w0 = clock64(); }
         beta = ll_gather_sum(&peers.mbox[peers.rank]->dot[1][e & 1u][0][0], peers.ranks, cgk_tag(gen, e), sc);
+        if (pb) { pb[4] = (unsigned long long)(clock64() - w0); pb[1] = global_ns(); }
     } else if (n_rr > 0) {
         beta = cta_sum_partials<VEC_NT>(rr_partials, n_rr);   /* deferred r.r of xr_update */
     } else {
@@ -737,6 +804,110 @@ cgb_p_update_kernel(double *p_loc, const double *__restrict__ r,
                 sc->ticket_vec = 0u;
                 sc->ep_p = ep + 1u;
             }
+            if (pb) pb[2] = global_ns();
+        }
+    }
+}
+
+/* xr_update and p_update of the peer exchange in one launch (cgk_xrp_update in cg_kernels.h;
+ * parallel_cg.c:298-323 with the MPI_Allreduce of :313 in the middle).  Every CTA of the grid is
+ * resident at once (the launcher checks), so a CTA may wait for a value another CTA of the same
+ * launch produces: the last CTA of the first phase sends the rank's r.r partial to every
+ * mailbox, its own included, and all CTAs pick the G partials up from the local mailbox.
+ * Flags: stop_req is read at the very start -- no CTA can write it (phase 2) before every CTA
+ * has passed phase 1, i.e. has read it.  Epochs: ep_xr is read at the start and both ep_xr and
+ * ep_p are advanced by the last CTA of phase 2, again after every CTA has read them. */
+__global__ void __launch_bounds__(VEC_NT)
+cgb_xrp_update_kernel(double *__restrict__ x, double *__restrict__ r, double *p_loc,
+                      const double *__restrict__ Ap, double *__restrict__ partials,
+                      cgk_scalars *sc, int cur, int guard, double eps, int ignore_stop,
+                      long long max_iter, long long m, const cgk_peers peers)
+{
+    long long i = (long long)blockIdx.x * VEC_NT + threadIdx.x;
+    const bool first = i < m;
+    double x0 = 0.0, p0 = 0.0, r0 = 0.0, a0 = 0.0;
+    if (first) { x0 = x[i]; p0 = p_loc[i]; r0 = r[i]; }        /* written by the previous launch of this kernel */
+    const double rho = sc->rr[cur];
+    pdl_wait();                                                /* Ap, the flags: the product */
+    pdl_launch_dependents();
+    if (first) a0 = __ldcg(Ap + i);
+    if (*(volatile int *)&sc->stop_req) return;
+    const unsigned int ep = *(volatile unsigned int *)&sc->ep_xr;
+    const unsigned int gen = *(volatile unsigned int *)&sc->gen;
+    const unsigned int e = ep + 1u;                            /* r.r events: 0 = init, k+1 = iteration k */
+    const double pAp = ll_gather_sum(&peers.mbox[peers.rank]->dot[0][ep & 1u][0][0], peers.ranks, cgk_tag(gen, ep), sc);
+    const double alpha = rho / pAp;
+    if (guard && !isfinite(alpha)) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) { sc->breakdown = 3; sc->stop_req = 3; sc->pAp = pAp; }
+        return;
+    }
+    /* ---- phase 1: x += alpha p, r -= alpha Ap, partial of r.r (parallel_cg.c:299-309) */
+    double s = 0.0;
+    const long long stride = (long long)gridDim.x * VEC_NT;
+    if (first) {
+        x[i] = __dadd_rn(x0, __dmul_rn(p0, alpha));
+        r0 = __dsub_rn(r0, __dmul_rn(a0, alpha));
+        r[i] = r0;
+        s = fma(r0, r0, s);
+    }
+    for (long long j = i + stride; j < m; j += stride) {
+        x[j] = __dadd_rn(x[j], __dmul_rn(p_loc[j], alpha));
+        const double rj = __dsub_rn(r[j], __dmul_rn(__ldcg(Ap + j), alpha));
+        r[j] = rj;
+        s = fma(rj, rj, s);
+    }
+    const double mine = vec_cta_sum(s);
+    double total = 0.0;
+    if (cta_partials_finish_sys<VEC_NT, false>(mine, partials, &sc->rr_local, &sc->ticket_vec, &total) && threadIdx.x == 0) {
+        for (int g = 0; g < peers.ranks; ++g)                  /* MPI_Allreduce(beta), :313 */
+            ll_send(&peers.mbox[g]->dot[1][e & 1u][peers.rank][0], total, cgk_tag(gen, e));
+        sc->pAp = pAp;
+    }
+    /* ---- phase 2: stop rule, p = r + (beta/rho) p pushed to every rank (:314-323) */
+    const double beta = ll_gather_sum(&peers.mbox[peers.rank]->dot[1][e & 1u][0][0], peers.ranks, cgk_tag(gen, e), sc);
+    const bool hit = sqrt(beta) < eps;
+    const bool brk = hit && !ignore_stop;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const long long k = sc->iters;
+        sc->iters = k + 1;
+        sc->final_beta = beta;
+        sc->rr[cur ^ 1] = beta;                               /* read as rho by the NEXT iteration only */
+        if (hit && sc->first_hit < 0) sc->first_hit = k;
+        if (brk) { sc->break_k = k; sc->stop_req = 1; }
+        else if (k + 1 >= max_iter) sc->stop_req = 2;
+    }
+    const bool lastly = !brk;
+    if (lastly) {
+        const double coef = beta / rho;
+        const long long lo = (long long)peers.rank * m;
+        if (first) {
+            const double pi = __dadd_rn(r0, __dmul_rn(p0, coef));
+            p_loc[i] = pi;
+            for (int g = 0; g < peers.ranks; ++g)
+                if (g != peers.rank) peers.p_full[g][lo + i] = pi;
+        }
+        for (long long j = i + stride; j < m; j += stride) {
+            const double pj = __dadd_rn(r[j], __dmul_rn(p_loc[j], coef));
+            p_loc[j] = pj;
+            for (int g = 0; g < peers.ranks; ++g)
+                if (g != peers.rank) peers.p_full[g][lo + j] = pj;
+        }
+    }
+    /* the epochs advance on a break too (as the two-kernel form's xr_update does): the ticket runs either way */
+    __shared__ int s_last2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (lastly) __threadfence_system();                   /* cumulative over the CTA's peer stores */
+        else __threadfence();
+        s_last2 = (atomicAdd(&sc->ticket_p, 1u) == gridDim.x - 1);
+        if (s_last2) {
+            if (lastly) {
+                __threadfence_system();
+                post_p_flags(peers, cgk_tag(gen, e));
+                sc->ep_p = e;
+            }
+            sc->ticket_p = 0u;
+            sc->ep_xr = e;
         }
     }
 }
@@ -900,6 +1071,7 @@ __global__ void cgb_reset_kernel(cgk_scalars *sc, unsigned int gen)
     sc->cg2_k[0] = sc->cg2_k[1] = 0u;
     sc->cg2_gprev[0] = sc->cg2_gprev[1] = 0.0;
     sc->cg2_aprev[0] = sc->cg2_aprev[1] = 0.0;
+    sc->ticket_p = 0u;
 }
 
 template <bool COMM>
@@ -1217,8 +1389,10 @@ extern "C" int cgk_gemv_make_plan_comm(cgk_gemv_plan *plan, int64_t m, int64_t n
         c = find_comm(plan->rows_per_cta, plan->unroll, plan->threads, vec);
     if (!c) {
         if (vec == 4) {
-            /* (8,2,512): all 64 doubles of A in flight before the flag check do not fit 128
-             * registers; (4,2,256) keeps 2 CTAs per SM and no spill */
+            /* (4,2,256): 3 CTAs per SM.  The one-rank kernel's (8,2,512) shape was measured here too
+             * (round 2, 2 GPUs, with the flag test moved out of the unrolled loops so that it fits
+             * 128 registers): 1 % slower at n = 65536 (7.31 against 7.38-7.44 TB/s) and 2 % slower at
+             * n = 16384, so it is not instantiated */
             if (n >= 8192) c = find_comm(4, 2, 256, 4);     /* measured on 2 GPUs: beats (2,1,256) at n = 16384 */
             else c = find_comm(4, 1, 128, 4);
         } else if (vec == 2) c = find_comm(4, 2, 128, 2);
@@ -1268,6 +1442,29 @@ extern "C" int cgk_xr_update(double *x, double *r, const double *p_loc, const do
     else
         cgk_launch(cgb_xr_update_kernel<false>, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials,
                    rr_out, sc, cur, guard, (long long)m, k_no_peers, dot_partials, n_dot);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_xrp_supported(int64_t m, int sm_count)
+{
+    static int per_sm = -1;
+    if (per_sm < 0) {
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cgb_xrp_update_kernel, VEC_NT, 0) != cudaSuccess) { (void)cudaGetLastError(); occ = 0; }
+        per_sm = occ;
+    }
+    if (sm_count <= 0) sm_count = 148;
+    /* half of what fits: the tail of the product may still hold part of the SMs when this kernel starts */
+    return (int64_t)vec_grid(m) <= (int64_t)sm_count * per_sm / 2;
+}
+
+extern "C" int cgk_xrp_update(double *x, double *r, double *p_loc, const double *Ap, double *partials,
+                              cgk_scalars *sc, int cur, int guard, double eps, int ignore_stop,
+                              int64_t max_iter, int64_t m, const cgk_peers *peers, void *stream)
+{
+    if (!peers) return (int)cudaErrorInvalidValue;
+    cgk_launch(cgb_xrp_update_kernel, dim3(vec_grid(m)), dim3(VEC_NT), 0, (cudaStream_t)stream, x, r, p_loc, Ap, partials, sc, cur,
+               guard, eps, ignore_stop, (long long)max_iter, (long long)m, *peers);
     return (int)cudaGetLastError();
 }
 

@@ -51,6 +51,8 @@ typedef struct cgk_scalars {
      * parity c reads slot [c] and CTA 0 writes slot [c ^ 1], so no launch reads what it writes */
     unsigned int cg2_k[2];
     double cg2_gprev[2], cg2_aprev[2];
+    unsigned int ticket_p; /* second ticket of cgk_xrp_update (its p phase)                      */
+    unsigned int pad_;
 } cgk_scalars;
 
 /* ---- peer-memory exchange over NVLink (replaces MPI_Allgather(p) parallel_cg.c:290-291 and the
@@ -78,7 +80,17 @@ typedef struct cgk_peers {
     double *p_full[CGK_MAX_RANKS];      /* every rank's gathered-direction vector, peer-mapped */
     cgk_mailbox *mbox[CGK_MAX_RANKS];   /* every rank's mailbox; mbox[rank] is local           */
     double *crecv[CGK_MAX_RANKS];       /* every rank's [ranks][m] receive area for column sums */
+    unsigned long long *probe;          /* NULL, or CGK_PROBE_WORDS words of device memory into which the
+                                         * exchange kernels of the classic iteration write per-CTA time stamps
+                                         * (CGB_PROBE=1; tools/probe_exchange.py reads them) */
 } cgk_peers;
+/* probe layout: 8 words per CTA; product CTAs first, then the CTAs of xr_update, then those of p_update.
+ * product:   [0] globaltimer at entry, [1] after the own column block, [2] after the flag wait, [3] before the
+ *            epilogue, [4] SM clocks spent in the wait (warp 0), [5] %smid, [6] epoch, [7] 1
+ * xr / p:    [0] entry, [1] after the mailbox gather, [2] end, [4] SM clocks in the gather, [5] %smid, [6] epoch, [7] 1 */
+#define CGK_PROBE_MAX_PRODUCT_CTAS 16384
+#define CGK_PROBE_VEC_CTAS 592
+#define CGK_PROBE_WORDS (8 * (CGK_PROBE_MAX_PRODUCT_CTAS + 2 * CGK_PROBE_VEC_CTAS))
 
 /* Row-sharded symmetric product (cg_symv.cu): which tiles of its m x n row block a rank reads.
  * Block pairs {g, h} are split so that every rank reads exactly half of its block: its own
@@ -162,6 +174,18 @@ int cgk_xr_update(double *x, double *r, const double *p_loc, const double *Ap,
                   double *partials, double *rr_out, cgk_scalars *sc, int cur, int guard,
                   int64_t m, const cgk_peers *peers, const double *dot_partials, int n_dot,
                   void *stream);
+/* cgk_xr_update + cgk_p_update as ONE launch for the peer exchange (ranks > 1): the grid (at most
+ * cgk_vec_max_ctas CTAs, all co-resident) updates x and r, its last CTA pushes the rank's r.r
+ * partial, every CTA then waits on the local mailbox for the G partials, applies the stop rule
+ * and updates / pushes its part of p with r and p still in registers.  One launch ramp, one
+ * drain and one reload of r less per iteration than the two-kernel form; same arithmetic, same
+ * order, same tags and epochs (the two forms can alternate between solves). */
+int cgk_xrp_update(double *x, double *r, double *p_loc, const double *Ap, double *partials,
+                   cgk_scalars *sc, int cur, int guard, double eps, int ignore_stop,
+                   int64_t max_iter, int64_t m, const cgk_peers *peers, void *stream);
+/* 1 when the merged kernel's grid for m elements is co-resident on this device. */
+int cgk_xrp_supported(int64_t m, int sm_count);
+
 /* Programmatic dependent launch for the calling thread's following launches of the one-rank
  * iteration kernels (cg_device.cuh explains the rule the kernels keep); 0 = plain launches. */
 void cgk_set_pdl(int on);

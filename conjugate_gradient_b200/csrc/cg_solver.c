@@ -389,7 +389,7 @@ int cgb_destroy(cgb_ctx *c)
     for (int i = 0; i < 3; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < c->n_gemv_ev; ++i) cudaEventDestroy(c->gemv_ev[i]);
     free(c->gemv_ev);
-    gfree(c, c->sc); gfree(c, c->partials_vec); cudaFree(c->flush_buf);
+    gfree(c, c->sc); gfree(c, c->partials_vec); cudaFree(c->flush_buf); cudaFree(c->probe);
     if (c->h_sc) cudaFreeHost(c->h_sc);
     if (c->stream) cudaStreamDestroy(c->stream);
     (void)cudaGetLastError();
@@ -624,6 +624,17 @@ int cgb_debug_read(cgb_ctx *c, int what, int64_t offset, int64_t count, double *
     return CGB_OK;
 }
 
+int64_t cgb_debug_probe_read(cgb_ctx *c, unsigned long long *dst, int64_t max_words)
+{
+    if (!c || !dst || max_words < 0) { cgb_set_error("%s%s (cg_solver.c:%d)", "cgb_debug_probe_read: bad argument", "", __LINE__); return CGB_ERR_ARG; }
+    if (!c->probe) { cgb_set_error("%s%s (cg_solver.c:%d)", "no probe data: solve on several ranks with CGB_PROBE=1 in the environment", "", __LINE__); return CGB_ERR_STATE; }
+    const int64_t w = max_words < CGK_PROBE_WORDS ? max_words : CGK_PROBE_WORDS;
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(dst, c->probe, (size_t)w * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return w;
+}
+
 /* Guard-band self test: one double stored at element `offset` of an array, where offset may lie up
  * to 32 elements outside it.  Refused unless the context was created with CGB_DEBUG_GUARDS=1. */
 int cgb_debug_poke(cgb_ctx *c, int what, int64_t offset, double value)
@@ -792,6 +803,13 @@ static int enqueue_iteration_body(cgb_ctx *c, const cgb_options *o, int64_t max_
     }
     int rc = enqueue_product(c, ev_a, ev_b);
     if (rc != CGB_OK) return rc;
+    if (peers && c->use_xrp) {
+        /* both vector kernels and the all-reduce between them in one launch (cgk_xrp_update) */
+        KL(cgk_xrp_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec, c->sc, cur, o->guard, o->eps, o->ignore_stop,
+                          max_iter, c->m, peers, st));                                     /* :298-323 */
+        c->launches += 1;
+        return CGB_OK;
+    }
     if (peers) {
         KL(cgk_xr_update(x_loc, c->r, p_loc, c->Ap, c->partials_vec, &c->sc->rr_local, c->sc, cur,
                          o->guard, c->m, peers, NULL, 0, st));                             /* :298-313 */
@@ -819,6 +837,7 @@ static int build_graph(cgb_ctx *c, const cgb_options *o, int64_t max_iter, int c
     key.A = c->A; key.win = c->win; key.comm = c->comm_mode;
     key.symv = c->use_symv; key.symv_ru = c->symv_ru; key.symv_split = c->symv_split;
     key.cg_variant = o->cg_variant; key.n_dot = c->n_dot; key.defer_rr = c->defer_rr; key.pdl = c->pdl;
+    key.xrp = c->use_xrp;
     if (c->graph_exec && memcmp(&key, &c->graph_key, sizeof key) == 0) return CGB_OK;
     drop_graph(c);
     const int64_t before = c->launches;
@@ -886,6 +905,17 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         }
         c->comm_mode = (o.comm == CGB_COMM_NCCL || !c->peer_ok) ? CGB_COMM_NCCL : CGB_COMM_PEER;
     }
+    if (c->comm_mode == CGB_COMM_PEER) {
+        /* CGB_PROBE=1: the exchange kernels leave per-CTA time stamps (cg_kernels.h, cgb_debug_probe_read) */
+        const char *e = getenv("CGB_PROBE");
+        const int want = e && *e && *e != '0';
+        if (want && !c->probe) {
+            CU(cudaMalloc((void **)&c->probe, (size_t)CGK_PROBE_WORDS * sizeof(unsigned long long)));
+            CU(cudaMemsetAsync(c->probe, 0, (size_t)CGK_PROBE_WORDS * sizeof(unsigned long long), st));
+        }
+        if ((c->peers.probe != NULL) != (want != 0)) drop_graph(c);     /* the captured kernels carry the pointer */
+        c->peers.probe = want ? c->probe : NULL;
+    }
     const cgk_peers *peers = c->comm_mode == CGB_COMM_PEER ? &c->peers : NULL;
     if (multi && !peers && o.cg_variant == CGB_CG_FUSED_REDUCTIONS)
         FAIL(CGB_ERR_STATE, "cg_variant = CGB_CG_FUSED_REDUCTIONS on several ranks needs the peer-memory exchange (CGB_COMM_PEER)");
@@ -916,6 +946,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
          * on 2 GPUs: +5 % at n = 4096, nothing to -2 % at n = 16384); not between NCCL's kernels */
         const int short_iter = 8.0 * (double)c->m * (double)c->n <= 3.0 * (double)c->l2_bytes;
         if ((!multi || (c->comm_mode == CGB_COMM_PEER && short_iter)) && !(e && *e == '0')) c->pdl = 1;
+        if (multi && c->comm_mode == CGB_COMM_PEER && e && *e == '2') c->pdl = 1;      /* measurement: at any size */
     }
     {
         const char *e = getenv("CGB_DEFER");
@@ -926,6 +957,14 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         }
     }
 
+    {
+        /* peer exchange, classic recurrence: the two vector kernels as ONE launch when CGB_XRP=1.  Off by
+         * default on the measurements of round 2 (8 GPUs, graph replay): n = 65536: 1618.1 -> 1619.3 it/s,
+         * n = 16384: 15995 -> 15570 it/s -- with programmatic dependent launch the second kernel's launch
+         * already hides behind the first, and the merged form makes every CTA wait twice */
+        const char *e = getenv("CGB_XRP");
+        c->use_xrp = peers && o.cg_variant == CGB_CG_CLASSIC && (e && *e == '1') && cgk_xrp_supported(c->m, c->sm_count);
+    }
     double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     const int use_graph = o.use_graph && !o.time_gemv;
     int chunk = 0;

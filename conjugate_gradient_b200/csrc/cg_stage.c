@@ -16,9 +16,12 @@
  *
  * Environment (read at every call; for measurements, tools/h2d_ceiling.py):
  *   CGB_STAGE=0            never stage (the driver's pageable path, as in round 1)
+ *   CGB_STAGE=stage        always the ring
  *   CGB_STAGE=register     pin the caller's pages in place, piece by piece, ahead of the DMA
+ *                          (unset / auto: the ring)
  *   CGB_STAGE_THREADS=T    copy threads (default: min(8, online CPUs / ranks), at least 2)
- *   CGB_STAGE_CHUNK_MB=C   bytes per piece (default 8 MiB)
+ *   CGB_STAGE_CHUNK_MB=C   bytes per piece (default 8 MiB for the ring, 32 MiB for in-place pinning);
+ *   CGB_STAGE_CHUNK_KB=K   the same in KiB (>= 64)
  */
 #define _GNU_SOURCE
 #include <cuda_runtime_api.h>
@@ -52,14 +55,20 @@ static int env_int(const char *name, int dflt, int lo, int hi)
     return (int)v;
 }
 
-int cgb_stage_mode(void)
+/* How a pageable source travels: the staging ring, unless the environment says otherwise.  Pinning the
+ * caller's pages in place (CGB_STAGE=register) moves no extra bytes through host memory, but
+ * cudaHostRegister serialises between processes: measured with two ranks uploading at once, 4-6 GB/s
+ * per GPU against 28 GB/s through the ring (one rank alone: 43 against 53) -- so it stays an option. */
+int cgb_stage_mode_for(int ranks)
 {
     const char *e = getenv("CGB_STAGE");
-    if (!e || !*e) return CGB_H2D_STAGED;
+    (void)ranks;
+    if (!e || !*e || !strcmp(e, "auto")) return CGB_H2D_STAGED;
     if (!strcmp(e, "0") || !strcmp(e, "off")) return CGB_H2D_DRIVER;
     if (!strcmp(e, "register")) return CGB_H2D_REGISTERED;
     return CGB_H2D_STAGED;
 }
+int cgb_stage_mode(void) { return cgb_stage_mode_for(1); }
 
 static int stage_threads(const cgb_ctx *c)
 {
@@ -236,8 +245,12 @@ int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int p
 {
     size_t total = 0;
     for (int64_t i = 0; i < nruns; ++i) total += runs[i].width * runs[i].rows;
-    int mode = pageable ? cgb_stage_mode() : CGB_H2D_DIRECT;
-    const size_t chunk = (size_t)env_int("CGB_STAGE_CHUNK_MB", 8, 1, 256) << 20;
+    int mode = pageable ? cgb_stage_mode_for(c->ranks) : CGB_H2D_DIRECT;
+    size_t chunk = (size_t)env_int("CGB_STAGE_CHUNK_MB", mode == CGB_H2D_REGISTERED ? 32 : 8, 1, 256) << 20;
+    {
+        const int kb = env_int("CGB_STAGE_CHUNK_KB", 0, 64, 256 << 10);       /* finer than a MiB, for the sweep */
+        if (kb > 0) chunk = (size_t)kb << 10;
+    }
     if (mode != CGB_H2D_DIRECT && mode != CGB_H2D_DRIVER && total < 2 * chunk) mode = CGB_H2D_DRIVER;   /* small: not worth a thread team */
     if (path_out) *path_out = mode;
     if (mode == CGB_H2D_DIRECT || mode == CGB_H2D_DRIVER) {

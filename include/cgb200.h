@@ -161,6 +161,13 @@ int cgb_debug_check_guards(cgb_ctx *ctx);
 /* Self test of the above (refused without CGB_DEBUG_GUARDS=1): stores one double at element
  * `offset` of array `what` (1 b, 2 x, 3 r, 5 Ap), -32 <= offset < length + 32. */
 int cgb_debug_poke(cgb_ctx *ctx, int what, int64_t offset, double value);
+/* With CGB_PROBE=1 in the environment of a solve on several ranks (peer-memory exchange), the
+ * exchange-fused kernels leave per-CTA time stamps of their last launch: when a CTA started,
+ * finished its own column block, saw the peers' flags, ended, and how long it polled.  Copies up
+ * to max_words 64-bit words (layout: 8 words per CTA, see tools/probe_exchange.py) and returns
+ * the number copied, or a negative status.  Measurement aid for the part of the path ncu cannot
+ * replay (a replayed pass would wait for pushes the peers never repeat). */
+int64_t cgb_debug_probe_read(cgb_ctx *ctx, unsigned long long *dst, int64_t max_words);
 
 /* ---- library / device ------------------------------------------------------ */
 int         cgb_version(void);

@@ -242,7 +242,12 @@ def test_stub_b200_arm_line_against_a_stub_context(monkeypatch):
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and r["bytes_per_launch"] == bench.gemv_bytes(65536, 65536)
     assert r["achieved"] == pytest.approx(r["bytes_per_launch"] / 4.5e-3 / 1e9) and r["frac"] == pytest.approx(r["achieved"] / r["peak"])
     assert line["gpu_launches"] == 3 * 20                     # the 4 set-up launches are outside the K iterations
-    assert ctx.solves[0]["max_iter"] == 3 and ctx.solves[1]["max_iter"] == 20 and ctx.solves[1]["time_gemv"] == 1
+    # warm-up (W stream-mode iterations, one pass of the graph run), the timed graph run, the instrumented pass
+    assert ctx.solves[0]["max_iter"] == 3 and ctx.solves[0]["time_gemv"] == 1
+    assert ctx.solves[1]["max_iter"] == 20 and "time_gemv" not in ctx.solves[1]
+    assert ctx.solves[2]["max_iter"] == 20 and "time_gemv" not in ctx.solves[2]
+    assert ctx.solves[3]["max_iter"] == 20 and ctx.solves[3]["time_gemv"] == 1
+    assert line["instrumented_pass"]["value"] == pytest.approx(line["value"]) and "graph" in line["timed_region"]["mode"]
     assert "symmetric_variant" in line and "fused_reductions_variant" in line
     json.dumps(line)                                         # serialisable as ONE line
 

@@ -71,6 +71,43 @@ def test_long_running_sharded_solve(cg, gpus, comm):
 
 
 @pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_merged_vector_kernel_gives_the_two_kernel_bits(cg, gpus, monkeypatch):
+    """CGB_XRP=1: xr_update, the r.r all-reduce and p_update as one launch (cgb_xrp_update_kernel).  Same
+    arithmetic in the same order as the two-kernel form, so the iterates agree bit for bit -- over a long
+    run (epochs, both slot parities, the break in the middle of a captured graph) and in fixed-iteration mode."""
+    need(cg, gpus)
+    n, seed, flags = 2048, 23, cg.GEN_KAPPA_LOG2(7)
+    xo, so = O.conjugrad(O.gen_A(n, seed, flags), O.gen_b(n, seed, flags), np.zeros(n), ranks=gpus)
+    monkeypatch.setenv("CGB_XRP", "0")
+    x2, st2 = cg.solve_generated(n, seed, gpus=gpus, flags=flags, comm=2)
+    f2, sf2 = cg.solve_generated(n, seed, gpus=gpus, flags=flags, comm=2, ignore_stop=1, max_iter=11)
+    monkeypatch.setenv("CGB_XRP", "1")
+    for use_graph in (1, 0):
+        x1, st1 = cg.solve_generated(n, seed, gpus=gpus, flags=flags, comm=2, use_graph=use_graph)
+        assert st1["iterations"] == st2["iterations"] and st1["exit_reason"] == 1 and so["iterations"] > 80
+        np.testing.assert_array_equal(x1, x2)
+        assert relerr(x1, xo) <= RTOL_X and abs(st1["iterations"] - so["iterations"]) <= 1
+        # one launch less per iteration
+        assert st1["kernel_launches"] < st2["kernel_launches"]
+    f1, sf1 = cg.solve_generated(n, seed, gpus=gpus, flags=flags, comm=2, ignore_stop=1, max_iter=11)
+    assert sf1["iterations"] == 11
+    np.testing.assert_array_equal(f1, f2)
+
+
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_pageable_rank_blocks_go_through_the_staging_ring(cg, gpus):
+    """cgb_conjugrad_host on malloc'ed arrays, several ranks uploading at once: every rank's block goes through its
+    own staging ring (cg_stage.c) and the solve sees exactly the caller's matrix."""
+    need(cg, gpus)
+    n, seed = 4096, 19                       # 16 MiB per rank at 8 ranks: above the small-copy cut-off
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus)
+    xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
+    assert relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    assert st["h2d_path"] in (2, 3), st["h2d_path"]
+
+
+@pytest.mark.parametrize("gpus", [2, 4, 8])
 def test_peer_exchange_is_bitwise_reproducible_and_rank_ordered(cg, gpus):
     # the mailbox sums add the partials in rank order on every rank: two runs agree bit for bit,
     # and so do the iteration counts of all ranks (else the solve would dead-lock or diverge)
@@ -219,4 +256,5 @@ def test_torchrun_bench_two_ranks(cg):
     line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert line["n_gpus"] == 2 and line["value"] > 0 and line["e2e"]["value"] > 0
     # one process per GPU: the windows are mapped through CUDA IPC
-    assert "peer" in line["config"]["exchange"]
+    assert "peer" in line["implementation"]["exchange"]
+    assert line["parity"]["ok"] and line["parity"]["ranks"] == 2 and line["parity"]["fixed_run"]["rel_err_x"] <= 1e-10

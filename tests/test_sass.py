@@ -48,7 +48,7 @@ def test_only_sm_100a_code():
 def test_every_kernel_family_is_present(sass):
     fam = {re.sub(r"<.*", "", k) for k in sass}
     want = {"cgb_rowblock_matvec_ldg", "cgb_rowblock_matvec_keep", "cgb_rowblock_matvec_comm", "cgb_rowblock_matvec_bulk",
-            "cgb_xr_update_kernel", "cgb_p_update_kernel", "cgb_init_residual_kernel", "cgb_after_init_kernel", "cgb_reset_kernel",
+            "cgb_xr_update_kernel", "cgb_p_update_kernel", "cgb_xrp_update_kernel", "cgb_init_residual_kernel", "cgb_after_init_kernel", "cgb_reset_kernel",
             "cgb_cg2_step_kernel", "cgb_cg2_step_one_kernel", "cgb_generate_A_kernel", "cgb_generate_b_kernel",
             "cgb_halfmat_tile_kernel", "cgb_halfmat_tile_comm_kernel", "cgb_halfmat_finish_kernel", "cgb_halfmat_finish_comm_kernel",
             "cgb_halfmat_push_kernel", "cgb_symmetry_check_kernel", "cgb_ingest_scan_kernel", "cgb_ingest_count_kernel",
@@ -76,15 +76,18 @@ def test_default_gemv_shapes_do_not_spill(sass):
 
 
 def test_every_vw4_gemv_uses_256_bit_loads(sass):
+    seen = 0
     for name, body in sass.items():
-        m = re.match(r"gemv_ldg(_keep|_comm)?_kernel<(\d+),(\d+),(\d+),(\d+)>", name)
+        m = re.match(r"cgb_rowblock_matvec(_ldg|_keep|_comm)<(\d+),(\d+),(\d+),(\d+)>", name)
         if not m:
             continue
+        seen += 1
         o = ops(body)
         if m.group(5) == "4":
             assert any(x.startswith("LDG.") and ".256" in x for x in o), name
         if m.group(1) == "_keep":       # rows meant to survive in L2: evict-last beside evict-first
             assert any(".ELL2." in x for x in o) and any(".EFL2." in x for x in o), name
+    assert seen >= 20, seen
 
 
 def test_bulk_variant_uses_the_tma_engine(sass):
@@ -123,8 +126,12 @@ def test_no_fp64_atomics_and_no_tensor_cores(sass):
 def test_peer_exchange_uses_system_scope_accesses(sass):
     # the kernels that push into peer windows fence at system scope, the consumers poll with sys loads
     assert any(x == "MEMBAR.SC.SYS" for x in ops(sass["cgb_p_update_kernel<true>"]))
-    for name in ("cgb_xr_update_kernel<true>", "cgb_p_update_kernel<true>", "cgb_rowblock_matvec_comm<4,2,256,4>"):
+    assert any(x == "MEMBAR.SC.SYS" for x in ops(sass["cgb_xrp_update_kernel"]))
+    for name in ("cgb_xr_update_kernel<true>", "cgb_p_update_kernel<true>", "cgb_xrp_update_kernel", "cgb_rowblock_matvec_comm<4,2,256,4>"):
         assert any(x.endswith("STRONG.SYS") and x.startswith("LDG") for x in ops(sass[name])), name
+    # the exchange-fused product keeps all R * U = 8 wide loads of A of a tile in flight
+    o = ops(sass["cgb_rowblock_matvec_comm<4,2,256,4>"])
+    assert sum(x == "LDG.E.NA.EFL2.256.CONSTANT" for x in o) >= 8
     # ... and the one-rank forms pay no system-scope fence
     for name in ("cgb_xr_update_kernel<false>", "cgb_p_update_kernel<false>", "cgb_rowblock_matvec_ldg<8,2,512,4>", "cgb_cg2_step_one_kernel"):
         assert "MEMBAR.SC.SYS" not in ops(sass[name]), name

@@ -1,11 +1,11 @@
 #!/usr/bin/env python
 """tools/h2d_ceiling.py -- what can this box move from host memory to HBM?
 
-One rank:   python tools/h2d_ceiling.py [--n 32768] [--sweep]
+One rank:   python tools/h2d_ceiling.py [--order 32768] [--sweep]
             pinned source (the DMA ceiling), pageable source left to the driver (CGB_STAGE=0),
             pageable source through the staging ring of cg_stage.c (threads x chunk sweep) and
             pinned in place piece by piece (CGB_STAGE=register) -- all through cgb_load_host.
-N ranks:    python -m torch.distributed.run --nproc-per-node N ... tools/h2d_ceiling.py --n 32768
+N ranks:    python -m torch.distributed.run --nproc-per-node N ... tools/h2d_ceiling.py --order 32768
             every subset the round-1 verdict asked for: all ranks at once, then the pairs (0,1), (0,2),
             (0,4) alone (a shared PCIe uplink shows as a pair that halves), pinned and staged.
 Prints one JSON object (rank 0); nothing here is a bench value.
@@ -23,7 +23,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=32768)
+    ap.add_argument("--order", dest="n", type=int, default=32768)   # not --n: torchrun's own parser trips over it
     ap.add_argument("--sweep", action="store_true")
     ap.add_argument("--reps", type=int, default=2)
     args = ap.parse_args()
@@ -92,17 +92,21 @@ def main():
         res["pageable_register"] = upload(pg_ptr, CGB_STAGE="register", CGB_STAGE_CHUNK_MB=64)
         if args.sweep:
             sw = {}
-            for t in (2, 4, 6, 8, 12, 16, 24, 32):
-                for mb in (2, 4, 8, 16, 32):
-                    sw[f"t{t}_c{mb}"] = round(upload(pg_ptr, CGB_STAGE_THREADS=t, CGB_STAGE_CHUNK_MB=mb), 2)
+            for t in (2, 4, 6, 8, 12, 16):
+                for kb in (256, 512, 1024, 2048, 4096, 8192, 16384, 32768):
+                    sw[f"t{t}_c{kb}k"] = round(upload(pg_ptr, CGB_STAGE_THREADS=t, CGB_STAGE_CHUNK_KB=kb), 2)
             res["staged_sweep_gbs"] = sw
             res["register_sweep_gbs"] = {f"t{t}_c{mb}": round(upload(pg_ptr, CGB_STAGE="register", CGB_STAGE_THREADS=t, CGB_STAGE_CHUNK_MB=mb), 2)
                                          for t in (2, 4, 8) for mb in (32, 128)}
     else:
         res["all_pinned_gbs_per_gpu"] = gather(round(upload(pin_ptr), 2))
-        res["all_staged_gbs_per_gpu"] = gather(round(upload(pg_ptr), 2))
-        for t in (2, 4, 8):
-            res[f"all_staged_t{t}_gbs_per_gpu"] = gather(round(upload(pg_ptr, CGB_STAGE_THREADS=t), 2))
+        res["all_default_gbs_per_gpu"] = gather(round(upload(pg_ptr), 2))
+        res["all_driver_gbs_per_gpu"] = gather(round(upload(pg_ptr, CGB_STAGE=0), 2))
+        cpus = len(os.sched_getaffinity(0))
+        for t in sorted({2, 4, max(2, cpus // world), max(2, 2 * cpus // world)}):
+            for kb in (256, 1024, 2048, 8192):
+                res[f"all_staged_t{t}_c{kb}k_gbs_per_gpu"] = gather(round(upload(pg_ptr, CGB_STAGE="stage", CGB_STAGE_THREADS=t, CGB_STAGE_CHUNK_KB=kb), 2))
+        res["all_register_t4_c32_gbs_per_gpu"] = gather(round(upload(pg_ptr, CGB_STAGE="register", CGB_STAGE_THREADS=4, CGB_STAGE_CHUNK_MB=32), 2))
         for pair in ((0, 1), (0, 2), (0, 4), (0, 7)):
             if pair[1] < world:
                 res[f"pair{pair[0]}{pair[1]}_pinned"] = [v for v in gather(round(upload(pin_ptr, active=rank in pair), 2)) if v]
