@@ -128,6 +128,7 @@ def lib():
         "cgb_debug_check_guards": ([vp], C.c_int),
         "cgb_debug_poke": ([vp, C.c_int, i64, C.c_double], C.c_int),
         "cgb_debug_probe_read": ([vp, vp, i64], i64),
+        "cgb_debug_rendezvous_id": ([C.c_int, C.c_int, vp], C.c_int),
         "cgb_load_text": ([vp, i64, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
         "cgb_conjugrad_files": ([C.c_char_p, C.c_char_p, C.c_char_p, i64, C.c_int, op, vp, sp], C.c_int),
         "cgb_generate": ([vp, i64, u64, C.c_uint], C.c_int), "cgb_set_x0": ([vp, vp], C.c_int),

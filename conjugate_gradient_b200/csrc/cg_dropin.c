@@ -15,6 +15,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
+#include <time.h>
 #include <unistd.h>
 
 #include "../../include/cgb200.h"
@@ -70,10 +72,79 @@ static void *team_solve_main(void *arg)
     return NULL;
 }
 
+/* Every member unmaps its peers' windows before any member frees its own (cg_solver.c: free_problem). */
 static void team_release(void)
 {
+    for (int g = 0; g < g_team.gpus; ++g) cgb_unmap_peers(g_team.ctx[g]);
     for (int g = 0; g < g_team.gpus; ++g) { cgb_destroy(g_team.ctx[g]); g_team.ctx[g] = NULL; }
     g_team.gpus = 0;
+}
+
+/* One host thread per member, all or none: the members meet in collectives, so a team with a thread
+ * missing would hang.  The threads wait at a gate until every pthread_create has succeeded; if one
+ * fails the gate opens with "abort", nobody calls fn, and the caller gets CGB_ERR_NOMEM. */
+typedef struct { pthread_mutex_t mu; pthread_cond_t cv; int state; } team_gate;      /* 0 wait, 1 go, -1 abort */
+typedef struct { void *(*fn)(void *); void *arg; team_gate *gate; } team_thunk;
+
+static void *team_thunk_main(void *arg)
+{
+    team_thunk *t = arg;
+    pthread_mutex_lock(&t->gate->mu);
+    while (t->gate->state == 0) pthread_cond_wait(&t->gate->cv, &t->gate->mu);
+    const int go = t->gate->state == 1;
+    pthread_mutex_unlock(&t->gate->mu);
+    if (go) t->fn(t->arg);
+    return NULL;
+}
+
+static int team_run(void *(*fn)(void *), void *members, size_t stride, int gpus)
+{
+    pthread_t th[MAX_GPUS];
+    team_thunk tk[MAX_GPUS];
+    team_gate gate;
+    pthread_mutex_init(&gate.mu, NULL);
+    pthread_cond_init(&gate.cv, NULL);
+    gate.state = 0;
+    int started = 0;
+    for (int g = 1; g < gpus; ++g) {                 /* member 0 runs on the calling thread */
+        tk[g].fn = fn; tk[g].arg = (char *)members + (size_t)g * stride; tk[g].gate = &gate;
+        if (pthread_create(&th[g], NULL, team_thunk_main, &tk[g]) != 0) break;
+        started = g;
+    }
+    const int all = started == gpus - 1;
+    pthread_mutex_lock(&gate.mu);
+    gate.state = all ? 1 : -1;
+    pthread_cond_broadcast(&gate.cv);
+    pthread_mutex_unlock(&gate.mu);
+    if (all) fn(members);
+    for (int g = 1; g <= started; ++g) pthread_join(th[g], NULL);
+    pthread_cond_destroy(&gate.cv);
+    pthread_mutex_destroy(&gate.mu);
+    if (!all) {
+        cgb_set_error("%s%s (cg_dropin.c:%d)", "could not start one host thread per GPU (pthread_create failed)", "", __LINE__);
+        return CGB_ERR_NOMEM;
+    }
+    return CGB_OK;
+}
+
+/* rc and message of a team phase: the member that failed by itself names the cause; members that only
+ * learnt of it through the status agreement ("another rank failed") speak only if nobody else does */
+#define TEAM_COLLECT(mb, gpus, rc, prefix)                                                              \
+    do {                                                                                                \
+        for (int pass_ = 0; pass_ < 2 && (rc) == CGB_OK; ++pass_)                                       \
+            for (int g_ = 0; g_ < (gpus) && (rc) == CGB_OK; ++g_)                                       \
+                if ((mb)[g_].rc != CGB_OK && (pass_ == 1 || !strstr((mb)[g_].err, "another rank failed"))) { \
+                    (rc) = (mb)[g_].rc;                                                                 \
+                    cgb_set_error("%s%s (cg_dropin.c:%d)", prefix, (mb)[g_].err, __LINE__);             \
+                }                                                                                       \
+    } while (0)
+
+static void team_release_keep_error(void)
+{
+    char keep[512];
+    snprintf(keep, sizeof keep, "%s", cgb_last_error());
+    team_release();
+    cgb_set_error("%s%s", keep, "", 0);
 }
 
 static int team_ensure(int gpus)
@@ -88,14 +159,11 @@ static int team_ensure(int gpus)
     unsigned char id[128];
     int rc = cgb_unique_id(id);
     if (rc != CGB_OK) return rc;
-    pthread_t th[MAX_GPUS];
     member_t mb[MAX_GPUS];
     memset(mb, 0, sizeof mb);
-    for (int g = 0; g < gpus; ++g) {
-        mb[g].g = g; mb[g].gpus = gpus; mb[g].id = id; mb[g].slot = &g_team.ctx[g];
-        pthread_create(&th[g], NULL, team_create_main, &mb[g]);
-    }
-    for (int g = 0; g < gpus; ++g) pthread_join(th[g], NULL);
+    for (int g = 0; g < gpus; ++g) { mb[g].g = g; mb[g].gpus = gpus; mb[g].id = id; mb[g].slot = &g_team.ctx[g]; }
+    rc = team_run(team_create_main, mb, sizeof mb[0], gpus);
+    if (rc != CGB_OK) return rc;
     for (int g = 0; g < gpus; ++g)
         if (mb[g].rc != CGB_OK) {
             cgb_set_error("%s%s (cg_dropin.c:%d)", "team create failed: ", mb[g].err, __LINE__);
@@ -137,18 +205,15 @@ int cgb_conjugrad_host_opt(const double *A, const double *b, double *x, int64_t 
         pthread_mutex_unlock(&g_team_mu);
         return rc;
     }
-    pthread_t th[MAX_GPUS];
     member_t mb[MAX_GPUS];
     memset(mb, 0, sizeof mb);
     for (int g = 0; g < gpus; ++g) {
         mb[g].g = g; mb[g].gpus = gpus; mb[g].slot = &g_team.ctx[g];
         mb[g].A = A; mb[g].b = b; mb[g].x = x; mb[g].n = n; mb[g].opt = opt;
-        pthread_create(&th[g], NULL, team_solve_main, &mb[g]);
     }
-    for (int g = 0; g < gpus; ++g) pthread_join(th[g], NULL);
-    rc = CGB_OK;
-    for (int g = 0; g < gpus; ++g)
-        if (mb[g].rc != CGB_OK) { rc = mb[g].rc; cgb_set_error("%s%s (cg_dropin.c:%d)", "rank failed: ", mb[g].err, __LINE__); break; }
+    rc = team_run(team_solve_main, mb, sizeof mb[0], gpus);
+    TEAM_COLLECT(mb, gpus, rc, "rank failed: ");
+    if (rc != CGB_OK) team_release_keep_error();       /* contexts and communicators of a failed call are not reused */
     if (rc == CGB_OK && stats) {
         *stats = mb[0].stats;
         for (int g = 1; g < gpus; ++g) {                  /* MPI_Barrier-bracketed timers: slowest rank */
@@ -201,17 +266,15 @@ int cgb_solve_generated(int64_t n, uint64_t seed, unsigned flags, int gpus,
     pthread_mutex_lock(&g_team_mu);
     int rc = team_ensure(gpus);
     if (rc != CGB_OK) { pthread_mutex_unlock(&g_team_mu); return rc; }
-    pthread_t th[MAX_GPUS];
     genmember_t mb[MAX_GPUS];
     memset(mb, 0, sizeof mb);
     for (int g = 0; g < gpus; ++g) {
         mb[g].g = g; mb[g].gpus = gpus; mb[g].slot = &g_team.ctx[g];
         mb[g].n = n; mb[g].seed = seed; mb[g].flags = flags; mb[g].opt = opt; mb[g].x = x;
-        pthread_create(&th[g], NULL, team_generated_main, &mb[g]);
     }
-    for (int g = 0; g < gpus; ++g) pthread_join(th[g], NULL);
-    for (int g = 0; g < gpus; ++g)
-        if (mb[g].rc != CGB_OK) { rc = mb[g].rc; cgb_set_error("%s%s (cg_dropin.c:%d)", "rank failed: ", mb[g].err, __LINE__); break; }
+    rc = team_run(team_generated_main, mb, sizeof mb[0], gpus);
+    TEAM_COLLECT(mb, gpus, rc, "rank failed: ");
+    if (rc != CGB_OK) team_release_keep_error();
     if (rc == CGB_OK && stats) {
         *stats = mb[0].stats;
         for (int g = 1; g < gpus; ++g) {
@@ -269,21 +332,19 @@ int cgb_conjugrad_files(const char *fileA, const char *fileB, const char *fileX,
     pthread_mutex_lock(&g_team_mu);
     int rc = team_ensure(gpus);
     if (rc != CGB_OK) { pthread_mutex_unlock(&g_team_mu); return rc; }
-    pthread_t th[MAX_GPUS];
     filemember_t mb[MAX_GPUS];
     memset(mb, 0, sizeof mb);
-    /* two collective phases: a rank whose input is bad must not leave the others inside a
-     * solve that waits for it */
+    /* two phases (cgb_load_text lets the ranks agree on its outcome, so one phase would do; two keep the
+     * first failing rank's message -- the name of the bad file -- rather than "another rank failed") */
     for (int phase = 0; phase < 2 && rc == CGB_OK; ++phase) {
         for (int g = 0; g < gpus; ++g) {
             mb[g].g = g; mb[g].gpus = gpus; mb[g].slot = &g_team.ctx[g]; mb[g].n = n;
             mb[g].fileA = fileA; mb[g].fileB = fileB; mb[g].fileX = fileX; mb[g].opt = opt; mb[g].x = x;
-            pthread_create(&th[g], NULL, phase == 0 ? team_files_main : team_files_solve_main, &mb[g]);
         }
-        for (int g = 0; g < gpus; ++g) pthread_join(th[g], NULL);
-        for (int g = 0; g < gpus; ++g)
-            if (mb[g].rc != CGB_OK) { rc = mb[g].rc; cgb_set_error("%s%s (cg_dropin.c:%d)", "", mb[g].err, __LINE__); break; }
+        rc = team_run(phase == 0 ? team_files_main : team_files_solve_main, mb, sizeof mb[0], gpus);
+        TEAM_COLLECT(mb, gpus, rc, "");
     }
+    if (rc != CGB_OK && rc != CGB_ERR_IO) team_release_keep_error();
     if (rc == CGB_OK && stats) {
         *stats = mb[0].stats;
         for (int g = 1; g < gpus; ++g) {
@@ -307,11 +368,24 @@ int cgb_conjugrad_host(const double *A, const double *b, double *x, int64_t n, d
 }
 
 /* ------------------------------------------------------------ reference-named wrappers */
+/* The run-time ROWS.  The reference's conjugrad() reads a compile-time macro and is re-entrant
+ * (serialConjugate.c:180, no globals); here the order set by a thread belongs to that thread, so two
+ * threads can run systems of different order side by side.  A thread that never set one uses the
+ * last value any thread set (a main() that sets the order and calls conjugrad() from a worker). */
 static int64_t g_dimension = 0;
+static __thread int64_t tl_dimension = 0;
 static __thread cgb_stats tl_stats;
 static __thread int tl_have_stats = 0;
 
-void cgb_set_dimension(int64_t n) { g_dimension = n; }
+void cgb_set_dimension(int64_t n)
+{
+    tl_dimension = n;
+    __atomic_store_n(&g_dimension, n, __ATOMIC_RELAXED);
+}
+static int64_t current_dimension(void)
+{
+    return tl_dimension > 0 ? tl_dimension : __atomic_load_n(&g_dimension, __ATOMIC_RELAXED);
+}
 
 int cgb_last_stats(cgb_stats *out)
 {
@@ -331,11 +405,12 @@ static int env_int(const char *name, int dflt)
 void conjugrad(double *matrixA, double *vectorB, double *vectorX)
 {
     tl_have_stats = 0;
-    if (g_dimension < 1) {
+    const int64_t dim = current_dimension();
+    if (dim < 1) {
         fprintf(stderr, "conjugrad: matrix order not set (call cgb_set_dimension(n): the run-time ROWS)\n");
         return;
     }
-    int rc = cgb_conjugrad_host(matrixA, vectorB, vectorX, g_dimension, CGB_EPSILON, 0,
+    int rc = cgb_conjugrad_host(matrixA, vectorB, vectorX, dim, CGB_EPSILON, 0,
                                 env_int("CGB_GPUS", 1), &tl_stats);
     if (rc != CGB_OK) { fprintf(stderr, "conjugrad: %s\n", cgb_last_error()); return; }
     tl_have_stats = 1;
@@ -351,27 +426,51 @@ static pthread_cond_t g_rdv_cv = PTHREAD_COND_INITIALIZER;
 static unsigned char g_rdv_id[128];
 static int g_rdv_have = 0, g_rdv_taken = 0;
 
+static void launch_tag(char tag[64])
+{
+    static const char *const vars[] = {"CGB_RUN_ID", "TORCHELASTIC_RUN_ID", "SLURM_JOB_ID", "OMPI_MCA_ess_base_jobid", "PMIX_NAMESPACE", "PMI_JOBID"};
+    memset(tag, 0, 64);
+    for (size_t i = 0; i < sizeof vars / sizeof vars[0]; ++i) {
+        const char *v = getenv(vars[i]);
+        if (v && *v) { snprintf(tag, 64, "%.15s=%.46s", vars[i], v); return; }
+    }
+}
+
 static int rendezvous_id(int rank, int np, unsigned char *id)
 {
     const char *path = getenv("CGB_ID_FILE");
     if (path && *path) {
+        /* File layout: 128 bytes of id, then a 64-byte launch tag.  The tag is whatever the launcher gives
+         * every rank of ONE launch (CGB_RUN_ID, torchrun's TORCHELASTIC_RUN_ID, SLURM_JOB_ID, OpenMPI's
+         * OMPI_MCA_ess_base_jobid, PMI_JOBID / PMIX_NAMESPACE); readers ignore a file whose tag is not theirs,
+         * so the id a crashed run left behind is never taken for this run's.  Without any such variable a
+         * reader accepts only a file written after it started (less two minutes of launch skew).  Rank 0
+         * also removes a stale file before it makes the new id. */
+        char tag[64];
+        launch_tag(tag);
         if (rank == 0) {
+            (void)unlink(path);
             int rc = cgb_unique_id(id);
             if (rc != CGB_OK) return rc;
             char tmp[4096];
             snprintf(tmp, sizeof tmp, "%s.tmp.%d", path, (int)getpid());
             FILE *f = fopen(tmp, "wb");
-            if (!f || fwrite(id, 1, 128, f) != 128) { if (f) fclose(f); return CGB_ERR_IO; }
+            if (!f || fwrite(id, 1, 128, f) != 128 || fwrite(tag, 1, sizeof tag, f) != sizeof tag) { if (f) fclose(f); return CGB_ERR_IO; }
             fclose(f);
             if (rename(tmp, path) != 0) return CGB_ERR_IO;
             return CGB_OK;
         }
+        const time_t started = time(NULL);
         for (int tries = 0; tries < 600000; ++tries) {
             FILE *f = fopen(path, "rb");
             if (f) {
+                char got_tag[64];
                 size_t got = fread(id, 1, 128, f);
+                size_t gt = fread(got_tag, 1, sizeof got_tag, f);
+                struct stat sb;
+                int fresh = fstat(fileno(f), &sb) == 0 && sb.st_mtime >= started - 120;
                 fclose(f);
-                if (got == 128) return CGB_OK;
+                if (got == 128 && gt == sizeof got_tag && memcmp(got_tag, tag, sizeof tag) == 0 && (tag[0] != '\0' || fresh)) return CGB_OK;
             }
             usleep(100);
         }
@@ -391,6 +490,13 @@ static int rendezvous_id(int rank, int np, unsigned char *id)
     if (++g_rdv_taken == np) { g_rdv_have = 0; pthread_cond_broadcast(&g_rdv_cv); }
     pthread_mutex_unlock(&g_rdv_mu);
     return rc;
+}
+
+/* test hook: the rendezvous alone (CPU tests of the stale-file rules) */
+int cgb_debug_rendezvous_id(int rank, int np, void *id128)
+{
+    if (!id128 || np < 1 || rank < 0 || rank >= np) return CGB_ERR_ARG;
+    return rendezvous_id(rank, np, id128);
 }
 
 static __thread cgb_ctx *tl_rank_ctx = NULL;

@@ -69,11 +69,19 @@ static int load_block_on_host(cgb_ctx *c, const char *fileA, int64_t first, int6
     return CGB_OK;
 }
 
+static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *fileB, const char *fileX);
 int cgb_load_text(cgb_ctx *c, int64_t n, const char *fileA, const char *fileB, const char *fileX)
 {
     if (!c || !fileA || !fileB || !fileX) { cgb_set_error("%s%s (cg_ingest.c:%d)", "cgb_load_text: null argument", "", __LINE__); return CGB_ERR_ARG; }
     int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
+    /* a rank whose part of the input is bad must not leave the others in the solve: all learn of it here */
+    return cgb_ranks_agree(c, load_text_body(c, n, fileA, fileB, fileX));
+}
+
+static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *fileB, const char *fileX)
+{
+    int rc = CGB_OK;
     const double t0 = now_s();
     const int64_t m = c->m, first = (int64_t)c->rank * m * n, count = m * n;
     cudaStream_t st = c->stream;

@@ -76,6 +76,8 @@ struct cgb_ctx {
     int peer_ok;                      /* every rank mapped every window                  */
     cgk_peers peers;
     unsigned long long *probe;        /* CGB_PROBE=1: per-CTA time stamps of the exchange kernels (CGK_PROBE_WORDS) */
+    int *d_agree;                     /* 2 ints: the status all-reduce of cgb_ranks_agree */
+    int broken;                       /* a collective failed or a peer stopped answering: no further collectives on this context */
     unsigned int gen;                 /* solve generation, in lockstep on all ranks      */
     int comm_mode;                    /* CGB_COMM_* in use by the current / last solve   */
     char peer_why[160];               /* why peer_ok == 0                                */
@@ -103,6 +105,10 @@ struct cgb_ctx {
 void cgb_set_error(const char *fmt, const char *a, const char *b, int line);
 /* (Re)allocates the device arrays (and, with ranks > 1, the peer window: collective) for order n. */
 int cgb_ensure_problem(cgb_ctx *c, int64_t n);
+/* MIN over the ranks of a status: everybody learns whether everybody is fine (cg_solver.c). */
+int cgb_ranks_agree(cgb_ctx *c, int rc_local);
+/* Unmaps the peers' windows of a context (team tear-down: all unmap before any frees). */
+void cgb_unmap_peers(cgb_ctx *c);
 /* cg_stage.c */
 int  cgb_host_is_pageable(const void *p);
 int  cgb_stage_mode(void);

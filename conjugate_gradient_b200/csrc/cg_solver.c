@@ -234,11 +234,61 @@ int cgb_create_rank(cgb_ctx **out, int device, int rank, int ranks, const void *
     return CGB_OK;
 }
 
+static void drop_graph(cgb_ctx *c);
+static void close_peers(cgb_ctx *c);
+void cgb_unmap_peers(cgb_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    drop_graph(c);                    /* the captured kernels point into the peers' windows */
+    close_peers(c);
+    (void)cudaGetLastError();
+}
+
 static void drop_graph(cgb_ctx *c)
 {
     if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = NULL; }
     if (c->graph) { cudaGraphDestroy(c->graph); c->graph = NULL; }
     memset(&c->graph_key, 0, sizeof c->graph_key);
+}
+
+/* Fault injection for the tests of the agreement below: CGB_DEBUG_FAIL_<step>=<rank> makes that rank
+ * (of a team of several) fail that local step with CGB_ERR_NOMEM, as if it had run out of memory. */
+static int injected_failure(const cgb_ctx *c, const char *step)
+{
+    char name[64];
+    snprintf(name, sizeof name, "CGB_DEBUG_FAIL_%s", step);
+    const char *e = getenv(name);
+    if (!e || !*e || c->ranks < 2 || atoi(e) != c->rank) return 0;
+    snprintf(tl_err, sizeof tl_err, "rank %d: injected failure of step %s (%s is set)", c->rank, step, name);
+    return 1;
+}
+
+/* Every rank contributes its status (CGB_OK or a negative code) and all ranks get the smallest one:
+ * the ranks agree BEFORE a collective step whether to enter it, so that a rank which failed on its
+ * own (out of device memory, a bad input file, a failed copy) never leaves the others inside an NCCL
+ * call or a spin on a mailbox -- NCCL has no time-out.  One 4-byte all-reduce; ranks == 1: nothing. */
+int cgb_ranks_agree(cgb_ctx *c, int rc_local)
+{
+    if (c->ranks < 2 || !c->has_comm || c->broken) return rc_local;
+    if (!c->d_agree) {
+        if (cudaMalloc((void **)&c->d_agree, 2 * sizeof(int)) != cudaSuccess) { (void)cudaGetLastError(); c->d_agree = NULL; }
+    }
+    int agreed = rc_local;
+    if (!c->d_agree ||
+        cudaMemcpyAsync(c->d_agree, &rc_local, sizeof(int), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+        ncclAllReduce(c->d_agree, c->d_agree + 1, 1, ncclInt, ncclMin, c->comm, c->stream) != ncclSuccess ||
+        cudaMemcpyAsync(&agreed, c->d_agree + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+        (void)cudaGetLastError();
+        c->broken = 1;
+        if (rc_local == CGB_OK) cgb_set_error("%s%s (cg_solver.c:%d)", "the ranks could not agree on a status (NCCL or CUDA failure)", "", __LINE__);
+        return rc_local != CGB_OK ? rc_local : CGB_ERR_NCCL;
+    }
+    if (agreed != CGB_OK && rc_local == CGB_OK)
+        snprintf(tl_err, sizeof tl_err, "rank %d: another rank failed (status %d) before a collective step; all ranks give up together", c->rank, agreed);
+    return agreed;
 }
 
 /* Unmaps the peers' windows.  No collective here: a solve ends with the all-gather of x, so
@@ -258,7 +308,16 @@ static void close_peers(cgb_ctx *c)
 static void free_problem(cgb_ctx *c)
 {
     drop_graph(c);
+    int ipc = 0;
+    for (int g = 0; g < CGK_MAX_RANKS; ++g) ipc |= c->peer_ipc[g];
     close_peers(c);
+    /* The window was exported with cudaIpcGetMemHandle and other PROCESSES hold it open: freeing it
+     * before they have closed their mapping is undefined (CUDA runtime, cudaIpcCloseMemHandle).  Every
+     * rank unmaps first (above), then all meet, then each frees its own.  Ranks that are threads of
+     * one process map each other by pointer and need no rendezvous (and may be torn down one after the
+     * other by a single thread, cg_dropin.c: team_release).  A communicator already known to be broken
+     * is not waited on. */
+    if (ipc && c->win) (void)cgb_ranks_agree(c, CGB_OK);
     gfree(c, c->A); gfree(c, c->b); gfree(c, c->r); gfree(c, c->Ap); gfree(c, c->svec);
     c->svec = NULL;
     if (c->win) cudaFree(c->win); else gfree(c, c->p_full);
@@ -385,7 +444,8 @@ int cgb_destroy(cgb_ctx *c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_problem(c);
     cgb_stage_release(c);
-    if (c->has_comm) ncclCommDestroy(c->comm);
+    cudaFree(c->d_agree);
+    if (c->has_comm) { if (c->broken) ncclCommAbort(c->comm); else ncclCommDestroy(c->comm); }
     for (int i = 0; i < 3; ++i) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < c->n_gemv_ev; ++i) cudaEventDestroy(c->gemv_ev[i]);
     free(c->gemv_ev);
@@ -413,6 +473,45 @@ int cgb_device_info(cgb_ctx *c, int *device, int *sm_count, int64_t *free_bytes,
 }
 
 /* ------------------------------------------------------------------ problem */
+/* The device arrays of an n x n system on this rank; no collective inside. */
+static int alloc_problem(cgb_ctx *c, int64_t n, int64_t m)
+{
+    if (injected_failure(c, "ALLOC")) return CGB_ERR_NOMEM;
+    const size_t abytes = (size_t)m * (size_t)n * sizeof(double);
+    cudaError_t e = galloc(c, (void **)&c->A, abytes, "A");
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        snprintf(tl_err, sizeof tl_err, "can't allocate memory for matrix block: %zu bytes on GPU %d (%s)",
+                 abytes, c->device, cudaGetErrorString(e));
+        return CGB_ERR_NOMEM;
+    }
+#define AL(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { (void)cudaGetLastError(); \
+        cgb_set_error("can't allocate memory for vector: %s in `%s` (cg_solver.c:%d)", cudaGetErrorString(e_), #call, __LINE__); \
+        return e_ == cudaErrorMemoryAllocation ? CGB_ERR_NOMEM : CGB_ERR_CUDA; } } while (0)
+    AL(galloc(c, (void **)&c->b, (size_t)m * sizeof(double), "b"));
+    AL(galloc(c, (void **)&c->r, (size_t)m * sizeof(double), "r"));
+    AL(galloc(c, (void **)&c->Ap, (size_t)m * sizeof(double), "Ap"));
+    AL(galloc(c, (void **)&c->svec, (size_t)m * sizeof(double), "s"));
+    if (c->ranks > 1) {
+        /* [mailbox | p_full (n) | column-sum receive area (ranks x m = n)] in one allocation of whole
+         * 2 MiB pages: one IPC handle */
+        const size_t gran = (size_t)2 << 20;
+        const size_t used = CGK_WINDOW_HEADER_BYTES + 2 * (size_t)n * sizeof(double);
+        c->win_bytes = (used + CGB_GUARD_BYTES + gran - 1) / gran * gran;
+        AL(cudaMalloc(&c->win, c->win_bytes));
+        AL(cudaMemsetAsync(c->win, 0, c->win_bytes, c->stream));
+        AL(cudaMemsetAsync((char *)c->win + used, CGB_GUARD_BYTE, CGB_GUARD_BYTES, c->stream));
+        AL(cudaStreamSynchronize(c->stream));
+        c->p_full = (double *)((char *)c->win + CGK_WINDOW_HEADER_BYTES);
+    } else {
+        AL(galloc(c, (void **)&c->p_full, (size_t)n * sizeof(double), "p"));
+    }
+    AL(galloc(c, (void **)&c->x_full, (size_t)n * sizeof(double), "x"));
+    AL(galloc(c, (void **)&c->partials_gemv, (size_t)cgk_gemv_max_ctas(m) * sizeof(double), "partials_gemv"));
+#undef AL
+    return CGB_OK;
+}
+
 int cgb_ensure_problem(cgb_ctx *c, int64_t n)
 {
     if (n < 1) FAIL(CGB_ERR_ARG, "matrix order must be >= 1");
@@ -426,48 +525,40 @@ int cgb_ensure_problem(cgb_ctx *c, int64_t n)
     CU(cudaSetDevice(c->device));
     if (n != c->cap_n || m != c->cap_m) {
         free_problem(c);
-        const size_t abytes = (size_t)m * (size_t)n * sizeof(double);
-        cudaError_t e = galloc(c, (void **)&c->A, abytes, "A");
-        if (e != cudaSuccess) {
-            (void)cudaGetLastError();
-            snprintf(tl_err, sizeof tl_err, "can't allocate memory for matrix block: %zu bytes on GPU %d (%s)",
-                     abytes, c->device, cudaGetErrorString(e));
-            return CGB_ERR_NOMEM;
+        int rc = alloc_problem(c, n, m);                   /* local */
+        rc = cgb_ranks_agree(c, rc);                       /* all ranks allocated, or none goes on */
+        if (rc == CGB_OK && c->ranks > 1) {
+            rc = exchange_windows(c, n);                   /* collective */
+            rc = cgb_ranks_agree(c, rc);
         }
-        CU(galloc(c, (void **)&c->b, (size_t)m * sizeof(double), "b"));
-        CU(galloc(c, (void **)&c->r, (size_t)m * sizeof(double), "r"));
-        CU(galloc(c, (void **)&c->Ap, (size_t)m * sizeof(double), "Ap"));
-        CU(galloc(c, (void **)&c->svec, (size_t)m * sizeof(double), "s"));
-        if (c->ranks > 1) {
-            /* [mailbox | p_full] in one allocation of whole 2 MiB pages: one IPC handle */
-            const size_t gran = (size_t)2 << 20;
-            /* [mailbox | p_full (n) | column-sum receive area (ranks x m = n)] */
-            const size_t used = CGK_WINDOW_HEADER_BYTES + 2 * (size_t)n * sizeof(double);
-            c->win_bytes = (used + CGB_GUARD_BYTES + gran - 1) / gran * gran;
-            CU(cudaMalloc(&c->win, c->win_bytes));
-            CU(cudaMemsetAsync(c->win, 0, c->win_bytes, c->stream));
-            CU(cudaMemsetAsync((char *)c->win + used, CGB_GUARD_BYTE, CGB_GUARD_BYTES, c->stream));
-            CU(cudaStreamSynchronize(c->stream));
-            c->p_full = (double *)((char *)c->win + CGK_WINDOW_HEADER_BYTES);
-            int rc = exchange_windows(c, n);
-            if (rc != CGB_OK) return rc;
-        } else {
-            CU(galloc(c, (void **)&c->p_full, (size_t)n * sizeof(double), "p"));
+        if (rc != CGB_OK) {
+            char keep[sizeof tl_err];
+            snprintf(keep, sizeof keep, "%s", tl_err);
+            free_problem(c);
+            snprintf(tl_err, sizeof tl_err, "%s", keep);
+            return rc;
         }
-        CU(galloc(c, (void **)&c->x_full, (size_t)n * sizeof(double), "x"));
-        CU(galloc(c, (void **)&c->partials_gemv, (size_t)cgk_gemv_max_ctas(m) * sizeof(double), "partials_gemv"));
         c->cap_n = n; c->cap_m = m;
     }
     c->n = n; c->m = m;
     return CGB_OK;
 }
 
+static int load_host_body(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows, const double *x0_full);
 int cgb_load_host(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows,
                   const double *x0_full)
 {
     if (!c || !A_rows || !b_rows || !x0_full) FAIL(CGB_ERR_ARG, "cgb_load_host: null argument");
     int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
+    /* every rank learns whether every rank's copy arrived: nobody enters the (collective) solve alone */
+    return cgb_ranks_agree(c, load_host_body(c, n, A_rows, b_rows, x0_full));
+}
+
+static int load_host_body(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows, const double *x0_full)
+{
+    int rc = CGB_OK;
+    if (injected_failure(c, "LOAD")) return CGB_ERR_NOMEM;
     const int64_t m = c->m;
     double t0 = now_s();
     CU(cudaMemcpyAsync(c->x_full, x0_full, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
@@ -504,17 +595,24 @@ static int symv_shape_ok(const cgb_ctx *c, int64_t n)
  * symmetric product never reads: only the rank's tiles of the tile list travel (for one rank
  * the 512 x 512 tiles on and above the diagonal, n (n + 512) / 2 values instead of n^2).
  * Strided copies, one per run of adjacent tiles in a tile row. */
+static int load_host_symmetric_body(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows, const double *x0_full);
 int cgb_load_host_symmetric(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows,
                             const double *x0_full)
 {
     if (!c || !A_rows || !b_rows || !x0_full) FAIL(CGB_ERR_ARG, "cgb_load_host_symmetric: null argument");
     int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
-    if (!symv_shape_ok(c, n)) {
+    if (!symv_shape_ok(c, n)) {          /* the same answer on every rank */
         snprintf(tl_err, sizeof tl_err, "cgb_load_host_symmetric needs n / ranks to be a multiple of %d and, on several ranks, "
                  "the peer-memory exchange (n = %lld, ranks = %d)", cgk_symv_tile(), (long long)n, c->ranks);
         return CGB_ERR_ARG;
     }
+    return cgb_ranks_agree(c, load_host_symmetric_body(c, n, A_rows, b_rows, x0_full));
+}
+
+static int load_host_symmetric_body(cgb_ctx *c, int64_t n, const double *A_rows, const double *b_rows, const double *x0_full)
+{
+    int rc = CGB_OK;
     const int64_t m = c->m, T = cgk_symv_tile();
     const int multi = c->ranks > 1;
     cgk_symplan sp;
@@ -562,11 +660,17 @@ int cgb_load_host_symmetric(cgb_ctx *c, int64_t n, const double *A_rows, const d
     return CGB_OK;
 }
 
+static int generate_body(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags);
 int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
 {
     if (!c) FAIL(CGB_ERR_ARG, "cgb_generate: null context");
     int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
+    return cgb_ranks_agree(c, generate_body(c, n, seed, flags));
+}
+
+static int generate_body(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
+{
     const int64_t row0 = (int64_t)c->rank * c->m;
     KL(cgk_generate_A(c->A, n, row0, c->m, seed, flags, c->stream));
     KL(cgk_generate_b(c->b, n, row0, c->m, seed, flags, c->stream));
@@ -883,10 +987,20 @@ static int ensure_gemv_events(cgb_ctx *c, int pairs)
     return CGB_OK;
 }
 
-int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
+/* What cgb_solve settles on this rank alone before the first collective step: options, transport,
+ * launch plan, workspaces of the symmetric product, the captured graph.  Anything here may fail on
+ * one rank only (device memory), which is why cgb_solve lets the ranks agree on the outcome. */
+typedef struct {
+    cgb_options o;
+    int64_t max_iter;
+    const cgk_peers *peers;
+    cgk_gemv_plan req;
+    int use_graph, chunk, timed_pairs;
+} solve_prep;
+
+static int solve_prepare(cgb_ctx *c, const cgb_options *opt, solve_prep *sp)
 {
-    if (!c) FAIL(CGB_ERR_ARG, "cgb_solve: null context");
-    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_solve: no problem loaded (cgb_load_host / cgb_generate first)");
+    if (injected_failure(c, "PREPARE")) return CGB_ERR_NOMEM;
     cgb_options o;
     if (opt) o = *opt; else cgb_default_options(&o);
     if (!(o.eps > 0.0)) o.eps = CGB_EPSILON;
@@ -927,7 +1041,6 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     if (peers) KL(cgk_gemv_make_plan_comm(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
     else KL(cgk_gemv_make_plan(&c->plan, c->m, c->n, c->A, c->p_full, c->sm_count));
     if ((int64_t)c->plan.grid > cgk_gemv_max_ctas(c->m)) FAIL(CGB_ERR_STATE, "gemv grid exceeds workspace");
-    if ((++c->gen & 0x3ffu) == 0u) ++c->gen;              /* tags never collide with zeroed memory */
     c->use_symv = 0;
     if (c->tiles_only && !o.symmetric)
         FAIL(CGB_ERR_STATE, "the matrix came through cgb_load_host_symmetric: only the symmetric product's tiles are on the "
@@ -965,7 +1078,6 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         const char *e = getenv("CGB_XRP");
         c->use_xrp = peers && o.cg_variant == CGB_CG_CLASSIC && (e && *e == '1') && cgk_xrp_supported(c->m, c->sm_count);
     }
-    double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
     const int use_graph = o.use_graph && !o.time_gemv;
     int chunk = 0;
     if (use_graph) {
@@ -984,7 +1096,29 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
         int rc = ensure_gemv_events(c, timed_pairs);
         if (rc != CGB_OK) return rc;
     }
+    sp->o = o; sp->max_iter = max_iter; sp->peers = peers; sp->req = req;
+    sp->use_graph = use_graph; sp->chunk = chunk; sp->timed_pairs = timed_pairs;
+    return CGB_OK;
+}
 
+int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
+{
+    if (!c) FAIL(CGB_ERR_ARG, "cgb_solve: null context");
+    if (!c->loaded) FAIL(CGB_ERR_STATE, "cgb_solve: no problem loaded (cgb_load_host / cgb_generate first)");
+    if (c->broken) FAIL(CGB_ERR_COMM, "cgb_solve: an earlier collective step of this context failed; destroy it and create a new one");
+    solve_prep sp;
+    memset(&sp, 0, sizeof sp);
+    int prc = cgb_ranks_agree(c, solve_prepare(c, opt, &sp));     /* all ranks enter the solve, or none */
+    if (prc != CGB_OK) return prc;
+    const cgb_options o = sp.o;
+    const int64_t max_iter = sp.max_iter;
+    const int multi = c->ranks > 1;
+    cudaStream_t st = c->stream;
+    const cgk_peers *peers = sp.peers;
+    const cgk_gemv_plan req = sp.req;
+    const int use_graph = sp.use_graph, chunk = sp.chunk, timed_pairs = sp.timed_pairs;
+    double *p_loc = c->p_full + (size_t)c->rank * (size_t)c->m;
+    if ((++c->gen & 0x3ffu) == 0u) ++c->gen;              /* tags never collide with zeroed memory */
     c->launches = 0;
     CU(cudaStreamSynchronize(st));
     const double t0 = now_s();
@@ -1048,6 +1182,7 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     CU(cudaStreamSynchronize(st));
     const double t1 = now_s();
     if (c->h_sc->comm_error != 0) {
+        c->broken = 1;                 /* the ranks are no longer in lockstep: no further collectives on this context */
         snprintf(tl_err, sizeof tl_err, "rank %d: a peer rank did not answer within %.0f s during the solve "
                  "(iteration %lld); results are invalid", c->rank, CGK_SPIN_TIMEOUT_NS * 1e-9, (long long)c->h_sc->iters);
         return CGB_ERR_COMM;

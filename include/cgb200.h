@@ -161,6 +161,10 @@ int cgb_debug_check_guards(cgb_ctx *ctx);
 /* Self test of the above (refused without CGB_DEBUG_GUARDS=1): stores one double at element
  * `offset` of array `what` (1 b, 2 x, 3 r, 5 Ap), -32 <= offset < length + 32. */
 int cgb_debug_poke(cgb_ctx *ctx, int what, int64_t offset, double value);
+/* The NCCL-id rendezvous of conjugrad_mpi() alone (tests): rank 0 makes a 128-byte id, every rank of
+ * the np callers receives it -- through the file named by CGB_ID_FILE when set (ranks = processes; a file
+ * left by another launch is ignored), else through a process-wide slot (ranks = threads). */
+int cgb_debug_rendezvous_id(int rank, int np, void *id128);
 /* With CGB_PROBE=1 in the environment of a solve on several ranks (peer-memory exchange), the
  * exchange-fused kernels leave per-CTA time stamps of their last launch: when a CTA started,
  * finished its own column block, saw the peers' flags, ended, and how long it polled.  Copies up

@@ -258,3 +258,26 @@ def test_torchrun_bench_two_ranks(cg):
     # one process per GPU: the windows are mapped through CUDA IPC
     assert "peer" in line["implementation"]["exchange"]
     assert line["parity"]["ok"] and line["parity"]["ranks"] == 2 and line["parity"]["fixed_run"]["rel_err_x"] <= 1e-10
+
+
+@pytest.mark.parametrize("step", ["ALLOC", "LOAD", "PREPARE"])
+@pytest.mark.parametrize("gpus", [2, 4])
+def test_a_rank_failing_alone_takes_the_team_with_it_instead_of_hanging(cg, gpus, step, monkeypatch):
+    """a rank that fails a local step (no device memory for its block, a failed copy, no workspace)
+    used to leave its peers inside the next NCCL call for ever.  The ranks now agree on a status before every
+    collective step: with the failure injected on the last rank every rank returns the error, promptly, and the
+    next call -- the team is rebuilt -- solves normally."""
+    need(cg, gpus)
+    import time
+    n, seed = 2048, 3
+    A, b = O.gen_A(n, seed), O.gen_b(n, seed)
+    monkeypatch.setenv(f"CGB_DEBUG_FAIL_{step}", str(gpus - 1))
+    t0 = time.time()
+    with pytest.raises(cg.CgbError) as e:
+        cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus)
+    assert time.time() - t0 < 60.0
+    assert e.value.code == -5 and "injected failure" in str(e.value), str(e.value)
+    monkeypatch.delenv(f"CGB_DEBUG_FAIL_{step}")
+    x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus)
+    xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
+    assert relerr(x, xo) <= RTOL_X and st["ranks"] == gpus
