@@ -8,7 +8,7 @@ but every computing call needs a B200 and raises CgbError otherwise, and a
 missing library raises ImportError instead of falling back to anything.
 """
 from ._binding import (  # noqa: F401
-    CG_CLASSIC, CG_FUSED_REDUCTIONS, CGB_EPSILON, COMM_AUTO, COMM_NCCL, COMM_PEER, GEMV_AUTO, GEMV_BULK, GEMV_LDG, GEN_KAPPA_LOG2, GEN_ROUND4, HEADER_SYMBOLS, LIB_PATH,
+    CG_CLASSIC, CG_FUSED_REDUCTIONS, CGB_EPSILON, COMM_AUTO, COMM_NCCL, COMM_PEER, GEMV_AUTO, GEMV_BULK, GEMV_LDG, GEN_GRAM, GEN_KAPPA_LOG2, GEN_ROUND4, GEN_SPECTRUM, HEADER_SYMBOLS, LIB_PATH,
     CgbError, Context, Options, Stats, build, conjugrad_files, conjugrad_host, device_count, lib,
     read_dimensions, read_values, solve_generated, unique_id, write_values,
 )

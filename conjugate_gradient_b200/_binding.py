@@ -13,7 +13,9 @@ CLI_PATH = os.path.join(PKG_DIR, "lib", "cg_b200")
 HEADER = os.path.join(ROOT, "include", "cgb200.h")
 
 CGB_EPSILON = 1.0e-6          # serialConjugate.c:28
-GEN_ROUND4 = 1
+
+
+GEN_ROUND4, GEN_SPECTRUM, GEN_GRAM = 1, 2, 4
 
 
 def GEN_KAPPA_LOG2(k):

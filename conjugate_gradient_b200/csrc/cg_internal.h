@@ -83,6 +83,7 @@ struct cgb_ctx {
     char peer_why[160];               /* why peer_ok == 0                                */
     /* symmetric product (cg_symv.cu) */
     int sym_state;                    /* 0 not checked, 1 exactly symmetric, -1 not      */
+    int sym_pending;                  /* several ranks: the cross-rank check is due at the next solve */
     int tiles_only;                   /* cgb_load_host_symmetric: only the tiles the symmetric product reads are on the device */
     int use_symv, symv_ru, symv_split;
     double *sy_rowpart, *sy_colpart;  /* (n / T) * n each                                */

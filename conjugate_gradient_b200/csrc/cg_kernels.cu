@@ -1125,6 +1125,21 @@ cgb_generate_A_kernel(double *__restrict__ A, long long n, long long row0, long 
     }
 }
 
+/* CGB_GEN_SPECTRUM (spd_gen.cuh): A = H diag(lambda) H element by element */
+__global__ void __launch_bounds__(256)
+cgb_generate_spectrum_kernel(double *__restrict__ A, long long n, long long row0, long long m,
+                             uint64_t key, unsigned flags, double inv, double s4)
+{
+    const long long total = m * n;
+    for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total;
+         e += (long long)gridDim.x * 256) {
+        const long long i = e / n, j = e - i * n;
+        double val = cgb_gen_spectrum_elem(key, (uint64_t)n, (uint64_t)(row0 + i), (uint64_t)j, flags, inv, s4);
+        if (flags & CGB_GEN_ROUND4) val = __ddiv_rn(rint(__dmul_rn(val, 1.0e4)), 1.0e4);
+        A[e] = val;
+    }
+}
+
 __global__ void __launch_bounds__(256)
 cgb_generate_b_kernel(double *__restrict__ b, long long n, long long row0, long long m,
                   uint64_t key, unsigned flags)
@@ -1526,6 +1541,17 @@ extern "C" int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uin
     if (g > 148 * 32) g = 148 * 32;
     cgb_generate_A_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)row0,
                                                                (long long)m, cgb_gen_key(seed), flags);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cgk_generate_spectrum_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                                       unsigned flags, double inv, double s4, void *stream)
+{
+    int64_t g = ceil_div(m * n, 256 * 8);
+    if (g < 1) g = 1;
+    if (g > 148 * 32) g = 148 * 32;
+    cgb_generate_spectrum_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)row0, (long long)m,
+                                                                          cgb_gen_key(seed), flags, inv, s4);
     return (int)cudaGetLastError();
 }
 

@@ -227,6 +227,11 @@ int cgk_generate_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
                    unsigned flags, void *stream);
 int cgk_generate_b(double *b, int64_t n, int64_t row0, int64_t m, uint64_t seed,
                    unsigned flags, void *stream);
+/* The other two families of spd_gen.cuh: CGB_GEN_SPECTRUM (inv, s4 from cgb_gen_spectrum_scalars on the
+ * host) and CGB_GEN_GRAM (cg_gram.cu: R R' + n diag(d) on the FP64 tensor pipe). */
+int cgk_generate_spectrum_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed,
+                            unsigned flags, double inv, double s4, void *stream);
+int cgk_generate_gram_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed, unsigned flags, void *stream);
 
 /* Writes `bytes` of zeros-then-ones traffic over buf: evicts L2 between timed launches. */
 int cgk_l2_flush(void *buf, int64_t bytes, void *stream);
@@ -253,6 +258,12 @@ int cgk_symv_comm(const double *A, const double *v, const double *w, double *y, 
                   const cgk_symplan *sp, const cgk_peers *peers, void *stream);
 /* *d_flag = 1 unless a_ij and a_ji are bit-identical for all i, j (and no NaN). */
 int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void *stream);
+/* the same for an n x n block inside a wider matrix (leading dimension ld) */
+int cgk_symmetry_check_ld(const double *A, int64_t n, int64_t ld, int *d_flag, void *stream);
+/* Row-sharded A: 64-bit fingerprints of the rank's G column blocks (sums[0..ranks)) and a NaN flag
+ * (sums[ranks]); blocks (g, h) and (h, g) have equal fingerprints iff a_ij == a_ji throughout them
+ * (up to a 2^-64 chance).  cg_symv.cu. */
+int cgk_symmetry_hash(const double *A, int64_t n, int64_t row0, int64_t m, int ranks, unsigned long long *sums, void *stream);
 
 /* ---- text ingest (cg_ingest.cu): the rank's part of matrixA.txt parsed on the GPU */
 typedef struct cgk_ingest_state {

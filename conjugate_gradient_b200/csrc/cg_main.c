@@ -21,6 +21,9 @@
  *   --seed S          generator seed (default 20170209)   --round4  "%.4f" rounding
  *   --kappa-log2 K    generator: spread the diagonal so that cond(A) ~ 2^K (K = 0: the
  *                     reference's kappa ~ 1.5 family, ~5 iterations)
+ *   --family F        generator: shift (0.5 (R + R') + n I, generateSPDmatrix.m:11,17: the default),
+ *                     gram (R R' + n I, the commented alternative of :12), spectrum (dense matrix
+ *                     with the prescribed eigenvalues n (1 + (2^K - 1) t^2))
  *   --bench-iters K   fixed-iteration timing mode (stop test recorded, not acted on)
  *   --gemv V          1 = streaming loads, 2 = bulk-async ring
  *   --comm nccl|peer  per-iteration exchange with --gpus > 1 (default: peer when the GPUs
@@ -56,6 +59,7 @@
 typedef struct {
     const char *fileA, *fileB, *fileX, *dims, *write_x, *record, *emit;
     int gpus, print_x, stats, round4, gemv, comm, kappa_log2, guard, symmetric, cg_variant;
+    unsigned family;             /* 0, CGB_GEN_SPECTRUM or CGB_GEN_GRAM */
     int64_t gen_n, max_iter, bench_iters;
     uint64_t seed;
     double eps;
@@ -127,6 +131,13 @@ static int parse_cli(int argc, char **argv, cli_t *c)
             if (!strcmp(v, "classic")) c->cg_variant = CGB_CG_CLASSIC;
             else if (!strcmp(v, "fused")) c->cg_variant = CGB_CG_FUSED_REDUCTIONS;
             else { fprintf(stderr, "--cg takes classic or fused\n"); return -1; }
+            ++i;
+        }
+        else if (!strcmp(a, "--family")) {
+            if (!strcmp(v, "shift")) c->family = 0u;                      /* generateSPDmatrix.m:11,17 */
+            else if (!strcmp(v, "gram")) c->family = CGB_GEN_GRAM;         /* its commented alternative, :12 */
+            else if (!strcmp(v, "spectrum")) c->family = CGB_GEN_SPECTRUM; /* prescribed eigenvalues */
+            else { fprintf(stderr, "--family takes shift, gram or spectrum\n"); return -1; }
             ++i;
         }
         else if (!strcmp(a, "--kappa-log2")) {
@@ -295,7 +306,7 @@ int main(int argc, char **argv)
         printf("Computing cg of matrix size : %lld\n", (long long)n * (long long)n);
         x = malloc((size_t)n * sizeof(double));
         if (!x) { printf("can't allocate memory for vector\n"); return 1; }
-        const unsigned gflags = (cli.round4 ? CGB_GEN_ROUND4 : 0u) | CGB_GEN_KAPPA_LOG2(cli.kappa_log2);
+        const unsigned gflags = (cli.round4 ? CGB_GEN_ROUND4 : 0u) | CGB_GEN_KAPPA_LOG2(cli.kappa_log2) | cli.family;
         if (cli.emit && emit_files(&cli, n, gflags) != 0) {
             fprintf(stderr, "cg_b200: cannot write the %s_* files: %s\n", cli.emit, cgb_last_error());
             return 1;

@@ -22,6 +22,7 @@
 #include "../../include/cgb200.h"
 #include "cg_kernels.h"
 #include "cg_internal.h"
+#include "spd_gen.cuh"
 
 static __thread char tl_err[512];
 
@@ -660,10 +661,22 @@ static int load_host_symmetric_body(cgb_ctx *c, int64_t n, const double *A_rows,
     return CGB_OK;
 }
 
+/* rows [row0, row0 + m) of the generated matrix in the family the flags name (spd_gen.cuh) */
+static int generate_rows(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed, unsigned flags, cudaStream_t st)
+{
+    if (flags & CGB_GEN_GRAM) return cgk_generate_gram_A(A, n, row0, m, seed, flags, st);
+    if (flags & CGB_GEN_SPECTRUM) {
+        double inv = 0.0, s4 = 0.0;
+        cgb_gen_spectrum_scalars(cgb_gen_key(seed), (uint64_t)n, flags, &inv, &s4);      /* two O(n) sums, host, index order */
+        return cgk_generate_spectrum_A(A, n, row0, m, seed, flags, inv, s4, st);
+    }
+    return cgk_generate_A(A, n, row0, m, seed, flags, st);
+}
 static int generate_body(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags);
 int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
 {
     if (!c) FAIL(CGB_ERR_ARG, "cgb_generate: null context");
+    if ((flags & CGB_GEN_GRAM) && (flags & CGB_GEN_SPECTRUM)) FAIL(CGB_ERR_ARG, "cgb_generate: CGB_GEN_GRAM and CGB_GEN_SPECTRUM are different families, pick one");
     int rc = cgb_ensure_problem(c, n);
     if (rc != CGB_OK) return rc;
     return cgb_ranks_agree(c, generate_body(c, n, seed, flags));
@@ -672,7 +685,7 @@ int cgb_generate(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
 static int generate_body(cgb_ctx *c, int64_t n, uint64_t seed, unsigned flags)
 {
     const int64_t row0 = (int64_t)c->rank * c->m;
-    KL(cgk_generate_A(c->A, n, row0, c->m, seed, flags, c->stream));
+    KL(generate_rows(c->A, n, row0, c->m, seed, flags, c->stream));
     KL(cgk_generate_b(c->b, n, row0, c->m, seed, flags, c->stream));
     CU(cudaMemsetAsync(c->x_full, 0, (size_t)n * sizeof(double), c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -785,12 +798,14 @@ static int prepare_symv(cgb_ctx *c, const cgb_options *o)
         return CGB_ERR_ARG;
     }
     cudaStream_t st = c->stream;
-    if (multi && c->sym_state != 1 && o->symmetric != 2)
-        FAIL(CGB_ERR_ARG, "cgb_options.symmetric = 1 on several ranks: a row block cannot verify a_ij == a_ji by itself; "
-                          "generated systems are symmetric by construction, for loaded ones pass symmetric = 2 to assert it");
+    if (multi && c->sym_state < 0)
+        FAIL(CGB_ERR_ARG, "cgb_options.symmetric: the matrix is not exactly symmetric (a_ij != a_ji somewhere)");
+    /* several ranks, loaded matrix, symmetric = 1: a row block cannot verify a_ij == a_ji by itself -- the
+     * ranks do it together (verify_symmetry_ranks, collective) once cgb_solve has let them agree to go on */
+    c->sym_pending = multi && c->sym_state == 0 && o->symmetric != 2;
     if (multi && o->symmetric == 2 && c->sym_state == 0) c->sym_state = 1;
     if (c->sym_state == 0 && o->symmetric == 2) c->sym_state = 1;
-    if (c->sym_state == 0) {
+    if (c->sym_state == 0 && !multi) {
         int *d_flag = NULL, h_flag = 1;
         CU(cudaMalloc((void **)&d_flag, sizeof(int)));
         int e = cgk_symmetry_check(c->A, c->n, d_flag, st);
@@ -987,6 +1002,41 @@ static int ensure_gemv_events(cgb_ctx *c, int pairs)
     return CGB_OK;
 }
 
+/* cgb_options.symmetric = 1 on a matrix loaded on several ranks: is a_ij == a_ji bit for bit?  Collective.
+ * Each rank compares its diagonal block exactly and fingerprints its G column blocks (cgk_symmetry_hash);
+ * one all-gather of G + 1 words per rank; every rank compares S[g][h] with S[h][g] and reaches the same
+ * verdict.  Sets c->sym_state to 1 or -1. */
+static int verify_symmetry_ranks(cgb_ctx *c)
+{
+    const int G = c->ranks;
+    cudaStream_t st = c->stream;
+    unsigned long long *d = NULL, h[CGK_MAX_RANKS * (CGK_MAX_RANKS + 2)];
+    int *d_flag = NULL, h_flag = 1;
+    if (G > CGK_MAX_RANKS) FAIL(CGB_ERR_ARG, "cgb_options.symmetric = 1 on more ranks than the peer exchange supports");
+    CU(cudaMalloc((void **)&d, (size_t)(G + 1) * (size_t)(G + 2) * sizeof *d));
+    unsigned long long *mine = d + (size_t)G * (size_t)(G + 2);           /* send buffer: G sums, NaN flag, diagonal verdict */
+    d_flag = (int *)(mine + G + 1);
+    int rc = CGB_OK;
+    if (cgk_symmetry_hash(c->A, c->n, (int64_t)c->rank * c->m, c->m, G, mine, st) != 0 ||
+        cudaMemsetAsync(d_flag, 0, sizeof(unsigned long long), st) != cudaSuccess ||
+        cgk_symmetry_check_ld(c->A + (size_t)c->rank * (size_t)c->m, c->m, c->n, d_flag, st) != 0) rc = CGB_ERR_CUDA;
+    if (rc == CGB_OK && ncclAllGather(mine, d, (size_t)(G + 2), ncclUint64, c->comm, st) != ncclSuccess) { rc = CGB_ERR_NCCL; c->broken = 1; }
+    if (rc == CGB_OK && (cudaMemcpyAsync(h, d, (size_t)G * (size_t)(G + 2) * sizeof *h, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                         cudaStreamSynchronize(st) != cudaSuccess)) rc = CGB_ERR_CUDA;
+    cudaFree(d);
+    (void)h_flag;
+    if (rc != CGB_OK) { (void)cudaGetLastError(); FAIL(rc, "the cross-rank symmetry check failed to run"); }
+    int sym = 1;
+    for (int g = 0; g < G; ++g) {
+        const unsigned long long *sg = h + (size_t)g * (size_t)(G + 2);
+        if (sg[G] != 0ull || (sg[G + 1] & 0xffffffffull) != 0ull) sym = 0;            /* a NaN, or its diagonal block differs */
+        for (int q = 0; q < G; ++q)
+            if (sg[q] != h[(size_t)q * (size_t)(G + 2) + (size_t)g]) sym = 0;
+    }
+    c->sym_state = sym ? 1 : -1;
+    return CGB_OK;
+}
+
 /* What cgb_solve settles on this rank alone before the first collective step: options, transport,
  * launch plan, workspaces of the symmetric product, the captured graph.  Anything here may fail on
  * one rank only (device memory), which is why cgb_solve lets the ranks agree on the outcome. */
@@ -1110,6 +1160,13 @@ int cgb_solve(cgb_ctx *c, const cgb_options *opt, cgb_stats *stats)
     memset(&sp, 0, sizeof sp);
     int prc = cgb_ranks_agree(c, solve_prepare(c, opt, &sp));     /* all ranks enter the solve, or none */
     if (prc != CGB_OK) return prc;
+    if (c->sym_pending) {
+        c->sym_pending = 0;
+        int vrc = verify_symmetry_ranks(c);               /* collective; every rank reaches the same verdict */
+        if (vrc != CGB_OK) return vrc;
+        if (c->sym_state < 0)
+            FAIL(CGB_ERR_ARG, "cgb_options.symmetric: the matrix is not exactly symmetric (a_ij != a_ji somewhere)");
+    }
     const cgb_options o = sp.o;
     const int64_t max_iter = sp.max_iter;
     const int multi = c->ranks > 1;
@@ -1451,7 +1508,7 @@ int cgb_op_generate(cgb_ctx *c, int64_t n, int64_t row0, int64_t m, uint64_t see
     if (A_rows) {
         if ((rc = dev_dup(c, &dA, NULL, m * n, st))) goto out;
         rc = CGB_ERR_CUDA;
-        if (cgk_generate_A(dA, n, row0, m, seed, flags, st) != 0) goto out;
+        if (generate_rows(dA, n, row0, m, seed, flags, st) != 0) goto out;
         if (cudaMemcpyAsync(A_rows, dA, (size_t)m * (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) goto out;
     }
     if (b_rows) {

@@ -148,7 +148,7 @@ cgb_halfmat_finish_kernel(const double *__restrict__ rowpart, const double *__re
  * row-wise (256-byte segments) and compared through a shared-memory transpose.  Any a_ij that
  * is not bit-identical to a_ji (NaNs included) raises *flag. */
 __global__ void __launch_bounds__(256)
-cgb_symmetry_check_kernel(const double *__restrict__ A, long long n, long long nb, int *flag)
+cgb_symmetry_check_kernel(const double *__restrict__ A, long long n, long long ld, long long nb, int *flag)
 {
     /* blockIdx.x enumerates (bi, bj), bi <= bj, row-major over the upper block triangle */
     long long t = blockIdx.x, bi = 0, rowlen = nb;
@@ -158,14 +158,14 @@ cgb_symmetry_check_kernel(const double *__restrict__ A, long long n, long long n
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;            /* 32 x 8 */
     for (int r = ty; r < 32; r += 8) {
         const long long i = bi * 32 + r, j = bj * 32 + tx;
-        s_a[r][tx] = (i < n && j < n) ? A[i * n + j] : 0.0;
+        s_a[r][tx] = (i < n && j < n) ? A[i * ld + j] : 0.0;
     }
     __syncthreads();
     int bad = 0;
     for (int r = ty; r < 32; r += 8) {
         const long long i = bj * 32 + r, j = bi * 32 + tx;             /* element (i, j) of the mirror block */
         if (i < n && j < n) {
-            const unsigned long long a = (unsigned long long)__double_as_longlong(A[i * n + j]);
+            const unsigned long long a = (unsigned long long)__double_as_longlong(A[i * ld + j]);
             const unsigned long long b = (unsigned long long)__double_as_longlong(s_a[tx][r]);
             const double av = __longlong_as_double((long long)a);
             if (a != b || av != av) bad = 1;
@@ -220,13 +220,69 @@ extern "C" int cgk_symv(const double *A, const double *v, const double *w, doubl
 
 extern "C" int cgk_symv_finish_grid(int64_t n) { return (int)(n / SY_FR); }
 
-extern "C" int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void *stream)
+extern "C" int cgk_symmetry_check_ld(const double *A, int64_t n, int64_t ld, int *d_flag, void *stream)
 {
     const long long nb = (n + 31) / 32;
     const long long blocks = nb * (nb + 1) / 2;
     if (blocks > 2147483647LL) return (int)cudaErrorInvalidValue;
     cudaMemsetAsync(d_flag, 0, sizeof(int), (cudaStream_t)stream);
-    cgb_symmetry_check_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, nb, d_flag);
+    cgb_symmetry_check_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)ld, nb, d_flag);
+    return (int)cudaGetLastError();
+}
+extern "C" int cgk_symmetry_check(const double *A, int64_t n, int *d_flag, void *stream)
+{
+    return cgk_symmetry_check_ld(A, n, n, d_flag, stream);
+}
+
+/* Symmetry ACROSS row blocks (ranks > 1): rank g cannot see a_ji for j in another rank's rows, but it can
+ * fingerprint its part of every block pair.  For the m x m block (g, h) of its rows the rank adds up, modulo
+ * 2^64, f(min(i,j), max(i,j), bits(a_ij)) over the block's elements, f a 64-bit mixing function: block
+ * (h, g) on rank h gives the same sum when a_ij == a_ji bit for bit throughout, and a different one
+ * otherwise except with probability ~2^-64.  The ranks exchange their G sums (one small all-gather) and every
+ * rank compares S[g][h] with S[h][g]; the diagonal block (g, g) is compared exactly by the kernel above.
+ * A NaN anywhere raises sums[ranks] (no a_ij == a_ji holds for NaNs).  One pass over the block at HBM rate. */
+__device__ __forceinline__ unsigned long long sym_mix(unsigned long long z)
+{
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+__global__ void __launch_bounds__(256)
+cgb_symmetry_hash_kernel(const double *__restrict__ A, long long n, long long row0, long long m, int ranks,
+                         unsigned long long *__restrict__ sums)
+{
+    __shared__ unsigned long long s_sum[CGK_MAX_RANKS + 1];
+    if (threadIdx.x <= CGK_MAX_RANKS) s_sum[threadIdx.x] = 0ull;
+    __syncthreads();
+    unsigned long long nan = 0ull;
+    for (long long r = blockIdx.x; r < m; r += gridDim.x) {
+        const unsigned long long i = (unsigned long long)(row0 + r);
+        const double *row = A + r * n;
+        for (int h = 0; h < ranks; ++h) {
+            unsigned long long acc = 0ull;
+            for (long long j = (long long)h * m + threadIdx.x; j < (long long)(h + 1) * m; j += 256) {
+                const double v = row[j];
+                const unsigned long long uj = (unsigned long long)j, lo = i < uj ? i : uj, hi = i < uj ? uj : i;
+                acc += sym_mix(sym_mix(lo * (unsigned long long)n + hi) ^ (unsigned long long)__double_as_longlong(v));
+                if (v != v) nan = 1ull;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&s_sum[h], acc);
+        }
+    }
+    if (nan) atomicOr(&s_sum[CGK_MAX_RANKS], 1ull);
+    __syncthreads();
+    if (threadIdx.x < ranks) atomicAdd(&sums[threadIdx.x], s_sum[threadIdx.x]);
+    if (threadIdx.x == 0 && s_sum[CGK_MAX_RANKS]) atomicOr(&sums[ranks], 1ull);
+}
+/* sums: ranks + 1 words of device memory (zeroed here): the fingerprints of the rank's G blocks, then the NaN flag */
+extern "C" int cgk_symmetry_hash(const double *A, int64_t n, int64_t row0, int64_t m, int ranks, unsigned long long *sums, void *stream)
+{
+    if (ranks < 1 || ranks > CGK_MAX_RANKS) return (int)cudaErrorInvalidValue;
+    cudaMemsetAsync(sums, 0, (size_t)(ranks + 1) * sizeof(unsigned long long), (cudaStream_t)stream);
+    long long g = m < 148 * 8 ? m : 148 * 8;
+    cgb_symmetry_hash_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(A, (long long)n, (long long)row0, (long long)m, ranks, sums);
     return (int)cudaGetLastError();
 }
 

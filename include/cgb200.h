@@ -45,6 +45,17 @@ extern "C" {
  * becomes n*diag(1 + (2^k - 1) t_i^2), t_i = i/(n-1), k in 1..63 (condition number ~2^k:
  * k = 4 -> ~35 CG iterations, 7 -> ~100, 10 -> ~270 at eps = 1e-6).  k = 0: the reference's. */
 #define CGB_GEN_KAPPA_LOG2(k) (((unsigned)(k) & 0x3fu) << 8)
+/* A dense matrix with a PRESCRIBED spectrum: A = H diag(lambda) H, H = I - 2 v v' a Householder
+ * reflector from the seeded stream, lambda_i = n (1 + (2^k - 1) t_i^2) with k from
+ * CGB_GEN_KAPPA_LOG2 -- the eigenvalues are exactly the lambda_i, so the iteration count of CG is a
+ * property of k alone (k = 10: ~230 iterations).  Exactly symmetric, bit-identical to the CPU twin. */
+#define CGB_GEN_SPECTRUM 2u
+/* The reference's commented alternative `A = A*A'` (generateSPDmatrix.m:12) followed by its
+ * `A = A + n*eye(n)` (:17): A = R R' + n diag(d), R = rand(n, n) from the seeded stream, d the
+ * spread of CGB_GEN_KAPPA_LOG2 (1 for k = 0).  An FP64 contraction of 2 n^3 flops, done on the
+ * FP64 tensor pipe; exactly symmetric; equal to the CPU twin to ~1e-15 relative per entry (the
+ * summation order of the tensor instruction is the hardware's). */
+#define CGB_GEN_GRAM 4u
 
 /* GEMV kernel selection (0 = library default) */
 #define CGB_GEMV_AUTO 0

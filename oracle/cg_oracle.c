@@ -78,6 +78,33 @@ void orc_gen_fill_A(double *A, int64_t n, int64_t row0, int64_t m, uint64_t seed
                     unsigned flags)
 {
     const uint64_t key = orc_gen_key(seed);
+    if (flags & ORC_GEN_SPECTRUM) {
+        const orc_spectrum sp = orc_gen_spectrum_setup(key, (uint64_t)n, flags);
+        for (int64_t i = 0; i < m; ++i)
+            for (int64_t j = 0; j < n; ++j)
+                A[i * n + j] = orc_gen_spectrum_a(key, (uint64_t)n, (uint64_t)(row0 + i), (uint64_t)j, flags, &sp);
+        return;
+    }
+    if (flags & ORC_GEN_GRAM) {
+        /* R in full (n x n), then the m x n block of R R' by rows: plain loops, k ascending */
+        double *R = malloc((size_t)n * (size_t)n * sizeof(double));
+        if (!R) { for (int64_t e = 0; e < m * n; ++e) A[e] = NAN; return; }
+        for (int64_t i = 0; i < n; ++i)
+            for (int64_t k = 0; k < n; ++k) R[i * n + k] = orc_gen_u(key, (uint64_t)(i * n + k));
+        for (int64_t i = 0; i < m; ++i) {
+            const double *ri = R + (row0 + i) * n;
+            for (int64_t j = 0; j < n; ++j) {
+                const double *rj = R + j * n;
+                double acc = 0.0;
+                for (int64_t k = 0; k < n; ++k) acc += ri[k] * rj[k];
+                if (row0 + i == j) acc = acc + (double)n * orc_gen_d((uint64_t)n, (uint64_t)j, flags);
+                if (flags & ORC_GEN_ROUND4) acc = orc_gen_round4(acc);
+                A[i * n + j] = acc;
+            }
+        }
+        free(R);
+        return;
+    }
     for (int64_t i = 0; i < m; ++i)
         for (int64_t j = 0; j < n; ++j)
             A[i * n + j] = orc_gen_a(key, (uint64_t)n, (uint64_t)(row0 + i), (uint64_t)j, flags);

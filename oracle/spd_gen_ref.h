@@ -75,6 +75,68 @@ static inline double orc_gen_a(uint64_t key, uint64_t n, uint64_t i, uint64_t j,
     return v;
 }
 
+/* ---- the two further families (product side: spd_gen.cuh, cg_gram.cu) -- written from their
+ * definitions, not from the product's code.
+ * ORC_GEN_SPECTRUM: A = H L H with H = I - 2 v v', L = diag(lambda), lambda_i = n d_i,
+ *   d_i = 1 + (2^k - 1) (i/(n-1))^2, v = w/|w|, w_i = u(n^2 + n + i) - 1/2:
+ *   (H L H)_ij = lambda_i [i==j] - 2 v_i v_j lambda_j - 2 lambda_i v_i v_j + 4 v_i v_j (v' L v)
+ *              = v_i v_j (4 s - 2 (lambda_i + lambda_j)) + lambda_i [i==j],   s = sum_k lambda_k v_k^2.
+ * ORC_GEN_GRAM: A = R R' + n diag(d), R_ik = u(i n + k)  (generateSPDmatrix.m:12 then :17). */
+#define ORC_GEN_SPECTRUM 2u
+#define ORC_GEN_GRAM 4u
+
+static inline double orc_gen_d(uint64_t n, uint64_t i, unsigned flags)
+{
+    unsigned k = (flags >> 8) & 0x3fu;
+    if (!k || n < 2) return 1.0;
+    double t = (double)i / (double)(n - 1);
+    double tt = t * t;
+    double span = (double)(1ULL << k) - 1.0;
+    double st = span * tt;
+    return 1.0 + st;
+}
+
+typedef struct { double inv_norm, four_s; } orc_spectrum;
+
+static inline orc_spectrum orc_gen_spectrum_setup(uint64_t key, uint64_t n, unsigned flags)
+{
+    orc_spectrum sp;
+    double norm2 = 0.0;
+    for (uint64_t i = 0; i < n; ++i) {
+        double w = orc_gen_u(key, n * n + n + i) - 0.5;
+        double ww = w * w;
+        norm2 = norm2 + ww;
+    }
+    sp.inv_norm = 1.0 / sqrt(norm2);
+    double s = 0.0;
+    for (uint64_t i = 0; i < n; ++i) {
+        double v = (orc_gen_u(key, n * n + n + i) - 0.5) * sp.inv_norm;
+        double vv = v * v;
+        double lam = (double)n * orc_gen_d(n, i, flags);
+        double term = lam * vv;
+        s = s + term;
+    }
+    sp.four_s = 4.0 * s;
+    return sp;
+}
+
+static inline double orc_gen_spectrum_a(uint64_t key, uint64_t n, uint64_t i, uint64_t j, unsigned flags,
+                                        const orc_spectrum *sp)
+{
+    double lam_i = (double)n * orc_gen_d(n, i, flags);
+    double lam_j = (double)n * orc_gen_d(n, j, flags);
+    double v_i = (orc_gen_u(key, n * n + n + i) - 0.5) * sp->inv_norm;
+    double v_j = (orc_gen_u(key, n * n + n + j) - 0.5) * sp->inv_norm;
+    double lsum = lam_i + lam_j;
+    double twice = 2.0 * lsum;
+    double coef = sp->four_s - twice;
+    double vv = v_i * v_j;
+    double a = vv * coef;
+    if (i == j) a = a + lam_i;
+    if (flags & ORC_GEN_ROUND4) a = orc_gen_round4(a);
+    return a;
+}
+
 static inline double orc_gen_b(uint64_t key, uint64_t n, uint64_t i, unsigned flags)
 {
     double v = orc_gen_u(key, n * n + i);

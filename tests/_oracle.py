@@ -10,7 +10,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 REF_DIR = os.path.join(ORACLE_DIR, "_ref")
-GEN_ROUND4 = 1
+GEN_ROUND4, GEN_SPECTRUM, GEN_GRAM = 1, 2, 4
 
 
 class OrcStats(C.Structure):

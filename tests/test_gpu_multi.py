@@ -162,18 +162,33 @@ def test_symmetric_product_row_sharded(cg, gpus, n, k):
     np.testing.assert_array_equal(x, x2)                       # fixed-order sums on every rank
 
 
-def test_symmetric_option_on_ranks_needs_assertion_for_loaded_matrices(cg):
-    need(cg, 2)
-    n = 1024
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_symmetric_option_on_ranks_verifies_loaded_matrices_across_the_ranks(cg, gpus):
+    """symmetric = 1 on a matrix LOADED on several ranks: no rank holds both a_ij and a_ji of an off-diagonal block,
+    so the ranks compare 64-bit fingerprints of their blocks (cg_symv.cu: cgk_symmetry_hash) and their diagonal blocks
+    exactly.  A symmetric matrix is accepted and solved with the half-bytes product; one flipped bit anywhere -- inside
+    a diagonal block, or in a block only another rank can mirror -- is refused on every rank, as is a NaN."""
+    need(cg, gpus)
+    n = 512 * gpus
     A, b = O.spd_with_condition(n, 30.0, seed=8)
-    with pytest.raises(cg.CgbError) as e:
-        cg.conjugrad_host(A, b, np.zeros(n), gpus=2, symmetric=1)
-    assert "symmetric = 2" in str(e.value)
-    x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=2, symmetric=2)
-    xo, so = O.conjugrad(A, b, np.zeros(n), ranks=2)
+    x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus, symmetric=1)
+    xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
     assert st["gemv_variant"] == 3 and relerr(x, xo) <= RTOL_X and abs(st["iterations"] - so["iterations"]) <= 1
+    m = n // gpus
+    for (i, j) in ((3, 40), (5, m + 7), (n - 1, 0)):            # own diagonal block; a block pair of two ranks; the far corner
+        B = A.copy()
+        B[i, j] = np.nextafter(B[i, j], np.inf)
+        with pytest.raises(cg.CgbError) as e:
+            cg.conjugrad_host(B, b, np.zeros(n), gpus=gpus, symmetric=1)
+        assert "not exactly symmetric" in str(e.value), str(e.value)
+    B = A.copy()
+    B[7, m + 1] = B[m + 1, 7] = np.nan
+    with pytest.raises(cg.CgbError):
+        cg.conjugrad_host(B, b, np.zeros(n), gpus=gpus, symmetric=1)
+    x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus, symmetric=2)     # the caller's assertion still skips the check
+    assert st["gemv_variant"] == 3 and relerr(x, xo) <= RTOL_X
     with pytest.raises(cg.CgbError):                            # NCCL transport: not available for this product
-        cg.solve_generated(n, 1, gpus=2, symmetric=1, comm=1)
+        cg.solve_generated(n, 1, gpus=gpus, symmetric=1, comm=1)
 
 
 @pytest.mark.parametrize("gpus", [2, 4, 8])
@@ -281,3 +296,27 @@ def test_a_rank_failing_alone_takes_the_team_with_it_instead_of_hanging(cg, gpus
     x, st = cg.conjugrad_host(A, b, np.zeros(n), gpus=gpus)
     xo, so = O.conjugrad(A, b, np.zeros(n), ranks=gpus)
     assert relerr(x, xo) <= RTOL_X and st["ranks"] == gpus
+
+
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+@pytest.mark.parametrize("family", ["spectrum", "gram"])
+def test_further_generator_families_row_sharded(cg, gpus, family):
+    """Every GPU generates its own rows of the prescribed-spectrum / R R' matrix; the sharded solve (full and
+    symmetric product: the blocks of different GPUs must agree bit for bit across the diagonal) against the oracle."""
+    need(cg, gpus)
+    n, seed = 4096, 13
+    flags = (cg.GEN_SPECTRUM | cg.GEN_KAPPA_LOG2(8)) if family == "spectrum" else (cg.GEN_GRAM | cg.GEN_KAPPA_LOG2(5))
+    x1, st1 = cg.solve_generated(n, seed, gpus=1, flags=flags)
+    x, st = cg.solve_generated(n, seed, gpus=gpus, flags=flags)
+    assert abs(st["iterations"] - st1["iterations"]) <= 1 and st["final_residual"] < EPS and st["iterations"] > 15
+    if st["iterations"] == st1["iterations"]:
+        assert relerr(x, x1) <= RTOL_X
+    xs, sts = cg.solve_generated(n, seed, gpus=gpus, flags=flags, symmetric=1)
+    assert sts["gemv_variant"] == 3 and abs(sts["iterations"] - st1["iterations"]) <= 1
+    if sts["iterations"] == st1["iterations"]:
+        assert relerr(xs, x1) <= RTOL_X
+    if family == "spectrum":
+        xo, so = O.conjugrad(O.gen_A(n, seed, flags), O.gen_b(n, seed, flags), np.zeros(n), ranks=gpus)
+        assert abs(st["iterations"] - so["iterations"]) <= 1
+        if st["iterations"] == so["iterations"]:
+            assert relerr(x, xo) <= RTOL_X

@@ -543,3 +543,47 @@ def test_cli_emitted_files_run_record_and_restart(cg, tmp_path):
     r = subprocess.run([B.CLI_PATH, files[0], files[1], xf, "--dims", files[4], "--run-record", rec],
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and json.load(open(rec))["iterations"] <= 2
+
+
+# ----------------------------------------------------------------- further generator families
+@pytest.mark.parametrize("n,row0,m,k,r4", [(64, 0, 64, 4, 0), (300, 0, 300, 10, 0), (1024, 512, 256, 7, 0), (513, 7, 100, 3, 1), (2, 0, 2, 1, 0)])
+def test_prescribed_spectrum_generator_bit_identical_to_cpu_twin(cg, ctx, n, row0, m, k, r4):
+    flags = cg.GEN_SPECTRUM | cg.GEN_KAPPA_LOG2(k) | r4
+    A, b = ctx.op_generate(n, 77, flags, row0, m)
+    assert A.tobytes() == O.gen_A(n, 77, flags, row0, m).tobytes()
+    assert b.tobytes() == O.gen_b(n, 77, flags, row0, m).tobytes()
+
+
+@pytest.mark.parametrize("n,row0,m,k", [(64, 0, 64, 0), (200, 0, 200, 5), (1000, 0, 1000, 0), (1024, 256, 300, 3), (77, 10, 50, 0)])
+def test_gram_generator_matches_cpu_twin_and_is_exactly_symmetric(cg, ctx, n, row0, m, k):
+    """A = R R' + n diag(d) from the FP64 tensor pipe (cg_gram.cu) against the CPU twin's plain loops: <= 1e-13
+    relative per entry (the instruction's internal summation order is the hardware's); bitwise symmetric."""
+    flags = cg.GEN_GRAM | cg.GEN_KAPPA_LOG2(k)
+    A, b = ctx.op_generate(n, 5, flags, row0, m)
+    want = O.gen_A(n, 5, flags, row0, m)
+    assert np.max(np.abs(A - want) / np.abs(want)) <= 1e-13
+    assert b.tobytes() == O.gen_b(n, 5, flags, row0, m).tobytes()
+    if m == n:
+        assert np.array_equal(A, A.T)
+    else:                                          # a row block: its square part against the transposed block of the other rows
+        full, _ = ctx.op_generate(n, 5, flags, 0, n)
+        assert np.array_equal(full, full.T) and full[row0:row0 + m].tobytes() == A.tobytes()
+
+
+@pytest.mark.parametrize("family,k,lo", [("spectrum", 7, 60), ("spectrum", 10, 150), ("gram", 0, 4), ("gram", 3, 10)])
+def test_solves_on_the_further_families_match_the_oracle(cg, ctx, family, k, lo):
+    """Iteration-bound parity runs: the matrix the GPU generated (read back, so both sides see the same bits even for
+    the gram family) through the oracle's serial CG against the resident solve; full and symmetric products."""
+    n, seed = 1024, 9
+    flags = (cg.GEN_SPECTRUM if family == "spectrum" else cg.GEN_GRAM) | cg.GEN_KAPPA_LOG2(k)
+    ctx.generate(n, seed, flags)
+    A = ctx.debug_read(0, 0, n * n).reshape(n, n)
+    b = ctx.debug_read(1, 0, n)
+    xo, so = O.conjugrad(A, b, np.zeros(n))
+    assert so["iterations"] >= lo, so["iterations"]
+    for sym in (0, 1):
+        ctx.set_x0(np.zeros(n))
+        st = ctx.solve(symmetric=sym)              # symmetric=1 verifies a_ij == a_ji on the device first
+        assert abs(st["iterations"] - so["iterations"]) <= 1 and st["final_residual"] < EPS
+        if st["iterations"] == so["iterations"]:
+            assert relerr(ctx.read_x(), xo) <= RTOL_X

@@ -249,3 +249,44 @@ def test_building_blocks_against_the_real_functions(n, prec):
     # ... and these bits are NOT what a fused or pairwise evaluation gives (the test has teeth)
     if n >= 512:
         assert y.tobytes() != (A @ v).astype(dt).tobytes()
+
+
+# ----------------------------------------------------------------- the two further generator families
+@pytest.mark.parametrize("n,k", [(64, 4), (256, 7), (301, 10)])
+def test_prescribed_spectrum_family_has_exactly_the_stated_eigenvalues(n, k):
+    """ORC_GEN_SPECTRUM: A = H diag(lambda) H with lambda_i = n (1 + (2^k - 1) t_i^2): symmetric bit for bit, and its
+    eigenvalues (LAPACK) are the stated ones."""
+    A = O.gen_A(n, 11, O.GEN_SPECTRUM | O.GEN_KAPPA_LOG2(k))
+    assert np.array_equal(A, A.T)
+    t = np.arange(n) / (n - 1)
+    want = np.sort(n * (1.0 + (2.0 ** k - 1.0) * t * t))
+    got = np.sort(np.linalg.eigvalsh(A))
+    assert np.max(np.abs(got - want) / want) < 1e-11
+    # rows generated on their own equal the rows of the whole matrix (what a rank of a row-sharded run generates)
+    assert O.gen_A(n, 11, O.GEN_SPECTRUM | O.GEN_KAPPA_LOG2(k), 5, 7).tobytes() == A[5:12].tobytes()
+
+
+def test_prescribed_spectrum_family_is_iteration_bound():
+    n = 512
+    counts = []
+    for k in (4, 7, 10):
+        A = O.gen_A(n, 3, O.GEN_SPECTRUM | O.GEN_KAPPA_LOG2(k))
+        x, st = O.conjugrad(A, O.gen_b(n, 3), np.zeros(n))
+        assert np.linalg.norm(A @ x - O.gen_b(n, 3)) < 1e-5
+        counts.append(st["iterations"])
+    assert counts[0] > 20 and counts[1] > 2 * counts[0] and counts[2] > 2 * counts[1], counts
+
+
+@pytest.mark.parametrize("n,k", [(96, 0), (200, 5)])
+def test_gram_family_is_R_Rt_plus_shift(n, k):
+    """ORC_GEN_GRAM: generateSPDmatrix.m:12's `A = A*A'` followed by :17's `+ n*eye(n)` (with the spread diagonal)."""
+    flags = O.GEN_GRAM | O.GEN_KAPPA_LOG2(k)
+    A = O.gen_A(n, 21, flags)
+    R = np.array([[O.lib().orc_gen_sample_u(21, i * n + j) for j in range(n)] for i in range(n)])
+    t = np.arange(n) / (n - 1)
+    d = 1.0 + (2.0 ** k - 1.0) * t * t if k else np.ones(n)
+    want = R @ R.T + np.diag(n * d)
+    assert np.array_equal(A, A.T)
+    assert np.max(np.abs(A - want) / np.abs(want)) < 1e-13
+    assert np.all(np.linalg.eigvalsh(A) > 0)
+    assert O.gen_A(n, 21, flags, 10, 3).tobytes() == A[10:13].tobytes()

@@ -116,11 +116,16 @@ def test_iteration_kernels_carry_programmatic_dependent_launch(sass):
     assert "ACQBULK" not in o and "PREEXIT" not in o
 
 
-def test_no_fp64_atomics_and_no_tensor_cores(sass):
+def test_no_fp64_atomics_and_tensor_cores_only_where_there_is_a_contraction(sass):
+    """The CG iteration is HBM-bound vector work: no tensor instruction anywhere on it.  The one dense contraction of
+    the package -- the R R' generator family (generateSPDmatrix.m:12), an FP64 SYRK -- runs on the FP64 tensor pipe."""
     for name, body in sass.items():
         for x in ops(body):
             assert not re.match(r"(ATOM|ATOMG|ATOMS|RED)\..*F64", x), (name, x)
-            assert not re.match(r"(HMMA|DMMA|IMMA|QMMA|UTCHMMA|UTCQMMA|UTCIMMA|HGMMA)", x), (name, x)
+            if not name.startswith("cgb_gram_rows_kernel"):
+                assert not re.match(r"(HMMA|DMMA|IMMA|QMMA|UTCHMMA|UTCQMMA|UTCIMMA|HGMMA)", x), (name, x)
+    gram = ops(sass["cgb_gram_rows_kernel"])
+    assert sum(x.startswith("DMMA") for x in gram) >= 32 and not any(x.startswith(("LDL", "STL")) for x in gram)
 
 
 def test_peer_exchange_uses_system_scope_accesses(sass):
