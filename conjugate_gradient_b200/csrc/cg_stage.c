@@ -20,7 +20,7 @@
  *   CGB_STAGE=register     pin the caller's pages in place, piece by piece, ahead of the DMA
  *                          (unset / auto: the ring)
  *   CGB_STAGE_THREADS=T    copy threads (default: min(8, online CPUs / ranks), at least 2)
- *   CGB_STAGE_CHUNK_MB=C   bytes per piece (default for the ring 8 MiB on one rank, 2 MiB on several; 32 MiB for in-place pinning);
+ *   CGB_STAGE_CHUNK_MB=C   bytes per piece (default for the ring 8 MiB on one rank, 1 MiB on several; 32 MiB for in-place pinning);
  *   CGB_STAGE_CHUNK_KB=K   the same in KiB (>= 64)
  */
 #define _GNU_SOURCE
@@ -247,10 +247,11 @@ int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int p
     for (int64_t i = 0; i < nruns; ++i) total += runs[i].width * runs[i].rows;
     int mode = pageable ? cgb_stage_mode_for(c->ranks) : CGB_H2D_DIRECT;
     /* piece size of the ring: alone on the host 8 MiB pieces measured best (52.3 GB/s of 55.5 pinned; 2 MiB: 43-47);
-     * with a second rank uploading at the same time the host's memory bandwidth is shared and 2 MiB pieces --
-     * rings small enough to be read back by the DMA engine out of the last-level cache -- gave 35-38 GB/s per
-     * GPU against 28 with 8 MiB (profiles/r02_h2d_2gpu_modes.json) */
-    size_t chunk = (size_t)env_int("CGB_STAGE_CHUNK_MB", mode == CGB_H2D_REGISTERED ? 32 : (c->ranks > 1 ? 2 : 8), 1, 256) << 20;
+     * with other ranks uploading at the same time the host's memory bandwidth is shared and small pieces -- rings
+     * small enough to be read back by the DMA engine out of the last-level cache -- do better: two ranks 37 GB/s
+     * per GPU with 1-2 MiB against 28 with 8 MiB; eight ranks (4 threads each) 13.6-14.4 with 1 MiB against 10.4-11
+     * with 2 MiB and 8.8 with 8 MiB (profiles/r02_h2d_2gpu_modes.json, r02_h2d_g8.json) */
+    size_t chunk = (size_t)env_int("CGB_STAGE_CHUNK_MB", mode == CGB_H2D_REGISTERED ? 32 : (c->ranks > 1 ? 1 : 8), 1, 256) << 20;
     {
         const int kb = env_int("CGB_STAGE_CHUNK_KB", 0, 64, 256 << 10);       /* finer than a MiB, for the sweep */
         if (kb > 0) chunk = (size_t)kb << 10;
