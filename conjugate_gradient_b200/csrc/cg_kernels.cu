@@ -1227,6 +1227,12 @@ typedef void (*gemv_keep_fn)(const double *, const double *, const double *, dou
 struct keep_cfg { int r, u, nt, vec; gemv_keep_fn fn; };
 static const keep_cfg k_keep[] = {
     {4, 1, 128, 4, cgb_rowblock_matvec_keep<4, 1, 128, 4>},
+    /* the same 16 doubles in flight per thread at a finer row granularity (2x / 4x the CTAs): selectable, never the
+     * default -- measured on one B200 for n = 1024 .. 7680 (profiles/r02_rows_per_cta_sweep.txt) (2,2) is within
+     * +-3 % of (4,1) except at n = 4096 (-16 %: two waves instead of one) and (1,4) is 10-30 % slower everywhere,
+     * i.e. the sizes between one and two waves of (4,1) CTAs are NOT limited by wave quantisation */
+    {2, 2, 128, 4, cgb_rowblock_matvec_keep<2, 2, 128, 4>},
+    {1, 4, 128, 4, cgb_rowblock_matvec_keep<1, 4, 128, 4>},
     {4, 2, 128, 4, cgb_rowblock_matvec_keep<4, 2, 128, 4>},
     {8, 1, 128, 4, cgb_rowblock_matvec_keep<8, 1, 128, 4>},
     {2, 1, 256, 4, cgb_rowblock_matvec_keep<2, 1, 256, 4>},
