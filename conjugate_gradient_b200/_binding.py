@@ -130,6 +130,7 @@ def lib():
         "cgb_debug_check_guards": ([vp], C.c_int),
         "cgb_debug_poke": ([vp, C.c_int, i64, C.c_double], C.c_int),
         "cgb_debug_probe_read": ([vp, vp, i64], i64),
+        "cgb_matvec_noalloc": ([vp, vp, vp, vp, vp, i64, i64, vp], C.c_int),
         "cgb_debug_rendezvous_id": ([C.c_int, C.c_int, vp], C.c_int),
         "cgb_load_text": ([vp, i64, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
         "cgb_conjugrad_files": ([C.c_char_p, C.c_char_p, C.c_char_p, i64, C.c_int, op, vp, sp], C.c_int),

@@ -328,6 +328,23 @@ int cgb_op_p_update(cgb_ctx *ctx, double rho, double beta, double eps, double *p
 int cgb_op_generate(cgb_ctx *ctx, int64_t n, int64_t row0, int64_t m, uint64_t seed,
                     unsigned flags, double *A_rows, double *b_rows);
 
+/* ---- no-allocation entry point ---------------------------------------------- */
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The matVec with the fused dot of cgb_op_matvec -- y = A v for an m x n row-major block, and
+ * *d_dot = sum_i w[i] y[i] when d_w / d_dot are given (both, or neither) -- on DEVICE pointers of
+ * the current device, enqueued on `stream` (asynchronous: results are ready when the stream is).
+ * It calls no cudaMalloc / cudaFree / allocating library routine and copies nothing: the kernel's
+ * scratch (one dot partial per CTA, ticket, flags) is a static device array of
+ * 512 + 8 * CGB_NOALLOC_MAX_CTAS bytes (1 MiB) that every GPU loading the library holds until
+ * exit.  Limit: m <= CGB_NOALLOC_MAX_ROWS, else CGB_ERR_ARG with a message.  All calls share the
+ * array: the part that must start at zero is cleared on `stream` before each launch, and two calls
+ * that overlap on one GPU (different streams or threads) race -- serialise them. */
+#define CGB_NOALLOC_MAX_CTAS 131072
+#define CGB_NOALLOC_MAX_ROWS ((int64_t)262144)      /* at least 2 rows per CTA for every shape the plan picks */
+int cgb_matvec_noalloc(const double *d_A, const double *d_v, const double *d_w, double *d_y,
+                       double *d_dot, int64_t m, int64_t n, void *stream);
+
 /* ---- measurement helpers --------------------------------------------------- */
 /* Times `reps` back-to-back launches of the GEMV on the resident problem
  * (v = current direction vector) with CUDA events on the solver stream, after
