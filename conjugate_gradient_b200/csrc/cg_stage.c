@@ -251,10 +251,36 @@ int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int p
      * small enough to be read back by the DMA engine out of the last-level cache -- do better: two ranks 37 GB/s
      * per GPU with 1-2 MiB against 28 with 8 MiB; eight ranks (4 threads each) 13.6-14.4 with 1 MiB against 10.4-11
      * with 2 MiB and 8.8 with 8 MiB (profiles/r02_h2d_2gpu_modes.json, r02_h2d_g8.json) */
-    size_t chunk = (size_t)env_int("CGB_STAGE_CHUNK_MB", mode == CGB_H2D_REGISTERED ? 32 : (c->ranks > 1 ? 1 : 8), 1, 256) << 20;
+    const size_t max_chunk = (size_t)(mode == CGB_H2D_REGISTERED ? 32 : (c->ranks > 1 ? 1 : 8)) << 20;
+    size_t chunk = (size_t)env_int("CGB_STAGE_CHUNK_MB", (int)(max_chunk >> 20), 1, 256) << 20;
+    int chunk_given = getenv("CGB_STAGE_CHUNK_MB") != NULL;
     {
         const int kb = env_int("CGB_STAGE_CHUNK_KB", 0, 64, 256 << 10);       /* finer than a MiB, for the sweep */
-        if (kb > 0) chunk = (size_t)kb << 10;
+        if (kb > 0) { chunk = (size_t)kb << 10; chunk_given = 1; }
+    }
+    int T = stage_threads(c);
+    if (mode == CGB_H2D_STAGED && !chunk_given) {
+        /* The ring is pinned memory, and pinning is not free: cudaHostAlloc measured 0.42 ms per MiB (2.4 GB/s) on
+         * the bench box, so the full 8 x 2 x 8 MiB ring costs 58 ms -- more than the whole upload of an n = 8192 system
+         * (537 MB: 10 ms at the pinned rate, 50 ms through the driver).  A caller shaped like the reference's main()
+         * calls conjugrad() ONCE, so the first call is the one that counts: the ring is sized from the bytes to move,
+         * total / 40 (pinning then costs about half of what the copy takes), between 2 MiB and threads x 2 x the
+         * piece size that is best once the ring exists; it only ever grows, and a later call uses what is there.
+         * Below 64 MiB the driver's own path (11 GB/s, no set-up) wins.  profiles/r02_first_call.txt */
+        if (total < ((size_t)64 << 20)) mode = CGB_H2D_DRIVER;
+        else {
+            const size_t ring_max = (size_t)T * STAGE_SLOTS * max_chunk;
+            size_t ring = total / 40;
+            if (ring < ((size_t)2 << 20)) ring = (size_t)2 << 20;
+            if (ring > ring_max) ring = ring_max;
+            if (c->stage_pin_bytes > ring) ring = c->stage_pin_bytes < ring_max ? c->stage_pin_bytes : ring_max;
+            chunk = ring / ((size_t)T * STAGE_SLOTS) & ~(size_t)0xffff;          /* multiple of 64 KiB */
+            if (chunk < ((size_t)256 << 10)) {                                   /* few bytes: fewer threads, not smaller pieces */
+                chunk = (size_t)256 << 10;
+                T = (int)(ring / (STAGE_SLOTS * chunk));
+                if (T < 1) T = 1;
+            }
+        }
     }
     if (mode != CGB_H2D_DIRECT && mode != CGB_H2D_DRIVER && total < 2 * chunk) mode = CGB_H2D_DRIVER;   /* small: not worth a thread team */
     if (path_out) *path_out = mode;
@@ -287,7 +313,6 @@ int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int p
         return CGB_OK;
     }
 
-    int T = stage_threads(c);
     {
         size_t pieces = (total + chunk - 1) / chunk;
         if ((size_t)T > pieces) T = (int)pieces;
