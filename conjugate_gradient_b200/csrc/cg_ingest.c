@@ -11,6 +11,7 @@
  */
 #define _GNU_SOURCE
 #include <cuda_runtime_api.h>
+#include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -21,7 +22,11 @@
 #include "cg_internal.h"
 #include "cg_io.h"
 
-#define CHUNK_BYTES ((size_t)32 << 20)
+/* Two pinned buffers of one chunk each.  Pinning costs ~0.42 ms per MiB and a
+ * one-shot caller -- the CLI -- pays it on every run: 2 x 32 MiB were 27 ms of a 0.19 s ingest of
+ * an n = 8192 matrix; 8 MiB pieces still move at the PCIe rate (profiles/r02_h2d_1gpu_sweep.json).
+ * CGB_INGEST_CHUNK_MIB (1..256) overrides it for measurements. */
+#define CHUNK_BYTES_DEFAULT ((size_t)8 << 20)
 #define CHUNK_SLACK 4096
 #define EXC_CAP 65536u
 
@@ -69,6 +74,66 @@ static int load_block_on_host(cgb_ctx *c, const char *fileA, int64_t first, int6
     return CGB_OK;
 }
 
+/* Staging memory of one text load: ONE pinned allocation (two chunk buffers) and ONE device allocation (two
+ * chunk buffers, the per-CTA token counts and offsets, the exception list, the running state), carved up at
+ * 256-byte borders -- nine allocator calls each way were 11 ms of a 50 ms load (CGB_INGEST_TIMING). */
+typedef struct {
+    unsigned char *pin_base, *dev_base;
+    unsigned char *pin[2], *dtxt[2];
+    cudaEvent_t ev[2];
+    unsigned int *d_counts;
+    long long *d_offsets, *d_exc_idx;
+    unsigned long long *d_exc_pos;
+    cgk_ingest_state *d_state;
+} ingest_buffers;
+
+static size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static int ingest_buffers_get(ingest_buffers *b, size_t buf_bytes, int64_t max_blocks, cudaStream_t st)
+{
+    int rc = CGB_OK;
+    const size_t chunk = up256(buf_bytes);
+    size_t off = 2 * chunk;
+    const size_t o_counts = off;  off += up256((size_t)max_blocks * sizeof(unsigned int));
+    const size_t o_offsets = off; off += up256((size_t)max_blocks * sizeof(long long));
+    const size_t o_exc_pos = off; off += up256((size_t)EXC_CAP * sizeof(unsigned long long));
+    const size_t o_exc_idx = off; off += up256((size_t)EXC_CAP * sizeof(long long));
+    const size_t o_state = off;   off += up256(sizeof(cgk_ingest_state));
+    CU(cudaHostAlloc((void **)&b->pin_base, 2 * chunk, cudaHostAllocDefault));
+    CU(cudaMalloc((void **)&b->dev_base, off));
+    for (int s = 0; s < 2; ++s) {
+        b->pin[s] = b->pin_base + (size_t)s * chunk;
+        b->dtxt[s] = b->dev_base + (size_t)s * chunk;
+        CU(cudaEventCreateWithFlags(&b->ev[s], cudaEventDisableTiming));
+    }
+    b->d_counts = (unsigned int *)(b->dev_base + o_counts);
+    b->d_offsets = (long long *)(b->dev_base + o_offsets);
+    b->d_exc_pos = (unsigned long long *)(b->dev_base + o_exc_pos);
+    b->d_exc_idx = (long long *)(b->dev_base + o_exc_idx);
+    b->d_state = (cgk_ingest_state *)(b->dev_base + o_state);
+    CU(cudaMemsetAsync(b->d_state, 0, sizeof *b->d_state, st));
+out:
+    return rc;
+}
+
+static void ingest_buffers_put(ingest_buffers *b)
+{
+    if (b->pin_base) cudaFreeHost(b->pin_base);
+    cudaFree(b->dev_base);
+    for (int s = 0; s < 2; ++s)
+        if (b->ev[s]) cudaEventDestroy(b->ev[s]);
+    memset(b, 0, sizeof *b);
+}
+
+/* The host threads count tokens (cgb_text_locate) while the calling thread pins and allocates. */
+typedef struct { const cgb_text *tx; int64_t first, count, total; size_t beg, end; } locate_job;
+static void *locate_main(void *arg)
+{
+    locate_job *j = arg;
+    j->total = cgb_text_locate(j->tx, j->first, j->count, &j->beg, &j->end);
+    return NULL;
+}
+
 static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *fileB, const char *fileX);
 int cgb_load_text(cgb_ctx *c, int64_t n, const char *fileA, const char *fileB, const char *fileX)
 {
@@ -87,15 +152,12 @@ static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *
     cudaStream_t st = c->stream;
 
     double *hv = NULL;
-    unsigned char *pin[2] = {NULL, NULL}, *dtxt[2] = {NULL, NULL};
-    cudaEvent_t ev[2] = {NULL, NULL};
-    unsigned int *d_counts = NULL;
-    long long *d_offsets = NULL, *d_exc_idx = NULL;
-    unsigned long long *d_exc_pos = NULL;
-    cgk_ingest_state *d_state = NULL, h_state;
+    ingest_buffers B;
+    cgk_ingest_state h_state;
     cgb_text tx;
     int have_text = 0;
     memset(&tx, 0, sizeof tx);
+    memset(&B, 0, sizeof B);
 
     /* ---- b (the rank's m entries) and x0 (all n): n values each, host parser */
     hv = malloc((size_t)n * sizeof(double));
@@ -115,28 +177,37 @@ static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *
     }
 
     /* ---- A: locate the rank's bytes, stream them, parse on the GPU */
+    const double t_vec = now_s();
+    double t_loc = t_vec, t_alloc = t_vec;
     if (cgb_text_open(fileA, &tx) != 0) { rc = io_error("Could not open file ", fileA); goto out; }
     have_text = 1;
-    size_t beg = 0, end = 0;
-    const int64_t total = cgb_text_locate(&tx, first, count, &beg, &end);
+    size_t CHUNK_BYTES = CHUNK_BYTES_DEFAULT;
+    {
+        const char *e = getenv("CGB_INGEST_CHUNK_MIB");
+        const long v = (e && *e) ? atol(e) : 0;
+        if (v >= 1 && v <= 256) CHUNK_BYTES = (size_t)v << 20;
+    }
+    const size_t buf_bytes = CHUNK_BYTES + CHUNK_SLACK;
+    locate_job lj = {&tx, first, count, 0, 0, 0};
+    pthread_t lth;
+    const int threaded = pthread_create(&lth, NULL, locate_main, &lj) == 0;
+    const int rc_buf = ingest_buffers_get(&B, buf_bytes, cgk_ingest_blocks((int64_t)buf_bytes), st);
+    t_alloc = now_s();
+    if (threaded) pthread_join(lth, NULL); else locate_main(&lj);
+    t_loc = now_s();
+    const size_t beg = lj.beg, end = lj.end;
+    const int64_t total = lj.total;
     if (total < 0) { rc = load_block_on_host(c, fileA, first, count); goto done; }
     /* fewer tokens than values: either a short file or tokens like "1-2" that the sequential
      * strtod loop reads as two values -- that loop is the authority (and words the error) */
     if (total < n * n) { rc = load_block_on_host(c, fileA, first, count); goto done; }
-
-    const size_t buf_bytes = CHUNK_BYTES + CHUNK_SLACK;
-    const int64_t max_blocks = cgk_ingest_blocks((int64_t)buf_bytes);
-    for (int s = 0; s < 2; ++s) {
-        CU(cudaHostAlloc((void **)&pin[s], buf_bytes, cudaHostAllocDefault));
-        CU(cudaMalloc((void **)&dtxt[s], buf_bytes));
-        CU(cudaEventCreateWithFlags(&ev[s], cudaEventDisableTiming));
-    }
-    CU(cudaMalloc((void **)&d_counts, (size_t)max_blocks * sizeof(unsigned int)));
-    CU(cudaMalloc((void **)&d_offsets, (size_t)max_blocks * sizeof(long long)));
-    CU(cudaMalloc((void **)&d_exc_pos, (size_t)EXC_CAP * sizeof(unsigned long long)));
-    CU(cudaMalloc((void **)&d_exc_idx, (size_t)EXC_CAP * sizeof(long long)));
-    CU(cudaMalloc((void **)&d_state, sizeof *d_state));
-    CU(cudaMemsetAsync(d_state, 0, sizeof *d_state, st));
+    if (rc_buf != CGB_OK) { rc = rc_buf; goto out; }
+    unsigned char **pin = B.pin, **dtxt = B.dtxt;
+    cudaEvent_t *ev = B.ev;
+    unsigned int *d_counts = B.d_counts;
+    long long *d_offsets = B.d_offsets, *d_exc_idx = B.d_exc_idx;
+    unsigned long long *d_exc_pos = B.d_exc_pos;
+    cgk_ingest_state *d_state = B.d_state;
 
     {
         size_t pos = beg;
@@ -199,6 +270,9 @@ static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *
 done:
     if (rc == CGB_OK) {
         c->h2d_seconds = now_s() - t0;
+        if (getenv("CGB_INGEST_TIMING"))                        /* where a text load spends its time (tools/ingest_rate.py) */
+            fprintf(stderr, "cgb_load_text rank %d: b+x0 %.4f s, buffers %.4f s while locating, locate joined after %.4f s, stream+parse %.4f s, total %.4f s\n",
+                    c->rank, t_vec - t0, t_alloc - t_vec, t_loc - t_vec, now_s() - t_loc, c->h2d_seconds);
         c->loaded = 1;
         c->sym_state = 0;
         c->tiles_only = 0;
@@ -208,11 +282,6 @@ done:
 out:
     if (have_text) cgb_text_close(&tx);
     free(hv);
-    for (int s = 0; s < 2; ++s) {
-        if (pin[s]) cudaFreeHost(pin[s]);
-        cudaFree(dtxt[s]);
-        if (ev[s]) cudaEventDestroy(ev[s]);
-    }
-    cudaFree(d_counts); cudaFree(d_offsets); cudaFree(d_exc_pos); cudaFree(d_exc_idx); cudaFree(d_state);
+    ingest_buffers_put(&B);
     return rc;
 }

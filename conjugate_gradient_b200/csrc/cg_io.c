@@ -80,13 +80,38 @@ static int64_t parse_all(const char *buf, size_t len, double *dst, int64_t cap, 
 static const double k_pow10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
-int cgb_is_sep_byte(unsigned char ch)
+/* The byte loops below run once per byte of a multi-GB text.  The exported names are reached
+ * through the PLT from inside a -fPIC library and are never inlined (~5 ns per byte, 0.2 GB/s per
+ * thread, measured: locating the rows of an n = 8192 matrix took 0.37 s on 8 cores), so the file
+ * uses these file-local forms and the exported ones are wrappers for the other translation units. */
+static inline int is_sep(unsigned char ch)
 {
-    return ch == ' ' || ch == '\t' || ch == '\n' || ch == '\r' || ch == ',' || ch == ';' || ch == '\f' || ch == '\v';
+    return (unsigned)(ch - '\t') <= 4u || ch == ' ' || ch == ',' || ch == ';';   /* \t \n \v \f \r are 9..13 */
 }
 
+int cgb_is_sep_byte(unsigned char ch) { return is_sep(ch); }
+
+#if defined(__SSE2__)
+#include <emmintrin.h>
+/* 16 bytes at p: bit i of the result = byte i is a separator; *high gets bit i = byte i >= 0x80 */
+static inline unsigned sep_mask16(const char *p, unsigned *high)
+{
+    const __m128i v = _mm_loadu_si128((const __m128i *)p);
+    const __m128i w = _mm_sub_epi8(v, _mm_set1_epi8('\t'));
+    __m128i m = _mm_cmpeq_epi8(_mm_min_epu8(w, _mm_set1_epi8(4)), w);            /* (ch - 9) <= 4, unsigned */
+    m = _mm_or_si128(m, _mm_cmpeq_epi8(v, _mm_set1_epi8(' ')));
+    m = _mm_or_si128(m, _mm_cmpeq_epi8(v, _mm_set1_epi8(',')));
+    m = _mm_or_si128(m, _mm_cmpeq_epi8(v, _mm_set1_epi8(';')));
+    *high = (unsigned)_mm_movemask_epi8(v);
+    return (unsigned)_mm_movemask_epi8(m);
+}
+#endif
+
 /* One token [p, e): returns 1 and *out if it is a plain decimal number, else 0. */
-int cgb_token_to_double(const char *p, const char *e, double *out)
+static inline int token_to_double(const char *p, const char *e, double *out);
+int cgb_token_to_double(const char *p, const char *e, double *out) { return token_to_double(p, e, out); }
+
+static inline int token_to_double(const char *p, const char *e, double *out)
 {
     const char *s = p;
     int neg = 0;
@@ -144,18 +169,31 @@ typedef struct {
     int irregular;
 } span_job;
 
+/* Token starts in [beg, end): a non-separator byte whose predecessor is a separator (or beg). */
 static void *span_count(void *arg)
 {
     span_job *j = arg;
     int64_t k = 0;
-    int in_tok = 0;
-    for (const char *p = j->beg; p < j->end; ++p) {
-        const unsigned char ch = (unsigned char)*p;
-        const int sep = cgb_is_sep_byte(ch);
-        if (ch >= 0x80) j->irregular = 1;                  /* BOM or junk: sequential path decides */
-        if (!sep && !in_tok) ++k;
-        in_tok = !sep;
+    unsigned prev_sep = 1, junk = 0;                       /* the span starts at a cut: "after a separator" */
+    const char *p = j->beg;
+#if defined(__SSE2__)
+    for (; j->end - p >= 16; p += 16) {
+        unsigned high;
+        const unsigned sep = sep_mask16(p, &high);
+        const unsigned starts = ~sep & ((sep << 1) | prev_sep) & 0xFFFFu;
+        k += __builtin_popcount(starts);
+        prev_sep = (sep >> 15) & 1u;
+        junk |= high;
     }
+#endif
+    for (; p < j->end; ++p) {
+        const unsigned char ch = (unsigned char)*p;
+        const unsigned sep = (unsigned)is_sep(ch);
+        junk |= ch & 0x80u;
+        k += (int64_t)(~sep & prev_sep & 1u);
+        prev_sep = sep;
+    }
+    if (junk) j->irregular = 1;                            /* BOM or junk: sequential path decides */
     j->count = k;
     return NULL;
 }
@@ -166,12 +204,12 @@ static void *span_parse(void *arg)
     const char *p = j->beg;
     int64_t k = j->offset;
     while (p < j->end) {
-        while (p < j->end && cgb_is_sep_byte((unsigned char)*p)) ++p;
+        while (p < j->end && is_sep((unsigned char)*p)) ++p;
         if (p >= j->end) break;
         const char *e = p;
-        while (e < j->end && !cgb_is_sep_byte((unsigned char)*e)) ++e;
+        while (e < j->end && !is_sep((unsigned char)*e)) ++e;
         if (k >= j->cap) break;                            /* caller wanted only the first `cap` values */
-        if (!cgb_token_to_double(p, e, &j->dst[k])) { j->irregular = 1; return NULL; }
+        if (!token_to_double(p, e, &j->dst[k])) { j->irregular = 1; return NULL; }
         ++k;
         p = e;
     }
@@ -219,7 +257,9 @@ void cgb_parallel_copy(void *dst, const void *src, size_t len)
     if (T > 8) T = 8;
     if (T <= 1) { memcpy(dst, src, len); return; }
     copy_job job[8];
-    const size_t per = (len / (size_t)T + 4095) & ~(size_t)4095;            /* page-sized pieces */
+    /* page-sized pieces that COVER len: the quotient is rounded up first (len / T rounded down left up to
+     * T - 1 tail bytes uncopied whenever len / T was a multiple of the page size: 8 MiB + 3 bytes on 8 threads) */
+    const size_t per = ((len + (size_t)T - 1) / (size_t)T + 4095) & ~(size_t)4095;
     int used = 0;
     for (size_t off = 0; off < len && used < 8; off += per, ++used) {
         job[used].dst = (char *)dst + off; job[used].src = (const char *)src + off;
@@ -237,7 +277,7 @@ static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t 
     for (int t = 0; t < T; ++t) {
         const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
         if (nxt < cut) nxt = cut;
-        while (nxt < end && !cgb_is_sep_byte((unsigned char)*nxt)) ++nxt;     /* cut only at a separator */
+        while (nxt < end && !is_sep((unsigned char)*nxt)) ++nxt;              /* cut only at a separator */
         memset(&job[t], 0, sizeof job[t]);
         job[t].beg = cut; job[t].end = nxt;
         cut = nxt;
@@ -290,10 +330,25 @@ void cgb_text_close(cgb_text *t)
 static const char *span_seek(const char *beg, const char *end, int64_t k)
 {
     const char *p = beg;
+#if defined(__SSE2__)
+    /* whole 16-byte groups whose token starts all lie before the k-th are skipped by count */
+    unsigned prev_sep = 1;
+    while (end - p >= 16) {
+        unsigned high;
+        const unsigned sep = sep_mask16(p, &high);
+        const int64_t c = __builtin_popcount(~sep & ((sep << 1) | prev_sep) & 0xFFFFu);
+        if (c > k) break;                                  /* the k-th start is inside this group */
+        k -= c;
+        prev_sep = (sep >> 15) & 1u;
+        p += 16;
+    }
+    if (!prev_sep)                                         /* inside a token counted already: step over its tail */
+        while (p < end && !is_sep((unsigned char)*p)) ++p;
+#endif
     for (;;) {
-        while (p < end && cgb_is_sep_byte((unsigned char)*p)) ++p;
+        while (p < end && is_sep((unsigned char)*p)) ++p;
         if (p >= end || k == 0) return p;
-        while (p < end && !cgb_is_sep_byte((unsigned char)*p)) ++p;
+        while (p < end && !is_sep((unsigned char)*p)) ++p;
         --k;
     }
 }
@@ -308,7 +363,7 @@ int64_t cgb_text_locate(const cgb_text *tx, int64_t first, int64_t count, size_t
     for (int t = 0; t < T; ++t) {
         const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
         if (nxt < cut) nxt = cut;
-        while (nxt < end && !cgb_is_sep_byte((unsigned char)*nxt)) ++nxt;
+        while (nxt < end && !is_sep((unsigned char)*nxt)) ++nxt;
         memset(&job[t], 0, sizeof job[t]);
         job[t].beg = cut; job[t].end = nxt;
         cut = nxt;

@@ -182,7 +182,9 @@ int main(int argc, char **argv)
 
     /* the ingest's staging copy: every byte, every split, exact-size buffers */
     {
-        const size_t sizes[] = {0, 1, 4095, 4096, 4097, (size_t)1 << 20, ((size_t)3 << 20) + 17, ((size_t)32 << 20) + 2053};
+        /* 8 MiB + 3 and 32 MiB + 5: a quotient len / threads that is a whole number of pages with a remainder left over */
+        const size_t sizes[] = {0, 1, 4095, 4096, 4097, (size_t)1 << 20, ((size_t)3 << 20) + 17, ((size_t)32 << 20) + 2053,
+                                ((size_t)8 << 20) + 3, ((size_t)32 << 20) + 5, ((size_t)2 << 20) + 1, (size_t)8 * 4096 + 7};
         for (unsigned t = 0; t < sizeof threads / sizeof *threads; ++t) {
             setenv("CGB_IO_THREADS", threads[t], 1);
             for (unsigned k = 0; k < sizeof sizes / sizeof *sizes; ++k) {

@@ -87,7 +87,7 @@ def test_bom_and_irregular_tokens_follow_the_sequential_parser(cg, ctx, tmp_path
 
 
 def test_multi_chunk_file(cg, ctx, tmp_path):
-    n = 2200                                                  # ~43 MB of text: two 32 MiB chunks
+    n = 2200                                                  # ~43 MB of text: six 8 MiB chunks (it was two of 32 MiB)
     fa, fb, fx = (str(tmp_path / s) for s in ("A.txt", "b.txt", "x.txt"))
     A = (np.random.default_rng(1).random(n * n) * 2048.0).round(4)
     cg.write_values(fa, A, 4)
@@ -100,6 +100,25 @@ def test_multi_chunk_file(cg, ctx, tmp_path):
     # extra values after the n*n-th are ignored, as fscanf's fixed count does (serialConjugate.c:92-98)
     ctx.load_text(n - 1, fa, fb, fx)
     assert ctx.debug_read(0, 0, (n - 1) * (n - 1)).tobytes() == want[: (n - 1) * (n - 1)].tobytes()
+
+
+def test_every_staging_chunk_size_gives_the_host_parsers_doubles(cg, ctx, tmp_path, monkeypatch):
+    """The bytes of a chunk reach the GPU through a pinned buffer filled by several host threads.  Round 2 found
+    that copy dropping up to 7 tail bytes of a chunk whose length / threads was a whole number of pages (8 MiB + 3):
+    the GPU then parsed whatever the recycled pinned buffer held there ("0.5618" read as "0.5").  Fresh buffers are
+    zero-filled and zeros go to the exception list, so a single load hid it; loads in a row with different chunk
+    sizes (CGB_INGEST_CHUNK_MIB) recycle pinned memory that holds text and do not."""
+    n = 2200
+    fa, fb, fx = (str(tmp_path / s) for s in ("A.txt", "b.txt", "x.txt"))
+    A = (np.random.default_rng(7).random(n * n) * 64.0).round(4)
+    cg.write_values(fa, A, 4)
+    cg.write_values(fb, np.ones(n), 4)
+    cg.write_values(fx, np.zeros(n), 1)
+    want = cg.read_values(fa, n * n).tobytes()
+    for mib in (32, 8, 1, 2, 4, 8, 1):
+        monkeypatch.setenv("CGB_INGEST_CHUNK_MIB", str(mib))
+        ctx.load_text(n, fa, fb, fx)
+        assert ctx.debug_read(0, 0, n * n).tobytes() == want, f"chunks of {mib} MiB"
 
 
 def test_short_and_missing_files_are_errors(cg, ctx, tmp_path):

@@ -178,6 +178,52 @@ def test_locating_a_ranks_rows_in_the_text(tmp_path, ranks):
         L.cgb_text_close(C.byref(tx))
 
 
+@pytest.mark.parametrize("threads", [1, 3, 8])
+def test_locate_on_several_spans_against_a_byte_level_reference(tmp_path, threads, monkeypatch):
+    """cgb_text_locate counts token starts 16 bytes at a time (SSE2) in one span per host thread and seeks the
+    rank's first / one-past-last token by skipping whole groups: tokens of 1..40 bytes, runs of every separator
+    the reader tolerates (initialize()'s "%f%*c", serialConjugate.c:92-98), tokens that straddle group and span
+    borders, a file of a few MiB so that there ARE several spans; checked against numpy on the raw bytes."""
+    L = _io()
+    monkeypatch.setenv("CGB_IO_THREADS", str(threads))
+    rng = np.random.default_rng(100 + threads)
+    ntok = 260_000
+    lens = rng.choice([1, 2, 3, 6, 7, 15, 16, 17, 31, 40], ntok)
+    digits = np.frombuffer(b"0123456789", np.uint8)
+    seps = np.frombuffer(b" \t\n\r,;\f\v", np.uint8)
+    pieces = [b"\n \t"]                                                       # leading separators
+    seplens = rng.choice([1, 1, 1, 2, 3, 17, 33], ntok)
+    body = digits[rng.integers(0, 10, int(lens.sum()))]
+    sepb = seps[rng.integers(0, 8, int(seplens.sum()))]
+    bo = np.concatenate(([0], np.cumsum(lens))); so = np.concatenate(([0], np.cumsum(seplens)))
+    for k in range(ntok):
+        pieces.append(body[bo[k]:bo[k + 1]].tobytes()); pieces.append(sepb[so[k]:so[k + 1]].tobytes())
+    raw = b"".join(pieces)
+    if threads == 3: raw = raw.rstrip(b" \t\n\r,;\f\v")                        # last token ends the file
+    assert len(raw) > 3 << 20
+    a = np.frombuffer(raw, np.uint8)
+    is_sep = np.isin(a, seps)
+    starts = np.flatnonzero(~is_sep & np.concatenate(([True], is_sep[:-1])))
+    assert len(starts) == ntok
+    f = tmp_path / "tokens.txt"
+    f.write_bytes(raw)
+    tx = Text()
+    assert L.cgb_text_open(os.fsencode(str(f)), C.byref(tx)) == 0
+    try:
+        beg, end = C.c_size_t(), C.c_size_t()
+        cases = [(0, ntok), (0, 1), (ntok - 1, 1), (ntok // 2, ntok // 2), (ntok // 3, ntok // 3), (5, 0)]
+        cases += [(int(x), int(c)) for x, c in zip(rng.integers(0, ntok - 1000, 40), rng.integers(1, 1000, 40))]
+        for first, count in cases:
+            assert L.cgb_text_locate(C.byref(tx), first, count, C.byref(beg), C.byref(end)) == ntok
+            assert beg.value == starts[first], (first, count)
+            want_end = starts[first] if count == 0 else (starts[first + count] if first + count < ntok else len(raw))
+            assert end.value == want_end, (first, count)
+        assert L.cgb_text_locate(C.byref(tx), 10, ntok, C.byref(beg), C.byref(end)) == ntok     # past the end: the count says so
+        assert beg.value == end.value == len(raw)
+    finally:
+        L.cgb_text_close(C.byref(tx))
+
+
 def test_locate_defers_files_with_a_bom_to_the_sequential_parser(tmp_path):
     L = _io()
     f = tmp_path / "bom.txt"
