@@ -16,6 +16,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <unistd.h>
 
 #include "../../include/cgb200.h"
 #include "cg_kernels.h"
@@ -153,6 +154,7 @@ static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *
 
     double *hv = NULL;
     ingest_buffers B;
+    cgb_copy_pool *pool = NULL;
     cgk_ingest_state h_state;
     cgb_text tx;
     int have_text = 0;
@@ -210,6 +212,14 @@ static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *
     cgk_ingest_state *d_state = B.d_state;
 
     {
+        /* the copy team spins between chunks: never more members than this rank's share of the CPUs */
+        int team = cgb_copy_pool_threads(CHUNK_BYTES);
+        const long share = sysconf(_SC_NPROCESSORS_ONLN) / (c->ranks > 0 ? c->ranks : 1);
+        if (team > share) team = (int)share;
+        { const char *e = getenv("CGB_INGEST_TEAM"); const long v = (e && *e) ? atol(e) : 0; if (v >= 1 && v <= 64) team = (int)v; }
+        pool = getenv("CGB_INGEST_NO_POOL") ? NULL : cgb_copy_pool_start(team);
+    }
+    {
         size_t pos = beg;
         int s = 0, used[2] = {0, 0};
         while (pos < end) {
@@ -220,7 +230,7 @@ static int load_text_body(cgb_ctx *c, int64_t n, const char *fileA, const char *
             const size_t len = cend - pos;
             const size_t padded = (len + 15) / 16 * 16;
             if (used[s]) CU(cudaEventSynchronize(ev[s]));         /* its previous upload has left the pinned buffer */
-            cgb_parallel_copy(pin[s], tx.p + pos, len);          /* mapped file -> pinned staging buffer */
+            cgb_copy_pool_run(pool, pin[s], tx.p + pos, len);    /* mapped file -> pinned staging buffer */
             memset(pin[s] + len, '\n', padded - len + 64);
             CU(cudaMemcpyAsync(dtxt[s], pin[s], padded + 64, cudaMemcpyHostToDevice, st));
             CU(cudaEventRecord(ev[s], st));
@@ -282,6 +292,7 @@ done:
 out:
     if (have_text) cgb_text_close(&tx);
     free(hv);
+    cgb_copy_pool_stop(pool);
     ingest_buffers_put(&B);
     return rc;
 }

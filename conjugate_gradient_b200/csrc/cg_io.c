@@ -5,6 +5,8 @@
 #include <errno.h>
 #include <fcntl.h>
 #include <pthread.h>
+#include <sched.h>
+#include <time.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/mman.h>
@@ -266,6 +268,139 @@ void cgb_parallel_copy(void *dst, const void *src, size_t len)
         job[used].len = len - off < per ? len - off : per;
     }
     run_jobs(copy_main, job, sizeof job[0], used);
+}
+
+/* A team of copy threads that lives for one text load: cgb_parallel_copy starts and joins its threads for
+ * every chunk, which is a third of the copy time at 8 MiB per chunk (20 against 33 GB/s on the build
+ * container).  Between chunks the workers SPIN on the chunk counter for up to POOL_SPIN_NS (the caller is
+ * back within tens of microseconds: it only issues one copy and three launches) and only then sleep on a
+ * condition variable -- waking 15 sleepers through futexes cost more than the 0.25 ms a chunk takes
+ * (measured on the 16-vCPU bench box: 8 MiB chunks on 16 threads 53-61 ms against 20 ms with 8 threads). */
+#define POOL_SPIN_NS 200000L
+struct cgb_copy_pool;
+typedef struct { struct cgb_copy_pool *pool; int share; } pool_arg;
+struct cgb_copy_pool {
+    int workers;                               /* threads besides the caller */
+    pthread_t th[IO_MAX_THREADS];
+    pthread_mutex_t mu;
+    pthread_cond_t go;
+    unsigned long epoch;                       /* one per chunk; atomic, stored under mu */
+    int pending;                               /* workers still copying; atomic */
+    int quit, sleepers;                        /* quit: atomic, stored under mu; sleepers: under mu */
+    char *dst; const char *src; size_t len, per;   /* published before the epoch (release / acquire) */
+    pool_arg arg[IO_MAX_THREADS];
+};
+
+static inline void cpu_relax(void)
+{
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+}
+
+static long mono_ns(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (long)ts.tv_sec * 1000000000L + ts.tv_nsec;
+}
+
+static void pool_copy_share(int share, char *dst, const char *src, size_t len, size_t per)
+{
+    const size_t off = (size_t)share * per;
+    if (off < len) memcpy(dst + off, src + off, len - off < per ? len - off : per);
+}
+
+static void *pool_main(void *a)
+{
+    struct cgb_copy_pool *p = ((pool_arg *)a)->pool;
+    const int share = ((pool_arg *)a)->share;
+    unsigned long seen = 0;
+    for (;;) {
+        unsigned long e;
+        long t_begin = 0;
+        unsigned spins = 0;
+        while ((e = __atomic_load_n(&p->epoch, __ATOMIC_ACQUIRE)) == seen && !__atomic_load_n(&p->quit, __ATOMIC_ACQUIRE)) {
+            cpu_relax();
+            if ((++spins & 63u) != 0) continue;
+            const long now = mono_ns();
+            if (!t_begin) t_begin = now;
+            if (now - t_begin < POOL_SPIN_NS) continue;
+            pthread_mutex_lock(&p->mu);                    /* nothing for a long while: sleep until told */
+            ++p->sleepers;
+            while (__atomic_load_n(&p->epoch, __ATOMIC_ACQUIRE) == seen && !__atomic_load_n(&p->quit, __ATOMIC_ACQUIRE))
+                pthread_cond_wait(&p->go, &p->mu);
+            --p->sleepers;
+            pthread_mutex_unlock(&p->mu);
+        }
+        if (e == seen) return NULL;                        /* quit */
+        seen = e;
+        pool_copy_share(share, p->dst, p->src, p->len, p->per);
+        __atomic_fetch_sub(&p->pending, 1, __ATOMIC_ACQ_REL);
+    }
+}
+
+cgb_copy_pool *cgb_copy_pool_start(int threads)
+{
+    if (threads > IO_MAX_THREADS) threads = IO_MAX_THREADS;
+    if (threads < 2) return NULL;
+    cgb_copy_pool *p = calloc(1, sizeof *p);
+    if (!p) return NULL;
+    pthread_mutex_init(&p->mu, NULL);
+    pthread_cond_init(&p->go, NULL);
+    for (int t = 0; t < threads - 1; ++t) {
+        p->arg[p->workers].pool = p; p->arg[p->workers].share = p->workers + 1;     /* share 0 is the caller's */
+        if (pthread_create(&p->th[p->workers], NULL, pool_main, &p->arg[p->workers]) != 0) break;
+        ++p->workers;                           /* a thread that cannot be started just makes the team smaller */
+    }
+    if (p->workers == 0) { cgb_copy_pool_stop(p); return NULL; }
+    return p;
+}
+
+void cgb_copy_pool_run(cgb_copy_pool *p, void *dst, const void *src, size_t len)
+{
+    if (!p) { cgb_parallel_copy(dst, src, len); return; }
+    if (len < ((size_t)1 << 20)) { memcpy(dst, src, len); return; }
+    const size_t shares = (size_t)p->workers + 1;
+    const size_t per = ((len + shares - 1) / shares + 4095) & ~(size_t)4095;        /* pages, covering len */
+    p->dst = dst; p->src = src; p->len = len; p->per = per;
+    __atomic_store_n(&p->pending, p->workers, __ATOMIC_RELAXED);
+    pthread_mutex_lock(&p->mu);
+    __atomic_store_n(&p->epoch, p->epoch + 1, __ATOMIC_RELEASE);
+    if (p->sleepers > 0) pthread_cond_broadcast(&p->go);
+    pthread_mutex_unlock(&p->mu);
+    pool_copy_share(0, (char *)dst, (const char *)src, len, per);
+    unsigned spins = 0;
+    while (__atomic_load_n(&p->pending, __ATOMIC_ACQUIRE) > 0) {
+        cpu_relax();
+        if ((++spins & 4095u) == 0) sched_yield();          /* a worker without a CPU of its own gets ours */
+    }
+}
+
+void cgb_copy_pool_stop(cgb_copy_pool *p)
+{
+    if (!p) return;
+    pthread_mutex_lock(&p->mu);
+    __atomic_store_n(&p->quit, 1, __ATOMIC_RELEASE);
+    pthread_cond_broadcast(&p->go);
+    pthread_mutex_unlock(&p->mu);
+    for (int t = 0; t < p->workers; ++t) pthread_join(p->th[t], NULL);
+    pthread_cond_destroy(&p->go);
+    pthread_mutex_destroy(&p->mu);
+    free(p);
+}
+
+/* threads a copy team should have for chunks of `chunk` bytes: the online CPUs (CGB_IO_THREADS caps it), at
+ * most 8 -- on the 16-vCPU bench box teams of 4 to 8 stream an 8 MiB chunk in the same time (stream + parse of
+ * the n = 8192 file 12.8-12.9 ms) and a team of 16 is slower (16.5 ms): the caller's CUDA calls and the driver's
+ * own threads want CPUs too -- and no thread with less than 512 KiB to move */
+int cgb_copy_pool_threads(size_t chunk)
+{
+    int T = io_threads((size_t)IO_MAX_THREADS << 20);
+    if (T > 8) T = 8;
+    const size_t by_size = chunk / ((size_t)512 << 10);
+    if ((size_t)T > by_size) T = (int)by_size;
+    return T < 1 ? 1 : T;
 }
 
 /* Returns the number of values, or -1 when the file needs the sequential path. */

@@ -28,6 +28,15 @@ int64_t cgb_text_locate(const cgb_text *t, int64_t first, int64_t count, size_t 
 /* memcpy split between up to 8 threads (CGB_IO_THREADS caps it; below 2 MiB a plain memcpy). */
 void cgb_parallel_copy(void *dst, const void *src, size_t len);
 
+/* The same copy by a team of threads that is started once and reused for every chunk of a text load
+ * (cgb_copy_pool_threads(chunk) members, the caller included).  start returns NULL when no team could be
+ * formed: run(NULL, ...) is cgb_parallel_copy. */
+typedef struct cgb_copy_pool cgb_copy_pool;
+int  cgb_copy_pool_threads(size_t chunk);
+cgb_copy_pool *cgb_copy_pool_start(int threads);
+void cgb_copy_pool_run(cgb_copy_pool *p, void *dst, const void *src, size_t len);
+void cgb_copy_pool_stop(cgb_copy_pool *p);
+
 /* cgb_write_values() with the choice to append (row blocks of a matrix written in turn). */
 int cgb_write_values_mode(const char *path, const double *v, int64_t count, int fmt_decimals, int append);
 #ifdef __cplusplus

@@ -197,6 +197,31 @@ int main(int argc, char **argv)
                 free(src); free(dst);
             }
         }
+        /* the team that lives for a whole text load: the same sizes in a row through ONE team, every team size */
+        const int teams[] = {2, 3, 8, 16};
+        for (unsigned t = 0; t < sizeof teams / sizeof *teams; ++t) {
+            cgb_copy_pool *pool = cgb_copy_pool_start(teams[t]);
+#ifdef CGB_TEST_THREADS_FAIL
+            CHECK(pool == NULL, "no team when no thread can be created (%d)", teams[t]);   /* run(NULL, ..) still copies */
+#else
+            CHECK(pool != NULL, "copy team of %d", teams[t]);
+#endif
+            for (int round = 0; round < 2; ++round)
+                for (unsigned k = 0; k < sizeof sizes / sizeof *sizes; ++k) {
+                    const size_t len = sizes[k];
+                    unsigned char *src = malloc(len + 1), *dst = malloc(len + 1);
+                    for (size_t i = 0; i < len; ++i) src[i] = (unsigned char)((i + k) * 2654435761u >> 11);
+                    memset(dst, 0xEE, len + 1);
+                    cgb_copy_pool_run(pool, dst, src, len);
+                    CHECK(memcmp(dst, src, len) == 0 && dst[len] == 0xEE, "team copy of %zu bytes (team %d)", len, teams[t]);
+                    free(src); free(dst);
+                }
+            cgb_copy_pool_stop(pool);
+        }
+        CHECK(cgb_copy_pool_start(1) == NULL, "a team of one is no team");
+        cgb_copy_pool_stop(NULL);
+        CHECK(cgb_copy_pool_threads((size_t)8 << 20) >= 1 && cgb_copy_pool_threads((size_t)8 << 20) <= 8, "team size");
+        CHECK(cgb_copy_pool_threads(1000) == 1, "team size for tiny chunks");
     }
 
     FILE *nul = fopen("/dev/null", "w");
