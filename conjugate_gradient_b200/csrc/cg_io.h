@@ -37,6 +37,10 @@ cgb_copy_pool *cgb_copy_pool_start(int threads);
 void cgb_copy_pool_run(cgb_copy_pool *p, void *dst, const void *src, size_t len);
 void cgb_copy_pool_stop(cgb_copy_pool *p);
 
+/* One value as printf("%.{decimals}f\n") would write it, by integer arithmetic (the writer's fast path);
+ * returns the bytes written (at most 48), or 0 when the value is left to printf (inf, nan, >= 2^52, decimals > 17). */
+size_t cgb_format_fixed(char *out, double v, int decimals);
+
 /* cgb_write_values() with the choice to append (row blocks of a matrix written in turn). */
 int cgb_write_values_mode(const char *path, const double *v, int64_t count, int fmt_decimals, int append);
 #ifdef __cplusplus

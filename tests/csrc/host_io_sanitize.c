@@ -224,6 +224,43 @@ int main(int argc, char **argv)
         CHECK(cgb_copy_pool_threads(1000) == 1, "team size for tiny chunks");
     }
 
+    /* the writer's integer-arithmetic "%.{d}f": byte for byte printf's, wherever it answers at all */
+    {
+        uint64_t st = 0x9E3779B97F4A7C15ull;
+        long covered = 0, total = 0;
+        const double fixed[] = {0.0, -0.0, 0.03125, 0.09375, 0.5, 1.5, 2.5, -2.5, 0.00005, 0.00015, 0.99995, 0.999949999999,
+                                8192.5118, 4096.00005, 1e-5, 4.9e-324, 2.2250738585072014e-308, 1e15, 9.2e14, 9.3e14,
+                                4503599627370495.5, 4503599627370496.0, 1e22, 1.7976931348623157e308, 0.125, 0.375, 1e-17,
+                                5e-18, 123456789.987654321, 0.1, 0.2, 0.3, 0.7, 1.0 / 3.0, 2.0 / 3.0, 1e-300};
+        for (int rep = 0; rep < 400000; ++rep) {
+            double v;
+            if (rep < (int)(sizeof fixed / sizeof *fixed)) v = fixed[rep];
+            else {
+                st ^= st << 13; st ^= st >> 7; st ^= st << 17;
+                const int kind = (int)(st % 5);
+                if (kind == 0) { uint64_t b = st * 0x2545F4914F6CDD1Dull; memcpy(&v, &b, 8); }              /* any bit pattern */
+                else if (kind == 1) v = (double)(st >> 11) / 9007199254740992.0;                              /* U(0,1), 53 bits */
+                else if (kind == 2) v = (double)(int64_t)(st >> 40) / (double)(1 << (int)((st >> 8) % 20));   /* exact ties at k / 2^j */
+                else if (kind == 3) v = ((double)(st >> 11) / 9007199254740992.0 - 0.5) * 65536.0;
+                else v = (double)((st >> 20) % 100000000ull) / 10000.0 + ((st & 1) ? 0.00005 : 0.0);
+            }
+            for (int d = 0; d <= 18; d += (rep < 64 ? 1 : 4)) {
+                char a[512], b[64];
+                memset(b, 0x7f, sizeof b);
+                const size_t k = cgb_format_fixed(b, v, d);
+                ++total;
+                if (!k) continue;
+                ++covered;
+                const int w = snprintf(a, sizeof a, "%.*f\n", d, v);
+                CHECK(k <= 48 && (size_t)w == k && memcmp(a, b, k) == 0 && b[k] == 0x7f, "format_fixed(%a, %d) = %.*s, printf %s", v, d, (int)k, b, a);
+            }
+        }
+        CHECK(covered * 10 > total * 6, "the fast path covers most values (%ld of %ld)", covered, total);
+        char b[64];
+        CHECK(cgb_format_fixed(b, 1.0 / 0.0, 4) == 0 && cgb_format_fixed(b, 0.0 / 0.0, 4) == 0 && cgb_format_fixed(b, 1e300, 4) == 0
+              && cgb_format_fixed(b, 1.0, 18) == 0 && cgb_format_fixed(b, 1.0, -1) == 0, "values left to printf");
+    }
+
     FILE *nul = fopen("/dev/null", "w");
     const double m[6] = {1, 2, 3, 4, 5, 6};
     cgb_print_vector(nul, m, 2, 3);
