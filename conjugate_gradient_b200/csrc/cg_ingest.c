@@ -8,6 +8,12 @@
  * two pinned staging buffers into HBM and lets the GPU tokenise and convert them
  * (cg_ingest.cu); the full matrix never exists on the host.  b and x0 are n values each and
  * use the host parser (cg_io.c).
+ *
+ * Environment (read at every call; for measurements, tools/ingest_rate.py):
+ *   CGB_INGEST_TIMING=1      one line on stderr per load: where the time went
+ *   CGB_INGEST_CHUNK_MIB=C   bytes per staging chunk (default 8 MiB, 1..256)
+ *   CGB_INGEST_TEAM=T        members of the copy team (default min(8, CPUs / ranks), chunk / 512 KiB at most)
+ *   CGB_INGEST_NO_POOL=1     no team: threads started and joined per chunk (cgb_parallel_copy), as in round 1
  */
 #define _GNU_SOURCE
 #include <cuda_runtime_api.h>
