@@ -260,20 +260,40 @@ int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int p
     }
     int T = stage_threads(c);
     if (mode == CGB_H2D_STAGED && !chunk_given) {
-        /* The ring is pinned memory, and pinning is not free: cudaHostAlloc measured 0.42 ms per MiB (2.4 GB/s) on
-         * the bench box, so the full 8 x 2 x 8 MiB ring costs 58 ms -- more than the whole upload of an n = 8192 system
+        /* The ring is pinned memory, and pinning is not free: cudaHostAlloc measured 0.37-0.45 ms per MiB on the bench
+         * boxes, so the full 8 x 2 x 8 MiB ring costs 45-58 ms -- more than the whole upload of an n = 8192 system
          * (537 MB: 10 ms at the pinned rate, 50 ms through the driver).  A caller shaped like the reference's main()
-         * calls conjugrad() ONCE, so the first call is the one that counts: the ring is sized from the bytes to move,
-         * total / 40 (pinning then costs about half of what the copy takes), between 2 MiB and threads x 2 x the
-         * piece size that is best once the ring exists; it only ever grows, and a later call uses what is there.
-         * Below 64 MiB the driver's own path (11 GB/s, no set-up) wins.  profiles/r02_first_call.txt */
+         * calls conjugrad() ONCE, so the first call is the one that counts.  Measured (tools/first_call.py,
+         * profiles/r02_first_call_slots.txt): a ring of 13-16 MiB worked by 4 threads with ~2 MiB slots already moves
+         * 44-47 GB/s (the full ring: 50-52), and a larger ring's pinning is not paid back below ~20 GB of upload
+         * (n = 16384, 2.1 GB: first call 53 ms with 13 MiB of ring against 83 ms with total / 40 = 54 MiB).  So:
+         *   - total / 40, between 2 and 16 MiB, below 16 GiB of upload;
+         *   - the full ring (threads x 2 x the best piece size) for uploads of 16 GiB and more;
+         *   - a ring only ever grows; a later call uses what is there.
+         * Growing to the full ring on a context's third upload was tried and dropped: the growth cost 60-160 ms
+         * (free, pin 128 MiB, more streams) and the uploads after it were no faster (n = 16384: 44.4 against 45.0 ms).
+         * Below 64 MiB the driver's own path (11 GB/s, no set-up) wins. */
         if (total < ((size_t)64 << 20)) mode = CGB_H2D_DRIVER;
         else {
             const size_t ring_max = (size_t)T * STAGE_SLOTS * max_chunk;
-            size_t ring = total / 40;
-            if (ring < ((size_t)2 << 20)) ring = (size_t)2 << 20;
+            const int solo = c->ranks <= 1;      /* several ranks: 1 MiB slots, ring_max is small already (measured on 2, 4, 8 GPUs) */
+            size_t ring;
+            if (solo && total >= ((size_t)16 << 30)) ring = ring_max;
+            else {
+                ring = total / 40;
+                if (ring < ((size_t)2 << 20)) ring = (size_t)2 << 20;
+                if (solo && ring > ((size_t)16 << 20)) ring = (size_t)16 << 20;
+            }
             if (ring > ring_max) ring = ring_max;
             if (c->stage_pin_bytes > ring) ring = c->stage_pin_bytes < ring_max ? c->stage_pin_bytes : ring_max;
+            /* A small ring is cut into FEWER, LARGER slots: pieces under ~2 MiB move slowly whatever the thread count
+             * (profiles/r02_h2d_1gpu_sweep.json, 16 MiB of ring either way: 8 threads x 1 MiB 33.7 GB/s, 4 threads x 2 MiB
+             * 46.6; 2 threads never pass 24.5), so a thread is added per 4 MiB of ring, from two up to the team's size. */
+            if (solo) {
+                int Tr = (int)((ring + ((size_t)4 << 20) - 1) / ((size_t)4 << 20));
+                if (Tr < 2) Tr = 2;
+                if (Tr < T) T = Tr;
+            }
             chunk = ring / ((size_t)T * STAGE_SLOTS) & ~(size_t)0xffff;          /* multiple of 64 KiB */
             if (chunk < ((size_t)256 << 10)) {                                   /* few bytes: fewer threads, not smaller pieces */
                 chunk = (size_t)256 << 10;
