@@ -116,5 +116,6 @@ int  cgb_stage_mode(void);
 int  cgb_stage_mode_for(int ranks);
 int  cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int pageable, int *path_out);
 void cgb_stage_release(cgb_ctx *c);
+void cgb_stage_plan(size_t total, int ranks, int team, size_t max_chunk, size_t have_ring, int *mode_out, int *threads_out, size_t *chunk_out);
 
 #endif

@@ -240,6 +240,43 @@ static void *stage_main(void *arg)
     return NULL;
 }
 
+/* The ring's shape for a staged upload of `total` bytes when nothing in the environment fixes it: pure arithmetic
+ * (tests/test_plans.py pins the decisions measured on 1, 2, 4 and 8 GPUs).  In: the team size the host allows, the
+ * best piece size once the ring exists (8 MiB alone, 1 MiB with other ranks), the ring the context already holds.
+ * Out: the path (the driver's below 64 MiB), threads, bytes per slot. */
+void cgb_stage_plan(size_t total, int ranks, int team, size_t max_chunk, size_t have_ring, int *mode_out, int *threads_out, size_t *chunk_out)
+{
+    int T = team;
+    *mode_out = CGB_H2D_STAGED; *threads_out = T; *chunk_out = max_chunk;
+    if (total < ((size_t)64 << 20)) { *mode_out = CGB_H2D_DRIVER; return; }
+    const size_t ring_max = (size_t)T * STAGE_SLOTS * max_chunk;
+    const int solo = ranks <= 1;          /* several ranks: 1 MiB slots, ring_max is small already (measured on 2, 4, 8 GPUs) */
+    size_t ring;
+    if (solo && total >= ((size_t)16 << 30)) ring = ring_max;
+    else {
+        ring = total / 40;
+        if (ring < ((size_t)2 << 20)) ring = (size_t)2 << 20;
+        if (solo && ring > ((size_t)16 << 20)) ring = (size_t)16 << 20;
+    }
+    if (ring > ring_max) ring = ring_max;
+    if (have_ring > ring) ring = have_ring < ring_max ? have_ring : ring_max;
+    /* A small ring is cut into FEWER, LARGER slots: pieces under ~2 MiB move slowly whatever the thread count
+     * (profiles/r02_h2d_1gpu_sweep.json, 16 MiB of ring either way: 8 threads x 1 MiB 33.7 GB/s, 4 threads x 2 MiB
+     * 46.6; 2 threads never pass 24.5), so a thread is added per 4 MiB of ring, from two up to the team's size. */
+    if (solo) {
+        int Tr = (int)((ring + ((size_t)4 << 20) - 1) / ((size_t)4 << 20));
+        if (Tr < 2) Tr = 2;
+        if (Tr < T) T = Tr;
+    }
+    size_t chunk = ring / ((size_t)T * STAGE_SLOTS) & ~(size_t)0xffff;              /* multiple of 64 KiB */
+    if (chunk < ((size_t)256 << 10)) {                                              /* few bytes: fewer threads, not smaller pieces */
+        chunk = (size_t)256 << 10;
+        T = (int)(ring / (STAGE_SLOTS * chunk));
+        if (T < 1) T = 1;
+    }
+    *threads_out = T; *chunk_out = chunk;
+}
+
 /* All runs to the device; returns when every byte has arrived.  *path_out says how. */
 int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int pageable, int *path_out)
 {
@@ -273,34 +310,7 @@ int cgb_stage_upload(cgb_ctx *c, const cgb_stage_run *runs, int64_t nruns, int p
          * Growing to the full ring on a context's third upload was tried and dropped: the growth cost 60-160 ms
          * (free, pin 128 MiB, more streams) and the uploads after it were no faster (n = 16384: 44.4 against 45.0 ms).
          * Below 64 MiB the driver's own path (11 GB/s, no set-up) wins. */
-        if (total < ((size_t)64 << 20)) mode = CGB_H2D_DRIVER;
-        else {
-            const size_t ring_max = (size_t)T * STAGE_SLOTS * max_chunk;
-            const int solo = c->ranks <= 1;      /* several ranks: 1 MiB slots, ring_max is small already (measured on 2, 4, 8 GPUs) */
-            size_t ring;
-            if (solo && total >= ((size_t)16 << 30)) ring = ring_max;
-            else {
-                ring = total / 40;
-                if (ring < ((size_t)2 << 20)) ring = (size_t)2 << 20;
-                if (solo && ring > ((size_t)16 << 20)) ring = (size_t)16 << 20;
-            }
-            if (ring > ring_max) ring = ring_max;
-            if (c->stage_pin_bytes > ring) ring = c->stage_pin_bytes < ring_max ? c->stage_pin_bytes : ring_max;
-            /* A small ring is cut into FEWER, LARGER slots: pieces under ~2 MiB move slowly whatever the thread count
-             * (profiles/r02_h2d_1gpu_sweep.json, 16 MiB of ring either way: 8 threads x 1 MiB 33.7 GB/s, 4 threads x 2 MiB
-             * 46.6; 2 threads never pass 24.5), so a thread is added per 4 MiB of ring, from two up to the team's size. */
-            if (solo) {
-                int Tr = (int)((ring + ((size_t)4 << 20) - 1) / ((size_t)4 << 20));
-                if (Tr < 2) Tr = 2;
-                if (Tr < T) T = Tr;
-            }
-            chunk = ring / ((size_t)T * STAGE_SLOTS) & ~(size_t)0xffff;          /* multiple of 64 KiB */
-            if (chunk < ((size_t)256 << 10)) {                                   /* few bytes: fewer threads, not smaller pieces */
-                chunk = (size_t)256 << 10;
-                T = (int)(ring / (STAGE_SLOTS * chunk));
-                if (T < 1) T = 1;
-            }
-        }
+        cgb_stage_plan(total, c->ranks, T, max_chunk, c->stage_pin_bytes, &mode, &T, &chunk);
     }
     if (mode != CGB_H2D_DIRECT && mode != CGB_H2D_DRIVER && total < 2 * chunk) mode = CGB_H2D_DRIVER;   /* small: not worth a thread team */
     if (path_out) *path_out = mode;

@@ -98,3 +98,47 @@ def test_symmetric_product_split():
     assert L.cgk_symv_pick_split(136, 148) == 1                 # >= 0.9 x SMs
     assert L.cgk_symv_pick_split(100, 148) == 2                 # >= SMs / 2
     assert L.cgk_symv_pick_split(36, 148) == 4                  # n = 4096: few tiles, 4 CTAs each
+
+
+# ----------------------------------------------------------------- staging ring of malloc'ed host buffers (cg_stage.c)
+MiB, GiB = 1 << 20, 1 << 30
+STAGED, DRIVER = 2, 3
+
+
+def ring_plan(total, ranks, team, have=0):
+    L = cg.lib()
+    L.cgb_stage_plan.argtypes = [C.c_size_t, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                 C.POINTER(C.c_size_t)]
+    L.cgb_stage_plan.restype = None
+    mode, T, chunk = C.c_int(), C.c_int(), C.c_size_t()
+    L.cgb_stage_plan(total, ranks, team, (1 if ranks > 1 else 8) * MiB, have, C.byref(mode), C.byref(T), C.byref(chunk))
+    return mode.value, T.value, chunk.value
+
+
+def test_staging_ring_shapes_are_the_measured_ones():
+    """cgb_stage_plan: what the ring of pinned slots looks like per upload size and rank count.  Every line is a
+    configuration measured on B200 boxes (profiles/r02_h2d_*.json, r02_first_call_slots.txt); the N > 1 lines in
+    particular cannot be re-measured cheaply, so an edit that changes them must fail here."""
+    # one rank, the bench size (34 GB): the full ring, 8 threads x 2 slots x 8 MiB
+    assert ring_plan(8 * 65536 * 65536, 1, 8) == (STAGED, 8, 8 * MiB)
+    # one rank, asserted-symmetric upload of the same system (17 GB): still the full ring
+    assert ring_plan(8 * 65536 * 65537 // 2, 1, 8) == (STAGED, 8, 8 * MiB)
+    # one rank, one-shot sizes: total / 40 capped at 16 MiB, a thread per 4 MiB of ring
+    m, T, ch = ring_plan(8 * 16384 * 16384, 1, 8)
+    assert (m, T, ch) == (STAGED, 4, 2 * MiB)
+    m, T, ch = ring_plan(8 * 8192 * 8192, 1, 8)                # 537 MB -> 13.4 MB of ring
+    assert m == STAGED and T == 4 and 1.5 * MiB <= ch <= 2 * MiB and ch % 65536 == 0
+    m, T, ch = ring_plan(8 * 4096 * 4096, 1, 8)                # 134 MB -> 3.4 MB of ring: two threads
+    assert m == STAGED and T == 2 and 768 * 1024 <= ch <= MiB
+    # below 64 MiB: the driver's own path
+    assert ring_plan(8 * 2048 * 2048, 1, 8)[0] == DRIVER
+    # a context that already holds a larger ring uses it
+    assert ring_plan(8 * 8192 * 8192, 1, 8, have=128 * MiB) == (STAGED, 8, 8 * MiB)
+    # several ranks uploading at once: 1 MiB slots (8 ranks on 32 CPUs: 4 threads each; 2 ranks: 8 threads each)
+    assert ring_plan(8 * 8192 * 65536, 8, 4) == (STAGED, 4, 1 * MiB)
+    assert ring_plan(8 * 16384 * 65536, 4, 8) == (STAGED, 8, 1 * MiB)
+    assert ring_plan(8 * 32768 * 65536, 2, 8) == (STAGED, 8, 1 * MiB)
+    assert ring_plan(8 * 16384 * 131072, 8, 4) == (STAGED, 4, 1 * MiB)
+    # several ranks, a small system: the ring shrinks with the bytes, the team does not fall below 256 KiB slots
+    m, T, ch = ring_plan(8 * 1024 * 8192, 8, 4)                # 67 MB per rank -> 2 MiB of ring
+    assert m == STAGED and T * 2 * ch <= 2 * MiB and ch >= 256 * 1024
