@@ -222,6 +222,12 @@ static void *span_parse(void *arg)
 static int io_threads(size_t len)
 {
     long nc = sysconf(_SC_NPROCESSORS_ONLN);
+    {
+        /* a process pinned to fewer CPUs than are online (taskset, a container's cpuset) gets threads for those:
+         * the copy team's workers spin between chunks and must not outnumber the CPUs they may run on */
+        cpu_set_t set;
+        if (sched_getaffinity(0, sizeof set, &set) == 0) { const int k = CPU_COUNT(&set); if (k > 0 && k < nc) nc = k; }
+    }
     const char *e = getenv("CGB_IO_THREADS");
     if (e && *e) nc = atol(e);
     if (nc < 1) nc = 1;

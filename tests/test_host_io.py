@@ -314,3 +314,23 @@ def test_print_format_is_the_real_printers(tmp_path):
     subprocess.run(["gcc", str(src), os.path.join(csrc, "cg_io.c"), "-I", csrc, "-o", str(exe), "-lpthread", "-lm"], check=True)
     ours = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout
     assert ours == real
+
+
+def test_host_thread_counts_follow_the_cpu_affinity_mask():
+    """io_threads(): a process pinned to two CPUs (taskset, a container's cpuset) gets a copy team of two -- its
+    workers spin between chunks and must not outnumber the CPUs they may run on (8 spinning on 2 CPUs measured
+    4x slower than 2)."""
+    import subprocess
+    import sys
+    if len(os.sched_getaffinity(0)) < 2:
+        pytest.skip("needs two CPUs")
+    two = sorted(os.sched_getaffinity(0))[:2]
+    code = ("import os, ctypes as C\n"
+            f"os.sched_setaffinity(0, {{{two[0]}, {two[1]}}})\n"
+            "import conjugate_gradient_b200 as cg\n"
+            "L = cg.lib(); L.cgb_copy_pool_threads.argtypes = [C.c_size_t]; L.cgb_copy_pool_threads.restype = C.c_int\n"
+            "print(L.cgb_copy_pool_threads(8 << 20), L.cgb_copy_pool_threads(1 << 20))\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                       env={k: v for k, v in os.environ.items() if k != "CGB_IO_THREADS"})
+    assert r.returncode == 0, r.stderr[-1500:]
+    assert r.stdout.split() == ["2", "2"]
