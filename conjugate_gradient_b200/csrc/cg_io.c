@@ -171,15 +171,15 @@ typedef struct {
     int irregular;
 } span_job;
 
-/* Token starts in [beg, end): a non-separator byte whose predecessor is a separator (or beg). */
-static void *span_count(void *arg)
+/* Token starts in [beg, end): a non-separator byte whose predecessor is a separator (or beg, which is a cut:
+ * "after a separator").  *junk is set when a byte >= 0x80 was seen (a BOM: the sequential path decides). */
+static inline int64_t count_range(const char *beg, const char *end, unsigned *junk_out)
 {
-    span_job *j = arg;
     int64_t k = 0;
-    unsigned prev_sep = 1, junk = 0;                       /* the span starts at a cut: "after a separator" */
-    const char *p = j->beg;
+    unsigned prev_sep = 1, junk = 0;
+    const char *p = beg;
 #if defined(__SSE2__)
-    for (; j->end - p >= 16; p += 16) {
+    for (; end - p >= 16; p += 16) {
         unsigned high;
         const unsigned sep = sep_mask16(p, &high);
         const unsigned starts = ~sep & ((sep << 1) | prev_sep) & 0xFFFFu;
@@ -188,15 +188,23 @@ static void *span_count(void *arg)
         junk |= high;
     }
 #endif
-    for (; p < j->end; ++p) {
+    for (; p < end; ++p) {
         const unsigned char ch = (unsigned char)*p;
         const unsigned sep = (unsigned)is_sep(ch);
         junk |= ch & 0x80u;
         k += (int64_t)(~sep & prev_sep & 1u);
         prev_sep = sep;
     }
-    if (junk) j->irregular = 1;                            /* BOM or junk: sequential path decides */
-    j->count = k;
+    *junk_out |= junk;
+    return k;
+}
+
+static void *span_count(void *arg)
+{
+    span_job *j = arg;
+    unsigned junk = 0;
+    j->count = count_range(j->beg, j->end, &junk);
+    if (junk) j->irregular = 1;
     return NULL;
 }
 
@@ -441,6 +449,52 @@ static int64_t parse_parallel(const char *buf, size_t len, double *dst, int64_t 
 /* Whole file, read-only: mmap when possible (no copy of a multi-GB text), else slurp. */
 typedef cgb_text text_t;
 
+/* Which file a mapping shows: (device, inode, size, mtime, ctime), kept beside the mappings this file hands out
+ * (cgb_text's layout is shared with callers and stays three fields).  The token locator uses it to recognise the
+ * same unchanged file when several ranks of one process ask about it. */
+typedef struct { dev_t dev; ino_t ino; off_t size; struct timespec mtim, ctim; } file_id;
+#define MAP_SLOTS 32
+static pthread_mutex_t g_map_mu = PTHREAD_MUTEX_INITIALIZER;
+static struct { const char *p; file_id id; } g_maps[MAP_SLOTS];
+
+static void map_register(const char *p, const struct stat *sb)
+{
+    pthread_mutex_lock(&g_map_mu);
+    for (int i = 0; i < MAP_SLOTS; ++i)
+        if (!g_maps[i].p) {
+            g_maps[i].p = p;
+            g_maps[i].id.dev = sb->st_dev; g_maps[i].id.ino = sb->st_ino; g_maps[i].id.size = sb->st_size;
+            g_maps[i].id.mtim = sb->st_mtim; g_maps[i].id.ctim = sb->st_ctim;
+            break;
+        }                                                  /* table full: this mapping is simply not shared */
+    pthread_mutex_unlock(&g_map_mu);
+}
+
+static int map_lookup(const char *p, file_id *id)
+{
+    int found = 0;
+    pthread_mutex_lock(&g_map_mu);
+    for (int i = 0; i < MAP_SLOTS && !found; ++i)
+        if (g_maps[i].p == p) { *id = g_maps[i].id; found = 1; }
+    pthread_mutex_unlock(&g_map_mu);
+    return found;
+}
+
+static void map_forget(const char *p)
+{
+    pthread_mutex_lock(&g_map_mu);
+    for (int i = 0; i < MAP_SLOTS; ++i)
+        if (g_maps[i].p == p) { g_maps[i].p = NULL; break; }
+    pthread_mutex_unlock(&g_map_mu);
+}
+
+static int same_file(const file_id *a, const file_id *b)
+{
+    return a->dev == b->dev && a->ino == b->ino && a->size == b->size &&
+           a->mtim.tv_sec == b->mtim.tv_sec && a->mtim.tv_nsec == b->mtim.tv_nsec &&
+           a->ctim.tv_sec == b->ctim.tv_sec && a->ctim.tv_nsec == b->ctim.tv_nsec;
+}
+
 int cgb_text_open(const char *path, cgb_text *t)
 {
     memset(t, 0, sizeof *t);
@@ -452,6 +506,7 @@ int cgb_text_open(const char *path, cgb_text *t)
         if (m != MAP_FAILED) {
             (void)madvise(m, (size_t)sb.st_size, MADV_SEQUENTIAL);
             t->p = m; t->len = (size_t)sb.st_size; t->mapped = 1;
+            map_register(m, &sb);
             close(fd);
             return 0;
         }
@@ -463,7 +518,7 @@ int cgb_text_open(const char *path, cgb_text *t)
 
 void cgb_text_close(cgb_text *t)
 {
-    if (t->mapped) munmap(t->p, t->len); else free(t->p);
+    if (t->mapped) { map_forget(t->p); munmap(t->p, t->len); } else free(t->p);
     t->p = NULL;
 }
 
@@ -494,38 +549,117 @@ static const char *span_seek(const char *beg, const char *end, int64_t k)
     }
 }
 
+/* ---- locating a rank's rows.  The file is cut into blocks of LOC_BLOCK bytes (each cut moved forward to the next
+ * separator, so no token straddles two blocks); the host threads count the token starts of every block; a rank's
+ * first and one-past-last token are then found by a prefix sum over the blocks and a seek inside ONE block.
+ *
+ * The counts of the last file located are shared between the ranks of one process: `cg_b200 --gpus G` runs G
+ * ranks as threads and every one of them needs the counts of the WHOLE file -- G passes over the same bytes at the
+ * same time (8 x 470 MB for the n = 8192 file where one rank's own share is 59 MB).  The first caller counts while
+ * the others wait on the mutex, then each seeks in its own mapping.  The entry is used only for the same
+ * unchanged file (file_id) and never for slurped (unmapped) text; CGB_LOCATE_NO_CACHE=1 turns it off
+ * (measurements of a single load: tools/ingest_rate.py). */
+#define LOC_BLOCK ((size_t)1 << 20)
+static pthread_mutex_t g_loc_mu = PTHREAD_MUTEX_INITIALIZER;
+static struct {
+    int valid, irregular;
+    file_id id;
+    size_t nblocks;
+    int64_t *count;                                        /* token starts per block */
+} g_loc;
+static unsigned long g_loc_passes;                         /* counting passes made so far (under g_loc_mu) */
+
+unsigned long cgb_text_locate_passes(void)
+{
+    pthread_mutex_lock(&g_loc_mu);
+    const unsigned long k = g_loc_passes;
+    pthread_mutex_unlock(&g_loc_mu);
+    return k;
+}
+
+/* where block k begins: its nominal position moved forward to the next separator (a pure function of the text) */
+static inline const char *block_cut(const char *buf, size_t len, size_t k)
+{
+    if (k == 0) return buf;
+    const char *end = buf + len;
+    if (k > len / LOC_BLOCK) return end;                  /* also keeps k * LOC_BLOCK from overflowing */
+    const char *p = buf + k * LOC_BLOCK;
+    while (p < end && !is_sep((unsigned char)*p)) ++p;
+    return p;
+}
+
+typedef struct { const char *buf; size_t len, k0, k1; int64_t *count; int irregular; } block_job;
+static void *block_count(void *arg)
+{
+    block_job *j = arg;
+    unsigned junk = 0;
+    const char *beg = block_cut(j->buf, j->len, j->k0);
+    for (size_t k = j->k0; k < j->k1; ++k) {
+        const char *nxt = block_cut(j->buf, j->len, k + 1);
+        j->count[k] = count_range(beg, nxt, &junk);
+        beg = nxt;
+    }
+    if (junk) j->irregular = 1;
+    return NULL;
+}
+
 int64_t cgb_text_locate(const cgb_text *tx, int64_t first, int64_t count, size_t *beg_out, size_t *end_out)
 {
     const char *buf = tx->p;
     const size_t len = tx->len;
-    const int T = io_threads(len);
-    span_job job[IO_MAX_THREADS];
-    const char *end = buf + len, *cut = buf;
-    for (int t = 0; t < T; ++t) {
-        const char *nxt = (t == T - 1) ? end : buf + (len / (size_t)T) * (size_t)(t + 1);
-        if (nxt < cut) nxt = cut;
-        while (nxt < end && !is_sep((unsigned char)*nxt)) ++nxt;
-        memset(&job[t], 0, sizeof job[t]);
-        job[t].beg = cut; job[t].end = nxt;
-        cut = nxt;
+    const size_t nblocks = len / LOC_BLOCK + 1;
+    file_id id;
+    const char *off = getenv("CGB_LOCATE_NO_CACHE");
+    const int share = tx->mapped && !(off && *off && *off != '0') && map_lookup(buf, &id);
+    int64_t *cnt = NULL;                                  /* the counts this call works with */
+    int irregular = 0;
+    *beg_out = *end_out = len;
+    pthread_mutex_lock(&g_loc_mu);
+    if (share && g_loc.valid && same_file(&g_loc.id, &id) && g_loc.nblocks == nblocks) {
+        cnt = malloc(nblocks * sizeof *cnt);              /* a copy: the entry may be replaced once the mutex is gone */
+        if (cnt) { memcpy(cnt, g_loc.count, nblocks * sizeof *cnt); irregular = g_loc.irregular; }
     }
-    run_jobs(span_count, job, sizeof job[0], T);
+    if (!cnt) {
+        if (!share) pthread_mutex_unlock(&g_loc_mu);       /* nothing to share: count without holding the others up */
+        cnt = malloc(nblocks * sizeof *cnt);
+        if (!cnt) { if (share) pthread_mutex_unlock(&g_loc_mu); return -1; }   /* -1: the sequential path, which reports */
+        int T = io_threads(len);
+        if ((size_t)T > nblocks) T = (int)nblocks;
+        block_job job[IO_MAX_THREADS];
+        for (int t = 0; t < T; ++t) {
+            job[t].buf = buf; job[t].len = len; job[t].count = cnt; job[t].irregular = 0;
+            job[t].k0 = nblocks * (size_t)t / (size_t)T; job[t].k1 = nblocks * (size_t)(t + 1) / (size_t)T;
+        }
+        run_jobs(block_count, job, sizeof job[0], T);
+        for (int t = 0; t < T; ++t) irregular |= job[t].irregular;
+        if (!share) pthread_mutex_lock(&g_loc_mu);
+        ++g_loc_passes;
+        if (share) {
+            int64_t *keep = malloc(nblocks * sizeof *keep);
+            if (keep) {
+                memcpy(keep, cnt, nblocks * sizeof *keep);
+                free(g_loc.count);
+                g_loc.count = keep; g_loc.nblocks = nblocks; g_loc.irregular = irregular; g_loc.id = id; g_loc.valid = 1;
+            }
+        }
+    }
+    pthread_mutex_unlock(&g_loc_mu);
+    if (irregular) { free(cnt); return -1; }
     int64_t total = 0;
-    for (int t = 0; t < T; ++t) {
-        if (job[t].irregular) return -1;
-        job[t].offset = total;
-        total += job[t].count;
-    }
-    if (first < 0 || count < 0 || first + count > total) { *beg_out = *end_out = len; return total; }
-    const char *pb = end, *pe = end;
-    for (int t = 0; t < T; ++t) {
-        if (first >= job[t].offset && first < job[t].offset + job[t].count)
-            pb = span_seek(job[t].beg, job[t].end, first - job[t].offset);
-        const int64_t last = first + count;                /* first token AFTER the range */
-        if (last >= job[t].offset && last < job[t].offset + job[t].count)
-            pe = span_seek(job[t].beg, job[t].end, last - job[t].offset);
+    for (size_t k = 0; k < nblocks; ++k) total += cnt[k];
+    if (first < 0 || count < 0 || first + count > total) { free(cnt); return total; }
+    const char *end = buf + len, *pb = end, *pe = end;
+    const int64_t last = first + count;                    /* first token AFTER the range */
+    int64_t before = 0;
+    for (size_t k = 0; k < nblocks; ++k) {
+        if (first >= before && first < before + cnt[k])
+            pb = span_seek(block_cut(buf, len, k), block_cut(buf, len, k + 1), first - before);
+        if (last >= before && last < before + cnt[k])
+            pe = span_seek(block_cut(buf, len, k), block_cut(buf, len, k + 1), last - before);
+        before += cnt[k];
     }
     if (count == 0) pe = pb;
+    free(cnt);
     *beg_out = (size_t)(pb - buf);
     *end_out = (size_t)(pe - buf);
     return total;

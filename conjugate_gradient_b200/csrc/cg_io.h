@@ -24,6 +24,8 @@ int  cgb_token_to_double(const char *p, const char *e, double *out);
  * byte of value `first`).  Returns the number of values in the file, or -1 when the text has
  * bytes the fast tokeniser does not handle (a BOM): use cgb_read_values() then. */
 int64_t cgb_text_locate(const cgb_text *t, int64_t first, int64_t count, size_t *beg, size_t *end);
+/* counting passes over a file cgb_text_locate has made in this process (the ranks of one process share a pass) */
+unsigned long cgb_text_locate_passes(void);
 
 /* memcpy split between up to 8 threads (CGB_IO_THREADS caps it; below 2 MiB a plain memcpy). */
 void cgb_parallel_copy(void *dst, const void *src, size_t len);

@@ -145,6 +145,18 @@ static void round_trip(const char *dir, int64_t count, const char *threads)
     free(got); free(want); free(txt);
 }
 
+/* ranks of one process locating their rows in one file at the same time: one counting pass, the same answers */
+typedef struct { const char *path; int64_t first, count, total; size_t beg, end; } rank_job;
+static void *rank_locate(void *arg)
+{
+    rank_job *j = arg;
+    cgb_text t;
+    if (cgb_text_open(j->path, &t) != 0) { j->total = -99; return NULL; }
+    j->total = cgb_text_locate(&t, j->first, j->count, &j->beg, &j->end);
+    cgb_text_close(&t);
+    return NULL;
+}
+
 int main(int argc, char **argv)
 {
     const char *dir = argc > 1 ? argv[1] : "/tmp";
@@ -223,6 +235,34 @@ int main(int argc, char **argv)
         CHECK(cgb_copy_pool_threads((size_t)8 << 20) >= 1 && cgb_copy_pool_threads((size_t)8 << 20) <= 8, "team size");
         CHECK(cgb_copy_pool_threads(1000) == 1, "team size for tiny chunks");
     }
+
+#ifndef CGB_TEST_THREADS_FAIL
+    {
+        snprintf(path, sizeof path, "%s/shared.txt", dir);
+        const int64_t cnt = 400000;
+        double *v = malloc((size_t)cnt * sizeof *v);
+        for (int64_t i = 0; i < cnt; ++i) v[i] = (double)(i % 9973) / 16.0;
+        CHECK(cgb_write_values(path, v, cnt, 4) == CGB_OK, "write shared");
+        free(v);
+        unsetenv("CGB_LOCATE_NO_CACHE");
+        enum { R = 6 };
+        for (int round = 0; round < 2; ++round) {
+            rank_job job[R], solo[R];
+            pthread_t th[R];
+            const unsigned long before = cgb_text_locate_passes();
+            for (int r = 0; r < R; ++r) { job[r].path = path; job[r].first = cnt / R * r; job[r].count = cnt / R; job[r].total = 0; job[r].beg = job[r].end = 0; }
+            for (int r = 0; r < R; ++r) pthread_create(&th[r], NULL, rank_locate, &job[r]);
+            for (int r = 0; r < R; ++r) pthread_join(th[r], NULL);
+            CHECK(cgb_text_locate_passes() - before == (round == 0 ? 1u : 0u), "one counting pass for %d ranks (round %d: %lu)", R, round, cgb_text_locate_passes() - before);
+            setenv("CGB_LOCATE_NO_CACHE", "1", 1);
+            for (int r = 0; r < R; ++r) { solo[r] = job[r]; rank_locate(&solo[r]); }
+            unsetenv("CGB_LOCATE_NO_CACHE");
+            for (int r = 0; r < R; ++r)
+                CHECK(job[r].total == cnt && solo[r].total == cnt && job[r].beg == solo[r].beg && job[r].end == solo[r].end && job[r].beg < job[r].end,
+                      "rank %d: shared [%zu,%zu) alone [%zu,%zu)", r, job[r].beg, job[r].end, solo[r].beg, solo[r].end);
+        }
+    }
+#endif
 
     /* the writer's integer-arithmetic "%.{d}f": byte for byte printf's, wherever it answers at all */
     {

@@ -5,6 +5,7 @@ multi-threaded (the file is cut at separators and the pieces are converted in pa
 properties are checked on files long enough to be split as well as on short ones.  Bit-exactness
 bar: every value equals Python's float() of the same token (correctly rounded, as strtod)."""
 import os
+import time
 
 import numpy as np
 import pytest
@@ -180,8 +181,8 @@ def test_locating_a_ranks_rows_in_the_text(tmp_path, ranks):
 
 @pytest.mark.parametrize("threads", [1, 3, 8])
 def test_locate_on_several_spans_against_a_byte_level_reference(tmp_path, threads, monkeypatch):
-    """cgb_text_locate counts token starts 16 bytes at a time (SSE2) in one span per host thread and seeks the
-    rank's first / one-past-last token by skipping whole groups: tokens of 1..40 bytes, runs of every separator
+    """cgb_text_locate counts token starts 16 bytes at a time (SSE2) per 1 MiB block, the blocks shared out between
+    the host threads, and seeks the rank's first / one-past-last token inside one block by skipping whole groups: tokens of 1..40 bytes, runs of every separator
     the reader tolerates (initialize()'s "%f%*c", serialConjugate.c:92-98), tokens that straddle group and span
     borders, a file of a few MiB so that there ARE several spans; checked against numpy on the raw bytes."""
     L = _io()
@@ -334,3 +335,66 @@ def test_host_thread_counts_follow_the_cpu_affinity_mask():
                        env={k: v for k, v in os.environ.items() if k != "CGB_IO_THREADS"})
     assert r.returncode == 0, r.stderr[-1500:]
     assert r.stdout.split() == ["2", "2"]
+
+
+def test_ranks_of_one_process_share_the_counting_pass(tmp_path, monkeypatch):
+    """cgb_text_locate: `cg_b200 --gpus G` runs its ranks as threads and each needs the token counts of the whole
+    file; the first one counts, the others wait and reuse its spans (one pass instead of G).  The shared entry is
+    for the same UNCHANGED file only: a rewrite (same path, same size) is counted again, and
+    CGB_LOCATE_NO_CACHE=1 turns the sharing off."""
+    import threading
+    L = _io()
+    L.cgb_text_locate_passes.argtypes = []; L.cgb_text_locate_passes.restype = C.c_ulong
+    monkeypatch.delenv("CGB_LOCATE_NO_CACHE", raising=False)
+    ranks, n = 8, 512
+    rng = np.random.default_rng(5)
+
+    def write(path):
+        toks = ["%.4f" % v for v in rng.random(n * n)]
+        raw = ("\n".join(toks) + "\n").encode()
+        path.write_bytes(raw)
+        a = np.frombuffer(raw, np.uint8)
+        return raw, np.flatnonzero((a != 10) & np.concatenate(([True], a[:-1] == 10)))
+
+    f = tmp_path / "A.txt"
+    raw, starts = write(f)
+    assert len(raw) > (1 << 20)                                                  # several spans
+    m = n // ranks
+
+    def rank_main(r, out):
+        tx = Text()
+        assert L.cgb_text_open(os.fsencode(str(f)), C.byref(tx)) == 0            # every rank maps the file itself
+        beg, end = C.c_size_t(), C.c_size_t()
+        total = L.cgb_text_locate(C.byref(tx), r * m * n, m * n, C.byref(beg), C.byref(end))
+        out[r] = (total, beg.value, end.value)
+        L.cgb_text_close(C.byref(tx))
+
+    def all_ranks():
+        out = [None] * ranks
+        th = [threading.Thread(target=rank_main, args=(r, out)) for r in range(ranks)]
+        before = L.cgb_text_locate_passes()
+        for t in th: t.start()
+        for t in th: t.join()
+        return out, L.cgb_text_locate_passes() - before
+
+    def check(out, starts, raw):
+        for r, (total, beg, end) in enumerate(out):
+            assert total == n * n and beg == starts[r * m * n]
+            assert end == (starts[(r + 1) * m * n] if r + 1 < ranks else len(raw))
+
+    out, passes = all_ranks()
+    check(out, starts, raw)
+    assert passes == 1                                                           # eight ranks, one pass
+    out, passes = all_ranks()
+    check(out, starts, raw)
+    assert passes == 0                                                           # the same unchanged file again
+    time.sleep(0.01)
+    raw2, starts2 = write(f)                                                     # same path, same size, other digits
+    assert len(raw2) == len(raw)
+    out, passes = all_ranks()
+    check(out, starts2, raw2)
+    assert passes == 1
+    monkeypatch.setenv("CGB_LOCATE_NO_CACHE", "1")
+    out, passes = all_ranks()
+    check(out, starts2, raw2)
+    assert passes == ranks

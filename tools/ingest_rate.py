@@ -21,6 +21,7 @@ subprocess.run([cli, "--gen", str(n), "--seed", "1", "--emit-files", pre], check
 out = {"n": n, "cores": os.cpu_count(), "emit_and_solve_seconds": round(time.time() - t, 3),
        "text_bytes": os.path.getsize(pre + "_matrix.txt"), "runs": []}
 os.environ["CGB_INGEST_TIMING"] = "1"
+os.environ["CGB_LOCATE_NO_CACHE"] = "1"      # every load counts the file's tokens itself, as a fresh process would
 fa, fb, fx = (pre + s for s in ("_matrix.txt", "_vector.txt", "_x0.txt"))
 with cg.Context(0) as ctx:
     for mib in chunks:
